@@ -1,0 +1,28 @@
+"""CPU oracle for the artspeech phoneme->articulation hot path.
+
+TEST INFRASTRUCTURE ONLY.  Nothing under ``oracle/`` is part of the product:
+only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline /
+``--impl reference`` legs may import it, and only as the checker or as the
+timed CPU baseline.  The product package ``artspeech_b200`` never imports it
+and raises if its CUDA library is missing.
+
+Contents (each function cites the reference file:line it restates; paths are
+relative to the reference checkout of vribeiro1/artspeech):
+
+* ``oracle.model``     - ArtSpeech forward restated over a plain ``state_dict``
+                         (stock torch CPU ops; fp32 or fp64) and a from-the-
+                         equations GRU used to cross-check ``nn.GRU``.
+* ``oracle.geometry``  - P2CP, Euclidean, Pearson and tract variables.
+* ``oracle.area``      - NumPy fp64 restatement of ``area_function.py``.
+                         PARITY UNPINNED: the reference module cannot run
+                         (shapely / vt_tools absent, ``np.float`` crash) and
+                         has no caller or test in the reference.
+* ``oracle.reference_loader`` / ``oracle.make_golden`` - import the real
+                         reference by file path (only where /root/reference
+                         exists) to pin the restatements and to write
+                         ``tests/golden/*.npz``.
+
+Parity status: model / P2CP / TV restatements are pinned against outputs of
+the unmodified reference run in the build container (tests/golden, script
+committed).  Area function: parity unpinned (see above).
+"""

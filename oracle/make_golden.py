@@ -1,0 +1,130 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference (build container only).
+
+TEST INFRASTRUCTURE ONLY.  Run as ``python -m oracle.make_golden`` from the repo root
+where /root/reference exists.  The fixtures hold seeded synthetic inputs and the
+reference's outputs on them, so that the GPU box (which has no reference checkout)
+can pin both the oracle restatements and the CUDA path.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from artspeech_b200 import synthetic  # noqa: E402
+from oracle import model as omodel  # noqa: E402
+from oracle import reference_loader as ref  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def golden_model():
+    m = ref.models()
+    torch.manual_seed(0)
+    net = m.ArtSpeech(45, 10).eval()
+    sd = {k: v.detach().clone() for k, v in net.state_dict().items()}
+    # per-key fp64 sums pin oracle.model.make_state_dict(seed=0) to the reference init
+    keys = sorted(sd.keys())
+    sums = np.array([sd[k].double().sum().item() for k in keys])
+    abssums = np.array([sd[k].double().abs().sum().item() for k in keys])
+
+    x = synthetic.tokens(3, 12, 45, seed=3)
+    lengths = torch.tensor([12, 9, 5], dtype=torch.int32)
+    with torch.no_grad():
+        out32 = net(x, lengths)
+        out64 = net.double()(x, lengths)
+    net.float()
+
+    # second case: LayerNorm affine terms perturbed so they are exercised
+    sd2 = omodel.randomize_affine(sd, seed=1)
+    net2 = m.ArtSpeech(45, 10).eval()
+    net2.load_state_dict(sd2)
+    with torch.no_grad():
+        out32_b = net2(x, lengths)
+        out64_b = net2.double()(x, lengths)
+
+    # SimpleArtSpeech (models.py:53-96) shares the predictors
+    torch.manual_seed(0)
+    simple = m.SimpleArtSpeech(45, 10).eval()
+    with torch.no_grad():
+        out_simple = simple(x, lengths)
+    simple_sums = np.array([v.double().sum().item() for k, v in sorted(simple.state_dict().items())])
+
+    np.savez_compressed(
+        os.path.join(GOLDEN, "model_small.npz"),
+        keys=np.array(keys), sums=sums, abssums=abssums,
+        x=x.numpy(), lengths=lengths.numpy(),
+        out32=out32.numpy(), out64=out64.numpy(),
+        out32_affine=out32_b.numpy(), out64_affine=out64_b.numpy(),
+        out_simple=out_simple.numpy(), simple_sums=simple_sums,
+    )
+    print("model_small:", tuple(out32.shape), "params", sum(v.numel() for v in sd.values()))
+
+
+def golden_p2cp():
+    pm = ref.p2a_metrics()
+    tgt = synthetic.contours(24, 10, 50, seed=5)
+    pred = synthetic.perturbed(tgt, seed=6)
+    fn = pm.MeanP2CPDistance(reduction="none")
+    u, v = pred.transpose(-1, -2), tgt.transpose(-1, -2)
+    with torch.no_grad():
+        ref64 = fn(u.double(), v.double())
+        ref32 = fn(u, v)
+        mean64 = pm.MeanP2CPDistance(reduction="mean")(u.double(), v.double())
+        # ragged point counts (n != m) through the generic (*, N, 2) entry
+        u2 = u[:4, :, :37, :].contiguous()
+        v2 = v[:4, :, 5:, :].contiguous()
+        ragged64 = fn(u2.double(), v2.double())
+        med64 = pm.EuclideanDistance(reduction="none")(pred.double(), tgt.double()).mean(dim=-1)
+    np.savez_compressed(
+        os.path.join(GOLDEN, "p2cp.npz"),
+        pred=pred.numpy(), target=tgt.numpy(), ref64=ref64.numpy(), ref32=ref32.numpy(),
+        mean64=mean64.numpy(), ragged64=ragged64.numpy(), med64=med64.numpy(),
+    )
+    rel = ((ref32.double() - ref64).abs() / ref64).max().item()
+    print("p2cp:", tuple(ref64.shape), "reference fp32-vs-fp64 max rel", rel)
+
+
+def golden_tv():
+    tv = ref.tract_variables()
+    frames = synthetic.tv_frames(24, seed=7)
+    # a degenerate frame with exact ties: every contour collapsed onto lattice points
+    tie = frames[0].clone()
+    tie[:, 0, :] = (torch.arange(50) % 2).float() * 0.25 + 0.25
+    tie[:, 1, :] = 0.5
+    tie[synthetic.TV_ART_INDEX["upper-lip"], 1, :] = 0.75
+    tie[synthetic.TV_ART_INDEX["upper-incisor"], 1, :] = 0.75
+    tie[synthetic.TV_ART_INDEX["pharynx"], 1, :] = 0.75
+    frames = torch.cat([frames, tie[None]], dim=0)
+    names = synthetic.TV_ARTICULATORS
+    F = frames.shape[0]
+    val = np.zeros((F, 4)); poc = np.zeros((F, 4, 2, 2))
+    val32 = np.zeros((F, 4))
+    for f in range(F):
+        d64 = {n: frames[f, k].double().T for k, n in enumerate(names)}
+        d32 = {n: frames[f, k].T for k, n in enumerate(names)}
+        r64 = tv.calculate_vocal_tract_variables(d64)
+        r32 = tv.calculate_vocal_tract_variables(d32)
+        for k, name in enumerate(("LA", "TTCD", "TBCD", "VEL")):
+            val[f, k] = r64[name]["value"]
+            val32[f, k] = r32[name]["value"]
+            poc[f, k, 0] = r64[name]["poc_1"].numpy()
+            poc[f, k, 1] = r64[name]["poc_2"].numpy()
+        assert all(r64[n] is None for n in ("LP", "TTCL", "TBCL", "GLO"))
+    np.savez_compressed(os.path.join(GOLDEN, "tv.npz"), frames=frames.numpy(),
+                        val64=val, poc64=poc, val32=val32)
+    print("tv:", F, "frames; reference fp32-vs-fp64 max rel",
+          np.max(np.abs(val32 - val) / np.maximum(val, 1e-30)))
+
+
+if __name__ == "__main__":
+    assert ref.available(), "reference checkout not found"
+    os.makedirs(GOLDEN, exist_ok=True)
+    golden_model()
+    golden_p2cp()
+    golden_tv()
