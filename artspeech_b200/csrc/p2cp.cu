@@ -1,0 +1,233 @@
+// P2CP (point-to-closest-point) distance and mean Euclidean distance between contours.
+//
+// Replaces MeanP2CPDistance.forward (phoneme_to_articulation/metrics.py:32-46) and the
+// p2cp_distance / euclidean_distance wrappers (metrics.py:38-68) of the reference, which
+// materialise a (…, n, m) cdist tensor and run on the CPU in the evaluation loop.
+//
+// Fast path (n = m = 50, planar (2,50) contours = the model's output layout):
+//   persistent CTAs, one per SM; tiles of 128 contour pairs (2 x 51 200 B) are staged in
+//   shared memory by 1-D bulk async copies (TMA, UBLKCP) into a 2-stage mbarrier ring; two
+//   threads share a contour pair: each keeps 26 rows of u in registers as natural fp32x2
+//   pairs and streams the columns of v two at a time, so that one distance evaluation feeds
+//   both the row minimum and the column minimum.  Squared distances use the direct
+//   (dx*dx + dy*dy) form on packed FADD2/FMUL2/FFMA2, minima use FMNMX3, sqrt is taken only
+//   of the 100 minima.  The kernel is fp32-issue bound, not HBM bound (kernel K1).
+#include "asb_common.cuh"
+
+namespace {
+
+using namespace asb;
+
+constexpr int kD = 50;               // points per contour on the fast path
+constexpr int kItemF = 2 * kD;       // floats per contour
+constexpr int kTile = 128;           // contour pairs per tile
+constexpr int kThreads = 2 * kTile;  // two threads per contour pair
+constexpr int kRowPairs = 13;        // 26 rows per thread: half 0 rows 0..25, half 1 rows 24..49
+constexpr int kStages = 2;
+constexpr size_t kSmemBytes = size_t(kStages) * 2 * kTile * kItemF * sizeof(float) + kStages * sizeof(uint64_t);
+
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+p2cp50_kernel(const float* __restrict__ u, const float* __restrict__ v, float* __restrict__ out, long long items) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* su = reinterpret_cast<float*>(smem_raw);
+  float* sv = su + kStages * kTile * kItemF;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sv + kStages * kTile * kItemF);
+
+  const int tid = threadIdx.x;
+  const long long n_tiles = (items + kTile - 1) / kTile;
+
+  if (tid == 0) {
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  auto issue = [&](long long tile, int stage) {
+    const long long first = tile * kTile;
+    const long long left = items - first;
+    const uint32_t cnt = left < kTile ? uint32_t(left) : uint32_t(kTile);
+    const uint32_t bytes = cnt * kItemF * sizeof(float);
+    mbar_arrive_expect_tx(&full[stage], 2 * bytes);
+    bulk_g2s(su + stage * kTile * kItemF, u + first * kItemF, bytes, &full[stage]);
+    bulk_g2s(sv + stage * kTile * kItemF, v + first * kItemF, bytes, &full[stage]);
+  };
+
+  long long tile = blockIdx.x;
+  if (tid == 0 && tile < n_tiles) issue(tile, 0);
+
+  const int local = tid >> 1;
+  const int half = tid & 1;
+  const int r0 = half * 24;
+  const float kInf = __int_as_float(0x7f800000);
+
+  for (int k = 0; tile < n_tiles; ++k, tile += gridDim.x) {
+    const int stage = k & 1;
+    const long long next = tile + gridDim.x;
+    if (tid == 0 && next < n_tiles) issue(next, stage ^ 1);
+    mbar_wait(&full[stage], (k >> 1) & 1);
+
+    const float* pu = su + stage * kTile * kItemF + local * kItemF;
+    const float* pv = sv + stage * kTile * kItemF + local * kItemF;
+
+    f32x2 ux[kRowPairs], uy[kRowPairs];
+    float rlo[kRowPairs], rhi[kRowPairs];
+#pragma unroll
+    for (int p = 0; p < kRowPairs; ++p) {
+      ux[p] = *reinterpret_cast<const f32x2*>(pu + r0 + 2 * p);
+      uy[p] = *reinterpret_cast<const f32x2*>(pu + kD + r0 + 2 * p);
+      rlo[p] = kInf;
+      rhi[p] = kInf;
+    }
+
+    float colsum = 0.f;
+#pragma unroll 1
+    for (int j = 0; j < kD; j += 2) {
+      const float2 vx = *reinterpret_cast<const float2*>(pv + j);
+      const float2 vy = *reinterpret_cast<const float2*>(pv + kD + j);
+      const f32x2 vxa = pack2(vx.x, vx.x), vxb = pack2(vx.y, vx.y);
+      const f32x2 vya = pack2(vy.x, vy.x), vyb = pack2(vy.y, vy.y);
+      float ca = kInf, cb = kInf;
+#pragma unroll
+      for (int p = 0; p < kRowPairs; ++p) {
+        const f32x2 dxa = sub2(ux[p], vxa), dya = sub2(uy[p], vya);
+        const f32x2 dxb = sub2(ux[p], vxb), dyb = sub2(uy[p], vyb);
+        const f32x2 qa = fma2(dya, dya, mul2(dxa, dxa));
+        const f32x2 qb = fma2(dyb, dyb, mul2(dxb, dxb));
+        float a0, a1, b0, b1;
+        unpack2(qa, a0, a1);
+        unpack2(qb, b0, b1);
+        rlo[p] = min3(rlo[p], a0, b0);
+        rhi[p] = min3(rhi[p], a1, b1);
+        ca = min3(ca, a0, a1);
+        cb = min3(cb, b0, b1);
+      }
+      // the partner thread holds the other 26 rows: exchange one column each way
+      const float send = half ? ca : cb;
+      const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+      const float mine = half ? cb : ca;
+      colsum += sqrt_approx(fminf(mine, recv));
+    }
+
+    float rowsum = 0.f;
+#pragma unroll
+    for (int p = 0; p < kRowPairs; ++p) {
+      // half 1 starts at row 24: its first pair (rows 24, 25) belongs to half 0
+      const float s = sqrt_approx(rlo[p]) + sqrt_approx(rhi[p]);
+      rowsum += (half && p == 0) ? 0.f : s;
+    }
+    rowsum += __shfl_xor_sync(0xffffffffu, rowsum, 1);
+    colsum += __shfl_xor_sync(0xffffffffu, colsum, 1);
+    const long long item = tile * kTile + local;
+    if (half == 0 && item < items) out[item] = (rowsum / float(kD) + colsum / float(kD)) * 0.5f;
+
+    __syncthreads();  // every thread is done with this stage before it is refilled
+  }
+}
+
+// General contours (any n, m; planar or interleaved): one warp per contour pair, operands
+// read through L1.  Used for ragged point counts and for MeanP2CPDistance on (*, n, 2) input.
+__global__ void __launch_bounds__(256)
+p2cp_generic_kernel(const float* __restrict__ u, const float* __restrict__ v, float* __restrict__ out,
+                    long long items, int n, int m, int u_sp, int u_sc, int v_sp, int v_sc) {
+  const long long item = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (item >= items) return;
+  const int lane = threadIdx.x & 31;
+  const float* pu = u + item * 2 * n;
+  const float* pv = v + item * 2 * m;
+  const float kInf = __int_as_float(0x7f800000);
+  float acc_u = 0.f, acc_v = 0.f;
+  for (int i = lane; i < n; i += 32) {
+    const float x = pu[i * u_sp], y = pu[i * u_sp + u_sc];
+    float best = kInf;
+    for (int j = 0; j < m; ++j) {
+      const float dx = x - pv[j * v_sp], dy = y - pv[j * v_sp + v_sc];
+      best = fminf(best, fmaf(dy, dy, dx * dx));
+    }
+    acc_u += sqrt_approx(best);
+  }
+  for (int j = lane; j < m; j += 32) {
+    const float x = pv[j * v_sp], y = pv[j * v_sp + v_sc];
+    float best = kInf;
+    for (int i = 0; i < n; ++i) {
+      const float dx = pu[i * u_sp] - x, dy = pu[i * u_sp + u_sc] - y;
+      best = fminf(best, fmaf(dy, dy, dx * dx));
+    }
+    acc_v += sqrt_approx(best);
+  }
+  acc_u = warp_sum(acc_u);
+  acc_v = warp_sum(acc_v);
+  if (lane == 0) out[item] = (acc_u / float(n) + acc_v / float(m)) * 0.5f;
+}
+
+// mean over points of |u_k - v_k| for planar contours: one warp per contour pair.
+__global__ void __launch_bounds__(256)
+mean_euclidean_kernel(const float* __restrict__ u, const float* __restrict__ v, float* __restrict__ out,
+                      long long items, int n) {
+  const long long item = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (item >= items) return;
+  const int lane = threadIdx.x & 31;
+  const float* pu = u + item * 2 * n;
+  const float* pv = v + item * 2 * n;
+  float acc = 0.f;
+  for (int k = lane; k < n; k += 32) {
+    const float dx = pu[k] - pv[k], dy = pu[n + k] - pv[n + k];
+    acc += sqrtf(fmaf(dy, dy, dx * dx));
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) out[item] = acc / float(n);
+}
+
+}  // namespace
+
+extern "C" int asb_p2cp(const float* u, const float* v, float* out, int64_t items, int n, int m, int layout,
+                        void* stream) {
+  if (items < 0 || n <= 0 || m <= 0) return asb::set_error(ASB_ERR_INVALID, "asb_p2cp: bad shape");
+  if (layout != ASB_LAYOUT_PLANAR && layout != ASB_LAYOUT_INTERLEAVED)
+    return asb::set_error(ASB_ERR_INVALID, "asb_p2cp: bad layout %d", layout);
+  if (items == 0) return ASB_OK;
+  if (!u || !v || !out) return asb::set_error(ASB_ERR_INVALID, "asb_p2cp: null pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool aligned = ((reinterpret_cast<uintptr_t>(u) | reinterpret_cast<uintptr_t>(v)) & 15) == 0;
+  if (n == kD && m == kD && layout == ASB_LAYOUT_PLANAR && aligned) {
+    static bool configured = false;
+    if (!configured) {
+      cudaError_t e = cudaFuncSetAttribute(p2cp50_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           int(kSmemBytes));
+      if (e != cudaSuccess) return asb::check_cuda(e, "asb_p2cp: smem attribute");
+      configured = true;
+    }
+    const long long n_tiles = (items + kTile - 1) / kTile;
+    const int grid = int(n_tiles < asb::sm_count() ? n_tiles : asb::sm_count());
+    p2cp50_kernel<<<grid, kThreads, kSmemBytes, st>>>(u, v, out, items);
+    ASB_CHECK_LAUNCH("p2cp50_kernel");
+    return ASB_OK;
+  }
+  const int sp = layout == ASB_LAYOUT_PLANAR ? 1 : 2;
+  const int warps = 8;
+  const long long blocks = (items + warps - 1) / warps;
+  if (blocks > 0x7fffffffLL) return asb::set_error(ASB_ERR_INVALID, "asb_p2cp: too many items");
+  p2cp_generic_kernel<<<unsigned(blocks), warps * 32, 0, st>>>(u, v, out, items, n, m, sp,
+                                                                 layout == ASB_LAYOUT_PLANAR ? n : 1, sp,
+                                                                 layout == ASB_LAYOUT_PLANAR ? m : 1);
+  ASB_CHECK_LAUNCH("p2cp_generic_kernel");
+  return ASB_OK;
+}
+
+extern "C" int asb_mean_euclidean(const float* u, const float* v, float* out, int64_t items, int n, void* stream) {
+  if (items < 0 || n <= 0) return asb::set_error(ASB_ERR_INVALID, "asb_mean_euclidean: bad shape");
+  if (items == 0) return ASB_OK;
+  if (!u || !v || !out) return asb::set_error(ASB_ERR_INVALID, "asb_mean_euclidean: null pointer");
+  const int warps = 8;
+  const long long blocks = (items + warps - 1) / warps;
+  if (blocks > 0x7fffffffLL) return asb::set_error(ASB_ERR_INVALID, "asb_mean_euclidean: too many items");
+  mean_euclidean_kernel<<<unsigned(blocks), warps * 32, 0, static_cast<cudaStream_t>(stream)>>>(u, v, out, items, n);
+  ASB_CHECK_LAUNCH("mean_euclidean_kernel");
+  return ASB_OK;
+}

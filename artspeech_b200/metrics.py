@@ -1,0 +1,133 @@
+"""Contour metrics with the reference's names and signatures, computed by the CUDA library.
+
+Mirrors (reference paths):
+  * ``MeanP2CPDistance``, ``EuclideanDistance``   phoneme_to_articulation/metrics.py:5-46
+  * ``p2cp_distance``, ``euclidean_distance``, ``pearsons_correlation``   metrics.py:9-68
+  * ``P2CPDistance``                              phoneme_to_articulation/encoder_decoder/metrics.py:7-26
+
+CPU tensors are accepted like in the reference (its evaluation loop passes CPU tensors,
+evaluation.py:65-72): they are copied to the GPU, the kernel runs there and the result comes back
+on the input's device.  There is no CPU implementation.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+
+def _as_f32_cuda(t, dev):
+    return t.detach().to(device=dev, dtype=torch.float32, non_blocking=True)
+
+
+def _p2cp_raw(u, v, items, n, m, layout, dev):
+    out = torch.empty(items, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().asb_p2cp(_lib.ptr(u), _lib.ptr(v), _lib.ptr(out), items, n, m, layout,
+                                       _lib.stream_ptr(dev)))
+    return out
+
+
+def _is_planar_view(t):
+    """True if ``t`` (*, n, 2) is a transposed view of contiguous (*, 2, n) storage, i.e. what
+    ``p2cp_distance`` passes down (metrics.py:47-50)."""
+    return t.dim() >= 2 and t.shape[-1] == 2 and t.transpose(-1, -2).is_contiguous()
+
+
+class MeanP2CPDistance(nn.Module):
+    """phoneme_to_articulation/metrics.py:27-46.  u_ (*, N, 2), v_ (*, M, 2) -> (*) or reduced."""
+
+    def __init__(self, reduction="mean"):
+        super().__init__()
+        self.reduction = getattr(torch, reduction, lambda x: x)
+
+    def forward(self, u_, v_):
+        if u_.shape[-1] != 2 or v_.shape[-1] != 2 or u_.shape[:-2] != v_.shape[:-2]:
+            raise ValueError(f"expected (*, N, 2) and (*, M, 2) with equal leading dims, got "
+                             f"{tuple(u_.shape)} and {tuple(v_.shape)}")
+        n, m = u_.shape[-2], v_.shape[-2]
+        lead = u_.shape[:-2]
+        dev = _lib.device_of(u_, v_)
+        if _is_planar_view(u_) and _is_planar_view(v_):
+            layout = _lib.LAYOUT_PLANAR
+            uc = _as_f32_cuda(u_.transpose(-1, -2), dev)
+            vc = _as_f32_cuda(v_.transpose(-1, -2), dev)
+        else:
+            layout = _lib.LAYOUT_INTERLEAVED
+            uc = _as_f32_cuda(u_, dev).contiguous()
+            vc = _as_f32_cuda(v_, dev).contiguous()
+        items = 1
+        for s in lead:
+            items *= int(s)
+        out = _p2cp_raw(uc, vc, items, n, m, layout, dev).view(lead)
+        out = out.to(device=u_.device, dtype=u_.dtype if u_.dtype.is_floating_point else torch.float32)
+        return self.reduction(out)
+
+
+class EuclideanDistance(nn.Module):
+    """phoneme_to_articulation/metrics.py:5-24: per-point distance (*, N_art, N_samples)."""
+
+    def __init__(self, reduction="mean"):
+        super().__init__()
+        self.reduction = getattr(torch, reduction, lambda x: x)
+
+    def forward(self, outputs, targets):
+        dx = outputs[..., 0, :] - targets[..., 0, :]
+        dy = outputs[..., 1, :] - targets[..., 1, :]
+        return self.reduction(torch.sqrt(dx ** 2 + dy ** 2))
+
+
+def p2cp_distance(outputs, targets):
+    """metrics.py:38-52.  (bs, seq_len, N_art, 2, N_samples) x2 -> (bs, seq_len, N_art)."""
+    return MeanP2CPDistance(reduction="none")(outputs.transpose(-1, -2), targets.transpose(-1, -2))
+
+
+def euclidean_distance(outputs, targets):
+    """metrics.py:54-68.  (bs, seq_len, N_art, 2, N_samples) x2 -> (bs, seq_len, N_art)."""
+    if outputs.shape != targets.shape or outputs.shape[-2] != 2:
+        raise ValueError("expected two (*, 2, N_samples) tensors of equal shape")
+    dev = _lib.device_of(outputs, targets)
+    n = outputs.shape[-1]
+    lead = outputs.shape[:-2]
+    o = _as_f32_cuda(outputs, dev).contiguous()
+    t = _as_f32_cuda(targets, dev).contiguous()
+    items = o.numel() // (2 * n)
+    out = torch.empty(items, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().asb_mean_euclidean(_lib.ptr(o), _lib.ptr(t), _lib.ptr(out), items, n,
+                                                 _lib.stream_ptr(dev)))
+    return out.view(lead).to(device=outputs.device, dtype=outputs.dtype)
+
+
+def pearsons_correlation(outputs, targets):
+    """metrics.py:9-35, including its quirk (x target mean taken from the x outputs, :22).
+    Stays on the tensors' device; (bs, T, N, 2, D) -> x_corr, y_corr (bs, N, D)."""
+    eps = 1e-5
+    xo, yo = outputs[:, :, :, 0, :], outputs[:, :, :, 1, :]
+    xt, yt = targets[:, :, :, 0, :], targets[:, :, :, 1, :]
+    vxo = xo - xo.mean(dim=1, keepdim=True)
+    vxt = xt - xo.mean(dim=1, keepdim=True)
+    x_corr = (vxo * vxt).sum(1) / (torch.sqrt((vxo ** 2).sum(1)) * torch.sqrt((vxt ** 2).sum(1)) + eps)
+    vyo = yo - yo.mean(dim=1, keepdim=True)
+    vyt = yt - yt.mean(dim=1, keepdim=True)
+    y_corr = (vyo * vyt).sum(1) / (torch.sqrt((vyo ** 2).sum(1)) * torch.sqrt((vyt ** 2).sum(1)) + eps)
+    return x_corr, y_corr
+
+
+class P2CPDistance(nn.Module):
+    """Validation metric, phoneme_to_articulation/encoder_decoder/metrics.py:7-26: mean over
+    sentences of the length-masked mean P2CP in millimetres."""
+
+    def __init__(self, dataset_config):
+        super().__init__()
+        self.dataset_config = dataset_config
+        self.to_mm = self.dataset_config.RES * self.dataset_config.PIXEL_SPACING
+        self.mean_p2cp = MeanP2CPDistance(reduction="none")
+
+    def forward(self, outputs, targets, lengths):
+        p2cp = self.mean_p2cp(outputs.transpose(-1, -2), targets.transpose(-1, -2)) * self.to_mm
+        L = torch.as_tensor(lengths, device=p2cp.device).view(-1, 1)
+        mask = (torch.arange(p2cp.shape[1], device=p2cp.device).view(1, -1) < L).unsqueeze(-1)
+        per_sentence = (p2cp * mask).sum(dim=(1, 2)) / (L.view(-1) * p2cp.shape[2])
+        return per_sentence.mean().cpu()

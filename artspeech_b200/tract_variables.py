@@ -1,0 +1,102 @@
+"""Tract variables with the reference's signature, computed by the CUDA library.
+
+Mirrors tract_variables.py:13-125 of the reference (``ART_SLICES``,
+``calculate_vocal_tract_variables``) and adds the batched device entry the evaluation
+driver needs: all frames of a batch in one launch instead of one Python call
+with three ``.item()`` syncs per search (phoneme_to_articulation/__init__.py:242-261).
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import _lib
+
+# string values of the vt_tools constants imported at tract_variables.py:3-10
+LOWER_LIP = "lower-lip"
+PHARYNX = "pharynx"
+SOFT_PALATE_MIDLINE = "soft-palate-midline"
+TONGUE = "tongue"
+UPPER_LIP = "upper-lip"
+UPPER_INCISOR = "upper-incisor"
+
+# tract_variables.py:13-20
+ART_SLICES = {
+    "tongue-tip": (30, 45),
+    "tongue-body": (10, 30),
+    "upper-incisor": (25, 50),
+    "hard-palate": (0, 25),
+    "soft-palate": (35, 50),
+    "velum": (0, 15),
+}
+
+# phoneme_to_articulation/__init__.py:37-44
+REQUIRED_ARTICULATORS_FOR_TVS = [LOWER_LIP, PHARYNX, SOFT_PALATE_MIDLINE, TONGUE, UPPER_LIP, UPPER_INCISOR]
+
+TV_NAMES = ("LA", "TTCD", "TBCD", "VEL")
+# order of art_index_host in the C ABI
+_ABI_ORDER = (LOWER_LIP, PHARYNX, SOFT_PALATE_MIDLINE, TONGUE, UPPER_INCISOR, UPPER_LIP)
+# (name of arr1, offset of its slice), per TV
+_ARR1 = ((LOWER_LIP, 0), (TONGUE, 30), (TONGUE, 10), (SOFT_PALATE_MIDLINE, 0))
+
+
+def tract_variables_batch(frames, articulators):
+    """All four TVs for every contour set in one launch.
+
+    frames: (..., N_art, 2, 50) float tensor (CPU or CUDA); ``articulators``: the N_art names in
+    row order, or a dict name -> row.  Returns (val (...,4) fp32, idx (...,4,2) int32,
+    poc (...,4,2,2) fp32) on the CUDA device; idx = (i into arr1, j into arr2) of each search,
+    poc = (arr1[i], arr2[j])."""
+    if isinstance(articulators, dict):
+        index = articulators
+    else:
+        index = {name: k for k, name in enumerate(articulators)}
+    rows = (ctypes.c_int32 * 6)(*[index[name] for name in _ABI_ORDER])  # KeyError like the reference
+    if frames.dim() < 3 or frames.shape[-2] != 2 or frames.shape[-1] != 50:
+        raise ValueError(f"expected (..., N_art, 2, 50) contours, got {tuple(frames.shape)}")
+    dev = _lib.device_of(frames)
+    f = frames.detach().to(device=dev, dtype=torch.float32).contiguous()
+    lead = f.shape[:-3]
+    n_art = f.shape[-3]
+    sets = f.numel() // (n_art * 100)
+    val = torch.empty(sets, 4, dtype=torch.float32, device=dev)
+    idx = torch.empty(sets, 4, 2, dtype=torch.int32, device=dev)
+    poc = torch.empty(sets, 4, 2, 2, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().asb_tract_variables(_lib.ptr(f), sets, n_art, rows, _lib.ptr(val), _lib.ptr(idx),
+                                                  _lib.ptr(poc), _lib.stream_ptr(dev)))
+    return val.view(*lead, 4), idx.view(*lead, 4, 2), poc.view(*lead, 4, 2, 2)
+
+
+def calculate_vocal_tract_variables(inputs_dict):
+    """tract_variables.py:73-125.  ``inputs_dict``: articulator name -> (50, 2) tensor.  Returns
+    {"LA"|"TTCD"|"TBCD"|"VEL": {"value": float, "poc_1": (2,) tensor, "poc_2": (2,) tensor},
+     "LP"|"TTCL"|"TBCL"|"GLO": None}; the PoCs are views into the inputs like the reference's."""
+    arrs = [inputs_dict[name] for name in _ABI_ORDER]  # KeyError for a missing articulator
+    for a in arrs:
+        if a.dim() != 2 or a.shape != (50, 2):
+            raise ValueError(f"expected (50, 2) contours, got {tuple(a.shape)}")
+    frame = torch.stack([a.transpose(0, 1) for a in arrs], dim=0)  # (6, 2, 50)
+    val, idx, _ = tract_variables_batch(frame, {name: k for k, name in enumerate(_ABI_ORDER)})
+    val = val.cpu().tolist()
+    idx = idx.cpu().tolist()
+
+    uinc, spm = inputs_dict[UPPER_INCISOR], inputs_dict[SOFT_PALATE_MIDLINE]
+
+    def arr2_point(k, j):
+        if k == 0:
+            return inputs_dict[UPPER_LIP][j]
+        if k == 1:
+            return uinc[25 + j]
+        if k == 2:
+            return uinc[j] if j < 25 else spm[35 + (j - 25)]
+        return inputs_dict[PHARYNX][j]
+
+    out = {"LA": None, "LP": None, "TTCD": None, "TTCL": None, "TBCD": None, "TBCL": None, "VEL": None,
+           "GLO": None}
+    for k, name in enumerate(TV_NAMES):
+        a1_name, a1_off = _ARR1[k]
+        i, j = idx[k]
+        out[name] = {"value": val[k], "poc_1": inputs_dict[a1_name][a1_off + i], "poc_2": arr2_point(k, j)}
+    return out

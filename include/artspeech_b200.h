@@ -1,0 +1,130 @@
+/*
+ * artspeech_b200 - C ABI of the B200-native phoneme->articulation hot path.
+ *
+ * The reference (vribeiro1/artspeech) is pure Python and has no FFI layer; the
+ * boundary it exposes for this path is its Python API.  Each entry point below
+ * names the reference function it replaces (paths relative to the reference
+ * checkout).  The Python package `artspeech_b200` binds these with ctypes and
+ * re-exports the reference's names and signatures.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless its name ends in `_host`;
+ *  - the caller owns all buffers; the library allocates only inside asb_model_create
+ *    (re-packed weight arena) and frees it in asb_model_destroy;
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *    all work is enqueued on it, nothing synchronises unless stated;
+ *  - return value: 0 = ok, otherwise an asb_status (>0) ; asb_last_error_string()
+ *    gives a thread-local description.  CUDA launch errors are reported as
+ *    ASB_ERR_CUDA with the cudaGetErrorString text.
+ */
+#ifndef ARTSPEECH_B200_H
+#define ARTSPEECH_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ASB_ABI_VERSION 1
+#if defined(__GNUC__)
+#define ASB_API __attribute__((visibility("default")))
+#else
+#define ASB_API
+#endif
+
+typedef enum asb_status {
+  ASB_OK = 0,
+  ASB_ERR_INVALID = 1,   /* bad argument (shape, null pointer, alignment)      -> Python ValueError   */
+  ASB_ERR_UNSORTED = 2,  /* lengths not sorted descending / out of range        -> Python RuntimeError
+                            (what pack_padded_sequence raises, models.py:136)                          */
+  ASB_ERR_CUDA = 3,      /* CUDA runtime error                                  -> Python RuntimeError */
+  ASB_ERR_WORKSPACE = 4, /* workspace too small                                 -> Python ValueError   */
+  ASB_ERR_UNSUPPORTED = 5
+} asb_status;
+
+ASB_API int asb_abi_version(void);
+ASB_API const char* asb_last_error_string(void);
+/* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
+ASB_API int64_t asb_launch_count(void);
+
+/* ------------------------------------------------------------------ geometry */
+
+/* Point layouts of a contour of n points */
+#define ASB_LAYOUT_PLANAR 0      /* (2, n): x row then y row - the model's output layout (models.py:31)   */
+#define ASB_LAYOUT_INTERLEAVED 1 /* (n, 2): what MeanP2CPDistance.forward receives (metrics.py:35-36)     */
+
+/* MeanP2CPDistance.forward with reduction="none", phoneme_to_articulation/metrics.py:32-46;
+ * with ASB_LAYOUT_PLANAR it is metrics.py:38-52 `p2cp_distance` without the transposes.
+ * u: items contours of n points, v: items contours of m points, out: (items) fp32.
+ * out[k] = ( sum_i min_j |u_i-v_j| / n + sum_j min_i |u_i-v_j| / m ) / 2, distances evaluated
+ * in fp32 with the direct (dx^2+dy^2) form, sqrt after the minimum. */
+ASB_API int asb_p2cp(const float* u, const float* v, float* out, int64_t items, int n, int m,
+             int layout, void* stream);
+
+/* EuclideanDistance(reduction="none")(...).mean(-1), metrics.py:54-68 over
+ * phoneme_to_articulation/metrics.py:10-24.  Planar (2,n) contours -> out (items). */
+ASB_API int asb_mean_euclidean(const float* u, const float* v, float* out, int64_t items, int n,
+                       void* stream);
+
+/* calculate_vocal_tract_variables, tract_variables.py:73-125 (LA, TTCD, TBCD, VEL via
+ * _calculate_TV :23-35) for `sets` contour sets of shape (n_art, 2, 50), planar.
+ * art_index_host[6]: rows of lower-lip, pharynx, soft-palate-midline, tongue, upper-incisor,
+ * upper-lip inside a set (host array).
+ * val (sets,4) fp32 distance; idx (sets,4,2) int32 = (i into arr1, j into arr2) with the
+ * reference's tie-break (smallest j, then smallest i); poc (sets,4,2,2) fp32 = arr1[i], arr2[j].
+ * TV order: LA, TTCD, TBCD, VEL. */
+ASB_API int asb_tract_variables(const float* sets_ptr, int64_t sets, int n_art,
+                        const int32_t* art_index_host, float* val, int32_t* idx, float* poc,
+                        void* stream);
+
+/* ------------------------------------------------------------------ model */
+
+typedef struct asb_model asb_model;
+
+#define ASB_CELL_GRU 3
+#define ASB_CELL_LSTM 4
+#define ASB_PRECISION_FAST 0 /* bf16 recurrent GEMM, tf32 elsewhere, fp32 accumulate/state (2e-3 gate) */
+#define ASB_PRECISION_FP32 1 /* 3xTF32 / FFMA everywhere (1e-5 gate)                                  */
+
+/* Device pointers to fp32 parameters in the reference's state_dict layout (SURVEY.md 8b;
+ * models.py:109-120).  Arrays of per-articulator pointers are HOST arrays of device pointers. */
+typedef struct asb_weights {
+  const float* embedding;          /* (V, E) */
+  const float* rnn_w_ih[2][2];     /* [layer][dir] (G*H, E or 2H) */
+  const float* rnn_w_hh[2][2];     /* (G*H, H) */
+  const float* rnn_b_ih[2][2];     /* (G*H) */
+  const float* rnn_b_hh[2][2];     /* (G*H) */
+  const float* linear_w;           /* (H, 2H)  linear.0 */
+  const float* linear_b;           /* (H) */
+  const float* const* ln0_w; const float* const* ln0_b;   /* [N] (H)      predictors.i.linear.0 */
+  const float* const* fc1_w; const float* const* fc1_b;   /* [N] (256,H)  predictors.i.linear.1 */
+  const float* const* ln1_w; const float* const* ln1_b;   /* [N] (256)    predictors.i.linear.3 */
+  const float* const* fc2_w; const float* const* fc2_b;   /* [N] (256,256) predictors.i.linear.4 */
+  const float* const* ln2_w; const float* const* ln2_b;   /* [N] (256)    predictors.i.linear.6 */
+  const float* const* xh_w;  const float* const* xh_b;    /* [N] (D,256)  predictors.i.x_coords */
+  const float* const* yh_w;  const float* const* yh_b;    /* [N] (D,256)  predictors.i.y_coords */
+} asb_weights;
+
+/* Re-packs the weights into the kernels' layouts (synchronises `stream`).  Replaces
+ * ArtSpeech.__init__ + load_state_dict + .to(device), models.py:99-120. */
+ASB_API int asb_model_create(const asb_weights* w, int vocab, int n_art, int embed_dim, int hidden,
+                     int n_samples, int cell, int precision, void* stream, asb_model** out);
+ASB_API void asb_model_destroy(asb_model* m);
+
+/* Bytes of scratch asb_model_forward needs for a (B, T) batch. */
+ASB_API size_t asb_model_workspace_bytes(const asb_model* m, int B, int T);
+
+/* ArtSpeech.forward(x, lengths), models.py:126-145.
+ * x (B, T_in) int64 tokens (row stride T_in); lengths_host (B) sorted descending, each in
+ * [1, T_in]; out (B, T, n_art, 2, n_samples) fp32 contiguous with T = lengths_host[0].
+ * Rows past a sequence's length receive the constant padded frame, as the reference does.
+ * use_rnn = 0 gives SimpleArtSpeech.forward (models.py:78-96; embedding -> linear). */
+ASB_API int asb_model_forward(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host, int B,
+                      float* out, void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ARTSPEECH_B200_H */
