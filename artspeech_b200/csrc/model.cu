@@ -1,11 +1,181 @@
-// placeholder until the model kernels land (replaced in the next commit)
-#include "asb_common.cuh"
-struct asb_model { int dummy; };
-extern "C" int asb_model_create(const asb_weights*, int, int, int, int, int, int, int, void*, asb_model**) {
-  return asb::set_error(ASB_ERR_UNSUPPORTED, "model kernels not built yet");
+// asb_model: weight re-packing and the forward pass of ArtSpeech
+// (phoneme_to_articulation/encoder_decoder/models.py:99-145) assembled from the kernels in
+// gru.cu and decoder.cu:
+//
+//   tokens --gather(tab0 = E.W_ih_l0^T + b)--> gi0 --GRU layer 0 (fwd | bwd CTAs)--> out0
+//   out0 --[M,256]x[256,768] tf32 GEMM--> gi1 --GRU layer 1--> out1 (zeros at padded steps)
+//   out1 --fused decoder (linear.0 + 10 predictors + sigmoid)--> contours (B, T, N, 2, D)
+#include <new>
+#include <vector>
+
+#include "model.cuh"
+
+namespace {
+
+using namespace asb;
+
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct ArenaPlan {
+  size_t total = 0;
+  size_t take(size_t bytes) {
+    const size_t off = total;
+    total += align_up(bytes, 256);
+    return off;
+  }
+};
+
+struct Workspace {
+  int* lengths;
+  float* gi;
+  float* out0;
+  float* out1;
+  size_t bytes;
+};
+
+Workspace plan_workspace(const asb_model* m, void* base, int B, int T) {
+  ArenaPlan p;
+  const size_t frames = (size_t)B * T;
+  const size_t o_len = p.take(sizeof(int) * (size_t)B);
+  const size_t o_gi = p.take(sizeof(float) * frames * 2 * m->G * kH);
+  const size_t o_out0 = p.take(sizeof(float) * frames * 2 * kH);
+  const size_t o_out1 = p.take(sizeof(float) * frames * 2 * kH);
+  char* b = static_cast<char*>(base);
+  Workspace w;
+  w.lengths = reinterpret_cast<int*>(b + o_len);
+  w.gi = reinterpret_cast<float*>(b + o_gi);
+  w.out0 = reinterpret_cast<float*>(b + o_out0);
+  w.out1 = reinterpret_cast<float*>(b + o_out1);
+  w.bytes = p.total;
+  return w;
 }
-extern "C" void asb_model_destroy(asb_model*) {}
-extern "C" size_t asb_model_workspace_bytes(const asb_model*, int, int) { return 0; }
-extern "C" int asb_model_forward(asb_model*, const int64_t*, int, const int32_t*, int, float*, void*, size_t, void*) {
-  return asb::set_error(ASB_ERR_UNSUPPORTED, "model kernels not built yet");
+
+}  // namespace
+
+extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, int embed_dim, int hidden,
+                                int n_samples, int cell, int precision, void* stream, asb_model** out) {
+  if (!src || !out) return set_error(ASB_ERR_INVALID, "asb_model_create: null argument");
+  *out = nullptr;
+  if (hidden != kH) return set_error(ASB_ERR_UNSUPPORTED, "asb_model_create: hidden_size must be %d (got %d)", kH, hidden);
+  if (cell != ASB_CELL_GRU)
+    return set_error(ASB_ERR_UNSUPPORTED, "asb_model_create: only the GRU cell (every shipped config) is built; LSTM is not");
+  if (vocab <= 0 || n_art <= 0 || embed_dim <= 0 || n_samples <= 0 || 2 * n_samples > kHeadPad)
+    return set_error(ASB_ERR_INVALID, "asb_model_create: bad sizes (vocab %d, n_art %d, embed %d, n_samples %d <= %d)",
+                     vocab, n_art, embed_dim, n_samples, kHeadPad / 2);
+  if (precision != ASB_PRECISION_FAST && precision != ASB_PRECISION_FP32)
+    return set_error(ASB_ERR_INVALID, "asb_model_create: bad precision %d", precision);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+  asb_model* m = new (std::nothrow) asb_model();
+  if (!m) return set_error(ASB_ERR_INVALID, "asb_model_create: out of host memory");
+  m->V = vocab; m->N = n_art; m->E = embed_dim; m->H = hidden; m->D = n_samples; m->G = cell;
+  m->precision = precision;
+  const int GH = m->G * kH;
+
+  ArenaPlan p;
+  const size_t o_tab0 = p.take(sizeof(float) * 2 * (size_t)vocab * GH);
+  size_t o_frag[2][2], o_wt[2][2], o_bn[2][2];
+  for (int l = 0; l < 2; ++l)
+    for (int d = 0; d < 2; ++d) {
+      o_frag[l][d] = p.take(sizeof(uint32_t) * (size_t)GH * kH / 2);
+      o_wt[l][d] = p.take(sizeof(float) * (size_t)GH * kH);
+      o_bn[l][d] = p.take(sizeof(float) * kH);
+    }
+  const size_t o_wih1 = p.take(sizeof(float) * 2 * (size_t)GH * 2 * kH);
+  const size_t o_bih1 = p.take(sizeof(float) * 2 * GH);
+  const size_t o_lin_w = p.take(sizeof(float) * kH * 2 * kH);
+  const size_t o_lin_b = p.take(sizeof(float) * kH);
+  const size_t N = n_art;
+  const size_t o_ln0_w = p.take(sizeof(float) * N * kH), o_ln0_b = p.take(sizeof(float) * N * kH);
+  const size_t o_fc1_w = p.take(sizeof(float) * N * kFc * kH), o_fc1_b = p.take(sizeof(float) * N * kFc);
+  const size_t o_ln1_w = p.take(sizeof(float) * N * kFc), o_ln1_b = p.take(sizeof(float) * N * kFc);
+  const size_t o_fc2_w = p.take(sizeof(float) * N * kFc * kFc), o_fc2_b = p.take(sizeof(float) * N * kFc);
+  const size_t o_ln2_w = p.take(sizeof(float) * N * kFc), o_ln2_b = p.take(sizeof(float) * N * kFc);
+  const size_t o_head_w = p.take(sizeof(float) * N * kHeadPad * kFc), o_head_b = p.take(sizeof(float) * N * kHeadPad);
+
+  cudaError_t e = cudaMalloc(&m->arena, p.total);
+  if (e != cudaSuccess) {
+    delete m;
+    return check_cuda(e, "asb_model_create: cudaMalloc of the weight arena");
+  }
+  m->arena_bytes = p.total;
+  char* b = static_cast<char*>(m->arena);
+  auto F = [&](size_t off) { return reinterpret_cast<float*>(b + off); };
+  PackedWeights& w = m->w;
+  w.tab0 = F(o_tab0);
+  for (int l = 0; l < 2; ++l)
+    for (int d = 0; d < 2; ++d) {
+      w.whh_frag[l][d] = reinterpret_cast<uint32_t*>(b + o_frag[l][d]);
+      w.whh_t[l][d] = F(o_wt[l][d]);
+      w.bhh_n[l][d] = F(o_bn[l][d]);
+    }
+  w.wih1 = F(o_wih1); w.bih1 = F(o_bih1);
+  w.lin_w = F(o_lin_w); w.lin_b = F(o_lin_b);
+  w.ln0_w = F(o_ln0_w); w.ln0_b = F(o_ln0_b);
+  w.fc1_w = F(o_fc1_w); w.fc1_b = F(o_fc1_b);
+  w.ln1_w = F(o_ln1_w); w.ln1_b = F(o_ln1_b);
+  w.fc2_w = F(o_fc2_w); w.fc2_b = F(o_fc2_b);
+  w.ln2_w = F(o_ln2_w); w.ln2_b = F(o_ln2_b);
+  w.head_w = F(o_head_w); w.head_b = F(o_head_b);
+
+  int rc = pack_recurrent_weights(m, src, st);
+  if (!rc) rc = pack_dense_weights(m, src, st);
+  if (!rc) rc = check_cuda(cudaStreamSynchronize(st), "asb_model_create: packing kernels");
+  if (rc) {
+    cudaFree(m->arena);
+    delete m;
+    return rc;
+  }
+  *out = m;
+  return ASB_OK;
+}
+
+extern "C" void asb_model_destroy(asb_model* m) {
+  if (!m) return;
+  cudaFree(m->arena);
+  delete m;
+}
+
+extern "C" size_t asb_model_workspace_bytes(const asb_model* m, int B, int T) {
+  if (!m || B <= 0 || T <= 0) return 0;
+  return plan_workspace(m, nullptr, B, T).bytes;
+}
+
+extern "C" int asb_model_forward(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host, int B,
+                                 float* out, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!m || !x || !lengths_host || !out) return set_error(ASB_ERR_INVALID, "asb_model_forward: null argument");
+  if (B <= 0 || T_in <= 0) return set_error(ASB_ERR_INVALID, "asb_model_forward: empty batch");
+  // pack_padded_sequence(enforce_sorted=True) semantics, models.py:136
+  for (int b = 0; b < B; ++b) {
+    if (lengths_host[b] <= 0)
+      return set_error(ASB_ERR_UNSORTED,
+                       "Length of all samples has to be greater than 0, but found an element in 'lengths' that is <= 0");
+    if (b > 0 && lengths_host[b] > lengths_host[b - 1])
+      return set_error(ASB_ERR_UNSORTED,
+                       "`lengths` array must be sorted in decreasing order when `enforce_sorted` is True.");
+  }
+  const int T = lengths_host[0];
+  if (T > T_in) return set_error(ASB_ERR_INVALID, "asb_model_forward: lengths[0] = %d exceeds the sequence dimension %d", T, T_in);
+  const Workspace ws = plan_workspace(m, workspace, B, T);
+  if (!workspace || workspace_bytes < ws.bytes)
+    return set_error(ASB_ERR_WORKSPACE, "asb_model_forward: workspace %zu B < required %zu B", workspace_bytes, ws.bytes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long M = (long long)B * T;
+  if (M > 0x7fffffffLL / 64) return set_error(ASB_ERR_INVALID, "asb_model_forward: batch too large");
+
+  int rc = check_cuda(cudaMemcpyAsync(ws.lengths, lengths_host, sizeof(int) * (size_t)B, cudaMemcpyHostToDevice, st),
+                      "asb_model_forward: lengths H2D");
+  if (rc) return rc;
+  // padded steps of the recurrent outputs are zero (pad_packed_sequence, models.py:138)
+  rc = check_cuda(cudaMemsetAsync(ws.out0, 0, sizeof(float) * (size_t)M * 2 * kH, st), "asb_model_forward: memset");
+  if (rc) return rc;
+  rc = check_cuda(cudaMemsetAsync(ws.out1, 0, sizeof(float) * (size_t)M * 2 * kH, st), "asb_model_forward: memset");
+  if (rc) return rc;
+  const long long* tok = reinterpret_cast<const long long*>(x);
+  if ((rc = launch_gather_gi0(m, tok, T_in, ws.gi, B, T, st))) return rc;
+  if ((rc = launch_recurrent_layer(m, 0, ws.gi, ws.lengths, ws.out0, B, T, st))) return rc;
+  if ((rc = launch_linear(m, ws.out0, m->w.wih1, m->w.bih1, ws.gi, int(M), 2 * m->G * kH, 2 * kH, st))) return rc;
+  if ((rc = launch_recurrent_layer(m, 1, ws.gi, ws.lengths, ws.out1, B, T, st))) return rc;
+  if ((rc = launch_decoder(m, ws.out1, out, int(M), st))) return rc;
+  return ASB_OK;
 }

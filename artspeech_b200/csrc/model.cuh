@@ -1,0 +1,63 @@
+// Internal layout of asb_model and the launchers the forward pass is assembled from.
+#pragma once
+
+#include "asb_common.cuh"
+
+namespace asb {
+
+constexpr int kH = 128;        // hidden size the kernels are specialised for (models.py:104)
+constexpr int kFc = 256;       // predictor width (models.py:12-16)
+constexpr int kHeadPad = 128;  // x/y heads stacked (2 * n_samples = 100 rows) and padded to 128
+
+// Every pointer lives in one device arena owned by the model.
+struct PackedWeights {
+  // embedding fused with the layer-0 input projection: tab0[dir][v][G*H] = E[v] . W_ih_l0^T + b_ih
+  // (+ b_hh for the gates where it can be folded: GRU r,z; all LSTM gates)
+  float* tab0;
+  // recurrent weights [layer][dir]
+  uint32_t* whh_frag[2][2];  // bf16, mma.m16n8k16 A-fragment order (fast mode)
+  float* whh_t[2][2];        // fp32 [K = H][G*H] transposed (fp32 mode)
+  float* bhh_n[2][2];        // GRU: b_hh of the n gate (cannot be folded); LSTM: zeros
+  // Dense weights are stored row-major [N][K] like nn.Linear.weight; in fast mode they are
+  // pre-rounded to tf32 (cvt.rna), in fp32 mode they are the raw fp32 values (split on the fly).
+  // layer-1 input projection, both directions stacked: [2*G*H][2H], bias with foldable b_hh added
+  float* wih1; float* bih1;
+  // linear.0 [H][2H]
+  float* lin_w; float* lin_b;
+  // predictors, stacked over articulators
+  float* ln0_w; float* ln0_b;     // [N][H]
+  float* fc1_w; float* fc1_b;     // [N][256][H], [N][256]
+  float* ln1_w; float* ln1_b;     // [N][256]
+  float* fc2_w; float* fc2_b;     // [N][256][256], [N][256]
+  float* ln2_w; float* ln2_b;     // [N][256]
+  float* head_w; float* head_b;   // [N][128][256] (x rows 0..D-1, y rows D..2D-1, rest zero), [N][128]
+};
+
+}  // namespace asb
+
+struct asb_model {
+  int V, N, E, H, D, G, precision;
+  void* arena;
+  size_t arena_bytes;
+  asb::PackedWeights w;
+};
+
+namespace asb {
+
+// ---- recurrent layer (gru.cu) -------------------------------------------------------
+// gi: (B*T, 2, G*H) input pre-activations; out: (B, T, 2H), pre-zeroed; lengths: device (B).
+int launch_recurrent_layer(const asb_model* m, int layer, const float* gi, const int* lengths, float* out, int B,
+                           int T, cudaStream_t st);
+// gi[(b*T+t), dir, :] = tab0[dir][x[b, t]]   (embedding + layer-0 projection as a gather)
+int launch_gather_gi0(const asb_model* m, const long long* x, int T_in, float* gi, int B, int T, cudaStream_t st);
+int pack_recurrent_weights(asb_model* m, const asb_weights* w, cudaStream_t st);
+
+// ---- dense layers (decoder.cu) ------------------------------------------------------
+// C[M][N] = A[M][K] . W[N][K]^T + bias[N]   (tf32 single pass or 3xTF32)
+int launch_linear(const asb_model* m, const float* A, const float* W, const float* bias, float* C, int M, int N,
+                  int K, cudaStream_t st);
+// rnn_out (M, 2H) -> contours (M, N_art, 2, D): linear.0 + ReLU, then every predictor, sigmoid
+int launch_decoder(const asb_model* m, const float* rnn_out, float* out, int M, cudaStream_t st);
+int pack_dense_weights(asb_model* m, const asb_weights* w, cudaStream_t st);
+
+}  // namespace asb

@@ -86,13 +86,21 @@ p2cp50_kernel(const float* __restrict__ u, const float* __restrict__ v, float* _
       rhi[p] = kInf;
     }
 
+    // Software pipeline over column pairs: the operands of pair j+2 are fetched and the
+    // partner exchange + sqrt of pair j-2 are retired while pair j is being evaluated, so the
+    // LDS / SHFL / MUFU latencies overlap the FMA-pipe-bound body.
     float colsum = 0.f;
+    float2 vx = *reinterpret_cast<const float2*>(pv);
+    float2 vy = *reinterpret_cast<const float2*>(pv + kD);
+    float prev_send = 0.f, prev_mine = 0.f;  // sqrt(min(0, 0)) = 0 retires harmlessly at j = 0
 #pragma unroll 1
     for (int j = 0; j < kD; j += 2) {
-      const float2 vx = *reinterpret_cast<const float2*>(pv + j);
-      const float2 vy = *reinterpret_cast<const float2*>(pv + kD + j);
       const f32x2 vxa = pack2(vx.x, vx.x), vxb = pack2(vx.y, vx.y);
       const f32x2 vya = pack2(vy.x, vy.x), vyb = pack2(vy.y, vy.y);
+      const int jn = (j + 2 < kD) ? j + 2 : j;
+      vx = *reinterpret_cast<const float2*>(pv + jn);
+      vy = *reinterpret_cast<const float2*>(pv + kD + jn);
+      const float recv = __shfl_xor_sync(0xffffffffu, prev_send, 1);
       float ca = kInf, cb = kInf;
 #pragma unroll
       for (int p = 0; p < kRowPairs; ++p) {
@@ -108,12 +116,12 @@ p2cp50_kernel(const float* __restrict__ u, const float* __restrict__ v, float* _
         ca = min3(ca, a0, a1);
         cb = min3(cb, b0, b1);
       }
+      colsum += sqrt_approx(fminf(prev_mine, recv));
       // the partner thread holds the other 26 rows: exchange one column each way
-      const float send = half ? ca : cb;
-      const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
-      const float mine = half ? cb : ca;
-      colsum += sqrt_approx(fminf(mine, recv));
+      prev_send = half ? ca : cb;
+      prev_mine = half ? cb : ca;
     }
+    colsum += sqrt_approx(fminf(prev_mine, __shfl_xor_sync(0xffffffffu, prev_send, 1)));
 
     float rowsum = 0.f;
 #pragma unroll

@@ -1,0 +1,186 @@
+"""Drop-in ``ArtSpeech`` for phoneme_to_articulation/encoder_decoder/models.py of the reference.
+
+Same constructor, same ``forward(x, lengths)``, same parameter names and shapes (so reference
+``state_dict`` checkpoints load unchanged, test_phoneme_to_articulation.py:70-72) - but the forward
+pass runs entirely in the hand-written sm_100a kernels behind the C ABI (asb_model_*).
+
+The torch submodules below are only PARAMETER CONTAINERS: they give identical initialisation
+(same RNG consumption order as the reference constructor, models.py:109-120), identical
+``state_dict`` keys, ``.to(device)`` and ``.parameters()``; their own ``forward`` is never
+called and there is no CPU or eager fallback.  Inference only: calling the module with autograd
+enabled on parameters that require grad raises (training support is SURVEY.md row N2).
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+PRECISIONS = {"fast": _lib.PRECISION_FAST, "bf16": _lib.PRECISION_FAST, "fp32": _lib.PRECISION_FP32}
+
+
+class ArticulatorPredictor(nn.Module):
+    """models.py:7-33 (parameter container; evaluated inside the fused decoder kernel)."""
+
+    def __init__(self, in_features, n_samples):
+        super().__init__()
+        self.linear = nn.Sequential(
+            nn.LayerNorm([in_features]),
+            nn.Linear(in_features=in_features, out_features=256),
+            nn.ReLU(),
+            nn.LayerNorm([256]),
+            nn.Linear(in_features=256, out_features=256),
+            nn.ReLU(),
+            nn.LayerNorm(256),
+        )
+        self.x_coords = nn.Linear(in_features=256, out_features=n_samples)
+        self.y_coords = nn.Linear(in_features=256, out_features=n_samples)
+
+    def forward(self, inputs):
+        raise RuntimeError("ArticulatorPredictor is evaluated inside ArtSpeech's fused CUDA decoder; "
+                           "it has no standalone forward in artspeech_b200")
+
+
+class _NativeHandle:
+    """Owns one asb_model (re-packed weights on one device) and frees it with the module."""
+
+    def __init__(self, ptr, key):
+        self.ptr = ptr
+        self.key = key
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                _lib.lib().asb_model_destroy(self.ptr)
+        except Exception:
+            pass
+        self.ptr = None
+
+
+class ArtSpeech(nn.Module):
+    """models.py:99-145.  ``precision``: "fast" (bf16 recurrent GEMM, tf32 elsewhere, fp32
+    accumulate/state; contours within 2e-3 of the fp32 reference) or "fp32" (within 1e-5)."""
+
+    def __init__(self, vocab_size, n_articulators, embed_dim=64, hidden_size=128, n_samples=50, dropout=0.,
+                 precision="fast"):
+        super().__init__()
+        self.embedding = nn.Embedding(vocab_size, embed_dim)
+        self.rnn = nn.GRU(embed_dim, hidden_size, num_layers=2, bidirectional=True, dropout=dropout,
+                          batch_first=True)
+        self.linear = nn.Sequential(nn.Linear(2 * hidden_size, hidden_size), nn.ReLU())
+        self.predictors = nn.ModuleList([
+            ArticulatorPredictor(hidden_size, n_samples) for _ in range(n_articulators)
+        ])
+        if precision not in PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(PRECISIONS)}")
+        self.precision = precision
+        self._dims = (vocab_size, n_articulators, embed_dim, hidden_size, n_samples)
+        self._native = None
+        self._workspace = None
+
+    @property
+    def total_parameters(self):
+        return sum(p.numel() for p in self.parameters())
+
+    # ------------------------------------------------------------------ native handle
+    def _weights_key(self):
+        return (self.precision,) + tuple((p.data_ptr(), p._version) for p in self.parameters())
+
+    def _ensure_native(self, dev):
+        key = self._weights_key()
+        if self._native is not None and self._native.key == key:
+            return self._native.ptr
+        self._native = None
+        sd = {k: v.detach() for k, v in self.named_parameters()}
+        for k, v in sd.items():
+            if not v.is_cuda or v.device != dev:
+                raise RuntimeError(f"parameter {k} is on {v.device}; artspeech_b200.ArtSpeech runs on CUDA only "
+                                   "(call .to('cuda')) - there is no CPU fallback")
+            if v.dtype != torch.float32 or not v.is_contiguous():
+                raise RuntimeError(f"parameter {k} must be contiguous float32")
+        w = _lib.AsbWeights()
+        w.embedding = sd["embedding.weight"].data_ptr()
+        for layer in range(2):
+            for d, sfx in enumerate(("", "_reverse")):
+                w.rnn_w_ih[layer][d] = sd[f"rnn.weight_ih_l{layer}{sfx}"].data_ptr()
+                w.rnn_w_hh[layer][d] = sd[f"rnn.weight_hh_l{layer}{sfx}"].data_ptr()
+                w.rnn_b_ih[layer][d] = sd[f"rnn.bias_ih_l{layer}{sfx}"].data_ptr()
+                w.rnn_b_hh[layer][d] = sd[f"rnn.bias_hh_l{layer}{sfx}"].data_ptr()
+        w.linear_w = sd["linear.0.weight"].data_ptr()
+        w.linear_b = sd["linear.0.bias"].data_ptr()
+        n = self._dims[1]
+        keep = []
+
+        def arr(fmt):
+            a = (ctypes.c_void_p * n)(*[sd[fmt.format(i)].data_ptr() for i in range(n)])
+            keep.append(a)
+            return ctypes.cast(a, ctypes.POINTER(ctypes.c_void_p))
+
+        w.ln0_w, w.ln0_b = arr("predictors.{}.linear.0.weight"), arr("predictors.{}.linear.0.bias")
+        w.fc1_w, w.fc1_b = arr("predictors.{}.linear.1.weight"), arr("predictors.{}.linear.1.bias")
+        w.ln1_w, w.ln1_b = arr("predictors.{}.linear.3.weight"), arr("predictors.{}.linear.3.bias")
+        w.fc2_w, w.fc2_b = arr("predictors.{}.linear.4.weight"), arr("predictors.{}.linear.4.bias")
+        w.ln2_w, w.ln2_b = arr("predictors.{}.linear.6.weight"), arr("predictors.{}.linear.6.bias")
+        w.xh_w, w.xh_b = arr("predictors.{}.x_coords.weight"), arr("predictors.{}.x_coords.bias")
+        w.yh_w, w.yh_b = arr("predictors.{}.y_coords.weight"), arr("predictors.{}.y_coords.bias")
+        vocab, n_art, embed, hidden, n_samples = self._dims
+        handle = ctypes.c_void_p()
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().asb_model_create(
+                ctypes.byref(w), vocab, n_art, embed, hidden, n_samples, _lib.CELL_GRU,
+                PRECISIONS[self.precision], _lib.stream_ptr(dev), ctypes.byref(handle)))
+        self._native = _NativeHandle(handle, key)
+        return handle
+
+    def _apply(self, fn, *args, **kwargs):
+        self._native = None  # parameters move / change dtype: re-pack lazily
+        self._workspace = None
+        return super()._apply(fn, *args, **kwargs)
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, x, lengths):
+        """
+        Args:
+            x (torch.tensor): Torch tensor of shape (bs, seq_len), int64 tokens.
+            lengths (list): Lengths of the input sequences sorted in decreasing order.
+
+        Return:
+            output (torch.tensor): (bs, max(lengths), n_articulators, 2, n_samples) float32
+        """
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            raise NotImplementedError(
+                "artspeech_b200.ArtSpeech implements inference only; call it under torch.no_grad() "
+                "(evaluation.py:56-57 does). Training/backward kernels are not built yet.")
+        if self.training and self.rnn.dropout > 0:
+            raise NotImplementedError("inter-layer dropout (train mode) is not implemented; call .eval()")
+        dev = self.embedding.weight.device
+        if not dev.type == "cuda":
+            raise RuntimeError("artspeech_b200.ArtSpeech runs on CUDA only (call .to('cuda')); no CPU fallback")
+        if x.dim() != 2:
+            raise ValueError(f"x must be (bs, seq_len), got {tuple(x.shape)}")
+        B, T_in = x.shape
+        if torch.is_tensor(lengths):
+            L = [int(v) for v in lengths.detach().cpu().tolist()]
+        else:
+            L = [int(v) for v in lengths]
+        if len(L) != B:
+            raise RuntimeError(f"Expected `len(lengths)` to be equal to batch_size, but got {len(L)} "
+                               f"(batch_size={B})")
+        xd = x.detach().to(device=dev, dtype=torch.int64).contiguous()
+        handle = self._ensure_native(dev)
+        T = max(1, min(L[0], T_in)) if L else 0
+        lib = _lib.lib()
+        need = int(lib.asb_model_workspace_bytes(handle, B, T))
+        if self._workspace is None or self._workspace.numel() < need or self._workspace.device != dev:
+            self._workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+        vocab, n_art, _, _, n_samples = self._dims
+        out = torch.empty(B, T, n_art, 2, n_samples, dtype=torch.float32, device=dev)
+        c_len = (ctypes.c_int32 * B)(*L)
+        with torch.cuda.device(dev):
+            _lib.check(lib.asb_model_forward(handle, _lib.ptr(xd), T_in, c_len, B, _lib.ptr(out),
+                                             _lib.ptr(self._workspace), self._workspace.numel(),
+                                             _lib.stream_ptr(dev)))
+        return out

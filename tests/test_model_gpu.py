@@ -1,0 +1,113 @@
+"""GPU parity of the drop-in ArtSpeech against the reference's golden outputs and the oracle.
+Gates (BASELINE.json north_star): contours within 2e-3 max-abs in fast (bf16/tf32) mode and
+1e-5 in fp32 mode, against the reference fp32 forward."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from artspeech_b200 import synthetic
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fast": 2e-3, "fp32": 1e-5}
+
+
+@pytest.fixture(scope="module")
+def mods():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from artspeech_b200 import models
+    from oracle import model as omodel
+    return models, omodel
+
+
+def _build(models, sd, precision, n_art=10, vocab=45):
+    net = models.ArtSpeech(vocab, n_art, precision=precision)
+    net.load_state_dict(sd)
+    return net.cuda().eval()
+
+
+@pytest.mark.parametrize("precision", ["fast", "fp32"])
+@pytest.mark.parametrize("affine", [False, True])
+def test_golden_small(mods, golden_dir, precision, affine):
+    models, omodel = mods
+    g = np.load(os.path.join(golden_dir, "model_small.npz"))
+    sd = omodel.make_state_dict(45, 10, seed=0)
+    if affine:
+        sd = omodel.randomize_affine(sd, seed=1)
+    net = _build(models, sd, precision)
+    x = torch.from_numpy(g["x"]).cuda()
+    with torch.no_grad():
+        out = net(x, torch.from_numpy(g["lengths"]))
+    want = g["out32_affine" if affine else "out32"]
+    assert out.shape == want.shape and out.dtype == torch.float32 and out.is_contiguous()
+    err = np.abs(out.cpu().numpy() - want).max()
+    print(f"golden_small[{precision}, affine={affine}] max-abs {err:.3e}")
+    assert err <= TOL[precision]
+
+
+@pytest.mark.parametrize("precision", ["fast", "fp32"])
+def test_variable_lengths_vs_oracle(mods, precision):
+    models, omodel = mods
+    sd = omodel.randomize_affine(omodel.make_state_dict(45, 10, seed=0), seed=3)
+    net = _build(models, sd, precision)
+    B, T = 37, 61
+    x = synthetic.tokens(B, T, 45, seed=5)
+    L = synthetic.sorted_lengths(B, 7, 53, seed=5)       # max(lengths) = 53 < T: output is cut to 53
+    with torch.no_grad():
+        out = net(x.cuda(), L)
+    want = omodel.artspeech_forward(sd, x, L, torch.float32)
+    assert out.shape == want.shape == (B, 53, 10, 2, 50)
+    err = (out.cpu() - want).abs().max().item()
+    print(f"variable_lengths[{precision}] max-abs {err:.3e}")
+    assert err <= TOL[precision]
+    # padded frames carry the constant decode(ReLU(b_linear)) frame (H3)
+    b = B - 1
+    pad = out[b, int(L[b]):]
+    assert (pad - pad[0]).abs().max().item() == 0.0
+
+
+def test_config2_shape_fast(mods):
+    """BASELINE config 2: batch 256, length 100, checked against the CPU reference path."""
+    models, omodel = mods
+    sd = omodel.make_state_dict(45, 10, seed=0)
+    net = _build(models, sd, "fast")
+    x = synthetic.tokens(256, 100, 45, seed=0)
+    L = [100] * 256
+    with torch.no_grad():
+        out = net(x.cuda(), L)
+    want = omodel.artspeech_forward(sd, x[:32], L[:32], torch.float32)
+    err = (out[:32].cpu() - want).abs().max().item()
+    print(f"config2 fast max-abs {err:.3e}")
+    assert err <= TOL["fast"]
+    # batch rows are independent: a sub-batch gives the same contours
+    with torch.no_grad():
+        sub = net(x[:8].cuda(), L[:8])
+    assert (sub - out[:8]).abs().max().item() <= 1e-6
+
+
+def test_errors_and_state_dict(mods):
+    models, omodel = mods
+    sd = omodel.make_state_dict(45, 2, seed=0)
+    net = models.ArtSpeech(45, 2)
+    assert sorted(net.state_dict().keys()) == sorted(sd.keys())
+    for k, v in net.state_dict().items():
+        assert v.shape == sd[k].shape
+    net.load_state_dict(sd)
+    assert net.total_parameters == sum(v.numel() for v in sd.values())
+    net = net.cuda().eval()
+    x = synthetic.tokens(3, 9, 45).cuda()
+    with torch.no_grad():
+        with pytest.raises(RuntimeError):
+            net(x, [5, 9, 3])              # unsorted, like pack_padded_sequence
+        with pytest.raises(RuntimeError):
+            net(x, [9, 5, 0])              # zero length
+        a = net(x, [9, 5, 3])
+        # weights changed in place -> the native copy is rebuilt
+        net.linear[0].bias.add_(1.0)
+        b = net(x, [9, 5, 3])
+    assert (a - b).abs().max().item() > 1e-4
+    with pytest.raises(NotImplementedError):
+        net(x, [9, 5, 3])                  # autograd enabled: training is not implemented
