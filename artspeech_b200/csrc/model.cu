@@ -132,6 +132,10 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
 
 extern "C" void asb_model_destroy(asb_model* m) {
   if (!m) return;
+  for (auto& set : m->pending)
+    for (auto e : set) cudaEventDestroy(e);
+  for (auto& set : m->free_sets)
+    for (auto e : set) cudaEventDestroy(e);
   cudaFree(m->arena);
   delete m;
 }
@@ -172,10 +176,63 @@ extern "C" int asb_model_forward(asb_model* m, const int64_t* x, int T_in, const
   rc = check_cuda(cudaMemsetAsync(ws.out1, 0, sizeof(float) * (size_t)M * 2 * kH, st), "asb_model_forward: memset");
   if (rc) return rc;
   const long long* tok = reinterpret_cast<const long long*>(x);
+  std::array<cudaEvent_t, ASB_N_STAGES + 1> ev{};
+  const bool prof = m->profile;
+  if (prof) {
+    if (!m->free_sets.empty()) {
+      ev = m->free_sets.back();
+      m->free_sets.pop_back();
+    } else {
+      for (auto& e : ev)
+        if ((rc = check_cuda(cudaEventCreate(&e), "asb_model_forward: cudaEventCreate"))) return rc;
+    }
+  }
+  auto mark = [&](int k) {
+    if (prof) cudaEventRecord(ev[k], st);
+  };
+  mark(0);
   if ((rc = launch_gather_gi0(m, tok, T_in, ws.gi, B, T, st))) return rc;
+  mark(1);
   if ((rc = launch_recurrent_layer(m, 0, ws.gi, ws.lengths, ws.out0, B, T, st))) return rc;
+  mark(2);
   if ((rc = launch_linear(m, ws.out0, m->w.wih1, m->w.bih1, ws.gi, int(M), 2 * m->G * kH, 2 * kH, st))) return rc;
+  mark(3);
   if ((rc = launch_recurrent_layer(m, 1, ws.gi, ws.lengths, ws.out1, B, T, st))) return rc;
+  mark(4);
   if ((rc = launch_decoder(m, ws.out1, out, int(M), st))) return rc;
+  mark(5);
+  if (prof) m->pending.push_back(ev);
+  return ASB_OK;
+}
+
+extern "C" int asb_model_profile_enable(asb_model* m, int enable) {
+  if (!m) return set_error(ASB_ERR_INVALID, "asb_model_profile_enable: null model");
+  m->profile = enable != 0;
+  return ASB_OK;
+}
+
+extern "C" int asb_model_profile_read(asb_model* m, float* stage_ms_out, int32_t* stage_calls_out, int reset) {
+  if (!m) return set_error(ASB_ERR_INVALID, "asb_model_profile_read: null model");
+  for (auto& ev : m->pending) {
+    int rc = check_cuda(cudaEventSynchronize(ev[ASB_N_STAGES]), "asb_model_profile_read: event sync");
+    if (rc) return rc;
+    for (int k = 0; k < ASB_N_STAGES; ++k) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, ev[k], ev[k + 1]) == cudaSuccess) {
+        m->stage_ms[k] += ms;
+        m->stage_calls[k] += 1;
+      }
+    }
+    m->free_sets.push_back(ev);
+  }
+  m->pending.clear();
+  for (int k = 0; k < ASB_N_STAGES; ++k) {
+    if (stage_ms_out) stage_ms_out[k] = float(m->stage_ms[k]);
+    if (stage_calls_out) stage_calls_out[k] = m->stage_calls[k];
+    if (reset) {
+      m->stage_ms[k] = 0;
+      m->stage_calls[k] = 0;
+    }
+  }
   return ASB_OK;
 }

@@ -35,11 +35,20 @@ struct PackedWeights {
 
 }  // namespace asb
 
+#include <array>
+#include <vector>
+
 struct asb_model {
   int V, N, E, H, D, G, precision;
   void* arena;
   size_t arena_bytes;
   asb::PackedWeights w;
+  // optional per-stage timing (asb_model_profile_*): one event set per profiled forward
+  bool profile = false;
+  std::vector<std::array<cudaEvent_t, ASB_N_STAGES + 1>> pending;
+  std::vector<std::array<cudaEvent_t, ASB_N_STAGES + 1>> free_sets;
+  double stage_ms[ASB_N_STAGES] = {0, 0, 0, 0, 0};
+  int stage_calls[ASB_N_STAGES] = {0, 0, 0, 0, 0};
 };
 
 namespace asb {

@@ -117,6 +117,7 @@ __device__ __forceinline__ Best search(const float* ax, const float* ay, ColFn c
 
 __global__ void __launch_bounds__(kWarps * 32)
 tract_variables_kernel(const float* __restrict__ sets_ptr, long long sets, int n_art, ArtIndex ai,
+                       const float* __restrict__ uinc_ext, long long uinc_stride,
                        float* __restrict__ val, int* __restrict__ idx, float* __restrict__ poc) {
   __shared__ __align__(16) float sm[kWarps][S_COUNT * kItemF];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -127,7 +128,10 @@ tract_variables_kernel(const float* __restrict__ sets_ptr, long long sets, int n
   // 6 contours x 25 float4
   for (int q = lane; q < S_COUNT * (kItemF / 4); q += 32) {
     const int slot = q / (kItemF / 4), part = q - slot * (kItemF / 4);
-    const float4 t = __ldg(reinterpret_cast<const float4*>(base + (long long)ai.v[slot] * kItemF) + part);
+    // the upper incisor may live outside the set (evaluation.py:93-109 injects a reference contour)
+    const float* src = (slot == S_UINC && uinc_ext) ? uinc_ext + set * uinc_stride
+                                                    : base + (long long)ai.v[slot] * kItemF;
+    const float4 t = __ldg(reinterpret_cast<const float4*>(src) + part);
     *reinterpret_cast<float4*>(s + slot * kItemF + 4 * part) = t;
   }
   __syncwarp();
@@ -179,25 +183,40 @@ tract_variables_kernel(const float* __restrict__ sets_ptr, long long sets, int n
 
 }  // namespace
 
-extern "C" int asb_tract_variables(const float* sets_ptr, int64_t sets, int n_art, const int32_t* art_index_host,
-                                   float* val, int32_t* idx, float* poc, void* stream) {
+static int tv_launch(const float* sets_ptr, int64_t sets, int n_art, const int32_t* art_index_host,
+                     const float* uinc, int64_t uinc_stride, float* val, int32_t* idx, float* poc, void* stream) {
   if (sets < 0 || n_art <= 0 || !art_index_host)
     return asb::set_error(ASB_ERR_INVALID, "asb_tract_variables: bad arguments");
   ArtIndex ai;
   for (int k = 0; k < 6; ++k) {
     ai.v[k] = art_index_host[k];
-    if (ai.v[k] < 0 || ai.v[k] >= n_art)
+    const bool external = (k == S_UINC && uinc != nullptr);
+    if (!external && (ai.v[k] < 0 || ai.v[k] >= n_art))
       return asb::set_error(ASB_ERR_INVALID, "asb_tract_variables: articulator row %d out of range [0,%d)", ai.v[k],
                             n_art);
   }
   if (sets == 0) return ASB_OK;
   if (!sets_ptr || !val || !idx || !poc) return asb::set_error(ASB_ERR_INVALID, "asb_tract_variables: null pointer");
-  if ((reinterpret_cast<uintptr_t>(sets_ptr) & 15) || (reinterpret_cast<uintptr_t>(poc) & 15))
-    return asb::set_error(ASB_ERR_INVALID, "asb_tract_variables: sets/poc must be 16-byte aligned");
+  if ((reinterpret_cast<uintptr_t>(sets_ptr) & 15) || (reinterpret_cast<uintptr_t>(poc) & 15) ||
+      (reinterpret_cast<uintptr_t>(uinc) & 15) || (uinc_stride & 3))
+    return asb::set_error(ASB_ERR_INVALID, "asb_tract_variables: sets/poc/upper_incisor must be 16-byte aligned");
   const long long blocks = (sets + kWarps - 1) / kWarps;
   if (blocks > 0x7fffffffLL) return asb::set_error(ASB_ERR_INVALID, "asb_tract_variables: too many sets");
   tract_variables_kernel<<<unsigned(blocks), kWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-      sets_ptr, sets, n_art, ai, val, idx, poc);
+      sets_ptr, sets, n_art, ai, uinc, uinc_stride, val, idx, poc);
   ASB_CHECK_LAUNCH("tract_variables_kernel");
   return ASB_OK;
+}
+
+extern "C" int asb_tract_variables(const float* sets_ptr, int64_t sets, int n_art, const int32_t* art_index_host,
+                                   float* val, int32_t* idx, float* poc, void* stream) {
+  return tv_launch(sets_ptr, sets, n_art, art_index_host, nullptr, 0, val, idx, poc, stream);
+}
+
+extern "C" int asb_tract_variables_ref(const float* sets_ptr, int64_t sets, int n_art,
+                                       const int32_t* art_index_host, const float* upper_incisor,
+                                       int64_t upper_incisor_stride, float* val, int32_t* idx, float* poc,
+                                       void* stream) {
+  if (!upper_incisor) return asb::set_error(ASB_ERR_INVALID, "asb_tract_variables_ref: null upper_incisor");
+  return tv_launch(sets_ptr, sets, n_art, art_index_host, upper_incisor, upper_incisor_stride, val, idx, poc, stream);
 }

@@ -1,0 +1,96 @@
+"""Device-resident evaluation step: forward -> P2CP -> tract variables -> per-utterance means.
+
+This is the batched form of the inner loops of the reference's ``run_test``
+(phoneme_to_articulation/encoder_decoder/evaluation.py:53-128) and of ``tract_variables``
+(phoneme_to_articulation/__init__.py:201-297): the reference moves the outputs to the CPU and
+loops per sentence / per frame in Python; here everything up to the small accumulator vector
+stays on the GPU.  Utterances are independent, so a multi-GPU run shards them by rank and sums
+the accumulators with one all-reduce (``reduce_accumulators``).
+"""
+from __future__ import annotations
+
+import torch
+
+from . import synthetic
+from .metrics import p2cp_distance
+from .tract_variables import tract_variables_batch
+
+# layout of the fp64 accumulator vector (all sums over utterances / valid frames of this rank)
+#   [0:N)        sum over utterances of the per-utterance mean P2CP, per articulator (evaluation.py:72,82)
+#   [N]          number of utterances
+#   [N+1 : N+5)  sum over valid frames of the predicted TVs (LA, TTCD, TBCD, VEL)
+#   [N+5 : N+9)  same for the target TVs
+#   [N+9 : N+13) sum over valid frames of |TV_pred - TV_target|
+#   [N+13]       number of valid frames
+
+
+def accumulator_size(n_articulators):
+    return n_articulators + 14
+
+
+def length_mask(lengths, T, device):
+    L = torch.as_tensor(lengths, device=device, dtype=torch.int64).view(-1, 1)
+    return torch.arange(T, device=device).view(1, -1) < L  # (B, T), helpers.py:79-91 make_padding_mask
+
+
+@torch.no_grad()
+def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_incisor=None, mark=None):
+    """One evaluation step on the model's device.
+
+    tokens (B, T) int64, lengths sorted descending, targets (B, T, N, 2, 50) fp32 - all on the GPU.
+    Returns dict(outputs, p2cp (B,T,N), tv_pred (B,T,4), tv_target (B,T,4), acc (N+14,) fp64).
+    ``mark(name)``, if given, is called at the stage boundaries (bench.py records CUDA events there).
+    """
+    mark = mark or (lambda name: None)
+    articulators = articulators or synthetic.ARTICULATORS
+    if upper_incisor is None:
+        upper_incisor = synthetic.UPPER_INCISOR_REF
+    mark("start")
+    outputs = model(tokens, lengths)                                  # evaluation.py:57
+    mark("forward")
+    T = outputs.shape[1]
+    tgt = targets[:, :T]
+    if not tgt.is_contiguous():
+        tgt = tgt.contiguous()
+    mask = length_mask(lengths, T, outputs.device)
+    p2cp = p2cp_distance(outputs, tgt)                                # evaluation.py:72 (all sentences at once)
+    mark("p2cp")
+    tv_pred, _, _ = tract_variables_batch(outputs, articulators, upper_incisor)   # __init__.py:256
+    tv_tgt, _, _ = tract_variables_batch(tgt, articulators, upper_incisor)        # __init__.py:261
+    mark("tv")
+    n = outputs.shape[2]
+    m = mask.unsqueeze(-1).to(torch.float64)
+    Lf = m.sum(dim=1)                                                 # (B, 1)
+    per_utt = (p2cp.to(torch.float64) * m).sum(dim=1) / Lf            # (B, N) mean over the valid frames
+    acc = torch.zeros(accumulator_size(n), dtype=torch.float64, device=outputs.device)
+    acc[:n] = per_utt.sum(dim=0)
+    acc[n] = float(outputs.shape[0])
+    acc[n + 1:n + 5] = (tv_pred.to(torch.float64) * m).sum(dim=(0, 1))
+    acc[n + 5:n + 9] = (tv_tgt.to(torch.float64) * m).sum(dim=(0, 1))
+    acc[n + 9:n + 13] = ((tv_pred - tv_tgt).abs().to(torch.float64) * m).sum(dim=(0, 1))
+    acc[n + 13] = m.sum()
+    mark("reduce")
+    return {"outputs": outputs, "p2cp": p2cp, "tv_pred": tv_pred, "tv_target": tv_tgt, "acc": acc}
+
+
+def reduce_accumulators(acc):
+    """Sum the accumulator vector over ranks (NCCL all-reduce when torch.distributed is up)."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(acc, op=dist.ReduceOp.SUM)
+    return acc
+
+
+def summarize(acc, n_articulators, articulators=None):
+    """Accumulators -> the numbers run_test reports (evaluation.py:142-159), in normalised units."""
+    articulators = articulators or synthetic.ARTICULATORS
+    a = acc.detach().cpu().tolist()
+    n = n_articulators
+    utt, frames = a[n], a[n + 13]
+    out = {art: {"p2cp": a[i] / utt} for i, art in enumerate(articulators[:n])}
+    for k, name in enumerate(("LA", "TTCD", "TBCD", "VEL")):
+        out[name] = {"pred_mean": a[n + 1 + k] / frames, "target_mean": a[n + 5 + k] / frames,
+                     "abs_err_mean": a[n + 9 + k] / frames}
+    out["utterances"] = utt
+    out["frames"] = frames
+    return out

@@ -140,6 +140,23 @@ class ArtSpeech(nn.Module):
         self._workspace = None
         return super()._apply(fn, *args, **kwargs)
 
+    # ------------------------------------------------------------------ per-stage timing
+    STAGES = ("gather", "gru_l0", "proj_l1", "gru_l1", "decoder")
+
+    def profile(self, enable=True):
+        """Record CUDA events around each kernel stage of subsequent forwards (asb_model_profile_*)."""
+        dev = self.embedding.weight.device
+        _lib.check(_lib.lib().asb_model_profile_enable(self._ensure_native(dev), 1 if enable else 0))
+
+    def read_profile(self, reset=True):
+        """{stage: (total_ms, calls)} accumulated since the last reset."""
+        if self._native is None:
+            return {}
+        ms = (ctypes.c_float * 5)()
+        calls = (ctypes.c_int32 * 5)()
+        _lib.check(_lib.lib().asb_model_profile_read(self._native.ptr, ms, calls, 1 if reset else 0))
+        return {name: (float(ms[k]), int(calls[k])) for k, name in enumerate(self.STAGES)}
+
     # ------------------------------------------------------------------ forward
     def forward(self, x, lengths):
         """

@@ -41,17 +41,22 @@ _ABI_ORDER = (LOWER_LIP, PHARYNX, SOFT_PALATE_MIDLINE, TONGUE, UPPER_INCISOR, UP
 _ARR1 = ((LOWER_LIP, 0), (TONGUE, 30), (TONGUE, 10), (SOFT_PALATE_MIDLINE, 0))
 
 
-def tract_variables_batch(frames, articulators):
+def tract_variables_batch(frames, articulators, upper_incisor=None):
     """All four TVs for every contour set in one launch.
 
     frames: (..., N_art, 2, 50) float tensor (CPU or CUDA); ``articulators``: the N_art names in
-    row order, or a dict name -> row.  Returns (val (...,4) fp32, idx (...,4,2) int32,
+    row order, or a dict name -> row.  ``upper_incisor``: optional (2, 50) contour shared by all
+    sets, or (..., 2, 50) one per set, used instead of a row of ``frames`` (the reference injects
+    a fixed reference contour, evaluation.py:93-109).  Returns (val (...,4) fp32, idx (...,4,2) int32,
     poc (...,4,2,2) fp32) on the CUDA device; idx = (i into arr1, j into arr2) of each search,
     poc = (arr1[i], arr2[j])."""
     if isinstance(articulators, dict):
         index = articulators
     else:
         index = {name: k for k, name in enumerate(articulators)}
+    if upper_incisor is not None:
+        index = dict(index)
+        index.setdefault(UPPER_INCISOR, -1)
     rows = (ctypes.c_int32 * 6)(*[index[name] for name in _ABI_ORDER])  # KeyError like the reference
     if frames.dim() < 3 or frames.shape[-2] != 2 or frames.shape[-1] != 50:
         raise ValueError(f"expected (..., N_art, 2, 50) contours, got {tuple(frames.shape)}")
@@ -64,8 +69,17 @@ def tract_variables_batch(frames, articulators):
     idx = torch.empty(sets, 4, 2, dtype=torch.int32, device=dev)
     poc = torch.empty(sets, 4, 2, 2, dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
-        _lib.check(_lib.lib().asb_tract_variables(_lib.ptr(f), sets, n_art, rows, _lib.ptr(val), _lib.ptr(idx),
-                                                  _lib.ptr(poc), _lib.stream_ptr(dev)))
+        if upper_incisor is None:
+            _lib.check(_lib.lib().asb_tract_variables(_lib.ptr(f), sets, n_art, rows, _lib.ptr(val),
+                                                      _lib.ptr(idx), _lib.ptr(poc), _lib.stream_ptr(dev)))
+        else:
+            ui = upper_incisor.detach().to(device=dev, dtype=torch.float32).contiguous()
+            if ui.shape[-2:] != (2, 50) or ui.numel() not in (100, sets * 100):
+                raise ValueError(f"upper_incisor must be (2, 50) or (..., 2, 50) per set, got {tuple(ui.shape)}")
+            stride = 0 if ui.numel() == 100 else 100
+            _lib.check(_lib.lib().asb_tract_variables_ref(_lib.ptr(f), sets, n_art, rows, _lib.ptr(ui), stride,
+                                                          _lib.ptr(val), _lib.ptr(idx), _lib.ptr(poc),
+                                                          _lib.stream_ptr(dev)))
     return val.view(*lead, 4), idx.view(*lead, 4, 2), poc.view(*lead, 4, 2, 2)
 
 

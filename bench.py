@@ -1,0 +1,345 @@
+"""Headline benchmark: articulatory frames/sec of the evaluation hot path (forward + P2CP + TVs).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --steps K --warmup W    # the reference's CPU path (oracle port)
+
+Workload = BASELINE.json configs[1]: the encoder_decoder model at batch 256, sequence length 100,
+followed by P2CP and the tract variables of prediction and target for every frame.  One "step" is
+one such batch (25 600 frames).  Under torchrun every rank runs its own batch (utterance sharding,
+weak scaling) and the fp64 metric accumulators are summed with one NCCL all-reduce per step.
+
+Prints ONE JSON line (rank 0).  `value` = frames/s with inputs resident in HBM, timed with CUDA
+events per step (L2 flushed between steps, outside the timed windows), max over ranks.  `e2e` =
+the same step through the public API starting from pinned HOST buffers (H2D of tokens + targets and
+D2H of the accumulators inside the timed region).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "articulatory frames/sec (fwd + P2CP/TV)"
+UNIT = "frames/s"
+VOCAB, N_ART, D = 45, 10, 50
+# per-frame work of the model
+MAC_DECODER = 32768 + 10 * 123904       # linear.0 + ten predictors
+MAC_PROJ_L1 = 2 * 384 * 256
+MAC_RECURRENT = 196608                  # the sequential h-path, both layers and directions
+BYTES_P2CP = 8040                       # 2*10*400 read + 40 written
+BYTES_TV = 5024                         # pred + target: 2 * (6*400 + 4*28)
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"hbm_gbs": p["hbm_gbs"], "tflops_burst": p["bf16_tflops"],
+                "tflops_sustained": p.get("bf16_tflops_sustained", p["bf16_tflops"]), "source": "measured"}
+    # fallback stated in /opt/skills/guides/B200_PROFILING.md
+    return {"hbm_gbs": 6650.0, "tflops_burst": 1590.0, "tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in self.lines:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, flag in zip(names, parts[3:7]):
+                if flag.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def visible_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        ids = [v for v in vis.split(",") if v != ""]
+        if local_rank < len(ids) and ids[local_rank].isdigit():
+            return int(ids[local_rank])
+    return local_rank
+
+
+def run_reference(args):
+    """The reference's own CPU implementation of the path (oracle port: /root/reference does not
+    exist on the GPU box), all host threads, on a bounded sample of the configs[1] workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import cpu_baseline as cb
+    from oracle import model as omodel
+    from artspeech_b200 import synthetic
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = omodel.make_state_dict(VOCAB, N_ART, seed=0)
+    sb, sl = args.ref_batch, args.seq_len
+    tokens = synthetic.tokens(sb, sl, VOCAB, seed=0)
+    lengths = [sl] * sb
+    targets = synthetic.contours(sb * sl, N_ART, D, seed=1).view(sb, sl, N_ART, 2, D)
+    for _ in range(max(args.warmup, 1) if args.warmup > 0 else 0):
+        cb.evaluate_batch_cpu(sd, tokens[:2], lengths[:2], targets[:2])
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cb.evaluate_batch_cpu(sd, tokens, lengths, targets)
+    dt = time.perf_counter() - t0
+    value = args.steps * sb * sl / dt
+    sample = f"{sb} utterances x {sl} frames per step (bounded sample of the 256 x {sl} batch), fp32, torch CPU ops"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"encoder_decoder BiGRU fwd + P2CP + TVs, batch 256 x len {sl} (configs[1])",
+                   "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    from artspeech_b200 import _lib, evaluation, models, synthetic
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: artspeech_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.lib()  # fail loudly here if the CUDA library is missing
+    peaks = load_peaks()
+
+    B, T = args.batch, args.seq_len
+    frames = B * T
+    torch.manual_seed(0)                       # same initial weights as the reference constructor
+    model = models.ArtSpeech(VOCAB, N_ART, precision=args.precision).to(dev).eval()
+    # synthetic utterances of this rank (sharded by utterance: rank r owns its own batch)
+    tokens_h = synthetic.tokens(B, T, VOCAB, seed=100 + rank).pin_memory()
+    targets_h = synthetic.contours(frames, N_ART, D, seed=200 + rank).view(B, T, N_ART, 2, D).pin_memory()
+    lengths = [T] * B
+    tokens_d = tokens_h.to(dev)
+    targets_d = targets_h.to(dev)
+    uinc_d = synthetic.UPPER_INCISOR_REF.to(dev)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    stage_events = []
+
+    def make_mark(store):
+        def mark(name):
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            store.append((name, ev))
+        return mark
+
+    def step(tok, tgt, mark=None):
+        res = evaluation.evaluate_batch(model, tok, lengths, tgt, upper_incisor=uinc_d, mark=mark)
+        evaluation.reduce_accumulators(res["acc"])
+        return res
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    for _ in range(max(args.warmup, 3)):
+        step(tokens_d, targets_d)
+    torch.cuda.synchronize()
+
+    # ---------------- device-resident timing (value)
+    model.profile(True)
+    model.read_profile(reset=True)
+    sampler = ClockSampler(visible_index(local_rank))
+    launches0 = _lib.launch_count()
+    barrier(); torch.cuda.synchronize()
+    sampler.start()
+    starts, ends = [], []
+    for _ in range(args.steps):
+        flush.zero_()                                   # evict L2 (not timed)
+        s = torch.cuda.Event(enable_timing=True); e = torch.cuda.Event(enable_timing=True)
+        marks = []
+        s.record()
+        step(tokens_d, targets_d, make_mark(marks))
+        e.record()
+        starts.append(s); ends.append(e); stage_events.append(marks)
+    torch.cuda.synchronize(); barrier()
+    clocks = sampler.stop()
+    launches = _lib.launch_count() - launches0
+    model.profile(False)
+    step_ms = [s.elapsed_time(e) for s, e in zip(starts, ends)]
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(total_ms.item())
+    value = world * frames * args.steps / (total_ms * 1e-3)
+
+    # per-stage device times (means over the timed steps)
+    prof = model.read_profile(reset=True)
+    stage_ms = {k: (v[0] / v[1] if v[1] else 0.0) for k, v in prof.items()}
+    agg = {}
+    for marks in stage_events:
+        for (n0, e0), (n1, e1) in zip(marks[:-1], marks[1:]):
+            agg[n1] = agg.get(n1, 0.0) + e0.elapsed_time(e1)
+    for k in agg:
+        agg[k] /= args.steps
+    stage_ms.update({"p2cp": agg.get("p2cp", 0.0), "tv_pred_and_target": agg.get("tv", 0.0),
+                     "forward_total": agg.get("forward", 0.0), "accumulate": agg.get("reduce", 0.0)})
+
+    # ---------------- roofline of the dominant kernel
+    kernels = {
+        "decoder": ("tensor", 2.0 * MAC_DECODER * frames, stage_ms.get("decoder", 0.0)),
+        "gru_l0": ("tensor", 2.0 * MAC_RECURRENT / 2 * frames, stage_ms.get("gru_l0", 0.0)),
+        "gru_l1": ("tensor", 2.0 * MAC_RECURRENT / 2 * frames, stage_ms.get("gru_l1", 0.0)),
+        "proj_l1": ("tensor", 2.0 * MAC_PROJ_L1 * frames, stage_ms.get("proj_l1", 0.0)),
+        "p2cp": ("hbm", float(BYTES_P2CP) * frames, stage_ms.get("p2cp", 0.0)),
+        "tract_variables": ("hbm", float(BYTES_TV) * frames, stage_ms.get("tv_pred_and_target", 0.0)),
+    }
+    top = max(kernels, key=lambda k: kernels[k][2])
+    bound, work, ms = kernels[top]
+    if bound == "tensor":
+        achieved = work / (ms * 1e-3) / 1e12 if ms > 0 else 0.0
+        peak, unit = peaks["tflops_sustained"], "TFLOP/s"
+    else:
+        achieved = work / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        peak, unit = peaks["hbm_gbs"], "GB/s"
+    roofline = {"kernel": top, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit,
+                "frac": achieved / peak if peak else None, "traffic": None,
+                "peak_source": f"{peaks['source']} (dense bf16 cuBLAS sustained; this kernel computes in tf32)"
+                if bound == "tensor" else peaks["source"],
+                "ms_per_launch": ms,
+                "all_kernels_ms": {k: round(v[2], 4) for k, v in kernels.items()},
+                "all_kernels_frac": {k: round((v[1] / (v[2] * 1e-3) / (1e12 if v[0] == "tensor" else 1e9)) /
+                                              (peaks["tflops_sustained"] if v[0] == "tensor" else peaks["hbm_gbs"]), 4)
+                                     if v[2] > 0 else None for k, v in kernels.items()}}
+
+    # ---------------- end to end from pinned host buffers (e2e)
+    for _ in range(2):
+        r = step(tokens_h.to(dev, non_blocking=True), targets_h.to(dev, non_blocking=True))
+        r["acc"].cpu()
+    barrier(); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        tok = tokens_h.to(dev, non_blocking=True)
+        tgt = targets_h.to(dev, non_blocking=True)
+        r = step(tok, tgt)
+        acc_h = r["acc"].cpu()                          # D2H of the step's result (synchronises)
+    torch.cuda.synchronize()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    barrier()
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = world * frames * args.steps / float(e2e_s.item())
+    h2d = tokens_h.numel() * tokens_h.element_size() + targets_h.numel() * targets_h.element_size()
+    d2h = acc_h.numel() * acc_h.element_size()
+
+    # ---------------- CPU baseline (rank 0, single-GPU run only): oracle port on the host cores
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import cpu_baseline as cb
+        cores = os.cpu_count() or 1
+        sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+        v, secs = cb.time_cpu_baseline(sd, args.cpu_batch, T, repeats=1, threads=cores)
+        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                        "sample": f"{args.cpu_batch} utterances x {T} frames of the same workload "
+                                  f"({secs:.1f} s of host time), fp32 torch CPU ops, per-frame TV loop"}
+
+    if rank == 0:
+        summary = evaluation.summarize(r["acc"], N_ART)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None,
+            "dtype": "tf32/bf16 mma, fp32 accumulate" if args.precision == "fast" else "f32 (3xTF32)",
+            "data": "synthetic",
+            "config": {"workload": f"encoder_decoder BiGRU fwd + P2CP + TVs (pred+target), batch {B} x len {T} "
+                                   f"per GPU (configs[1]), 10 articulators x 50 points",
+                       "precision": args.precision, "frames_per_step_per_gpu": frames,
+                       "parallelism": f"utterance-sharded x{world}, one NCCL all-reduce of {N_ART + 14} fp64 per step",
+                       "l2": "256 MiB flush between timed steps; per-step working set > L2"},
+            "stage_ms": {k: round(v, 4) for k, v in stage_ms.items()},
+            "roofline": roofline, "cpu_baseline": cpu_baseline,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "check": {"mean_p2cp_first_articulator": summary[synthetic.ARTICULATORS[0]]["p2cp"],
+                      "frames_accumulated": summary["frames"]},
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--seq-len", type=int, default=100)
+    ap.add_argument("--precision", default="fast", choices=["fast", "fp32"])
+    ap.add_argument("--cpu-batch", type=int, default=32, help="utterances in the bounded CPU-baseline sample")
+    ap.add_argument("--ref-batch", type=int, default=8, help="utterances per step of --impl reference")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

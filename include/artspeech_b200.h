@@ -79,6 +79,16 @@ ASB_API int asb_tract_variables(const float* sets_ptr, int64_t sets, int n_art,
                         const int32_t* art_index_host, float* val, int32_t* idx, float* poc,
                         void* stream);
 
+/* Same, with the upper-incisor contour taken from outside the sets: evaluation.py:93-109 injects a
+ * fixed reference contour that the model does not predict; passing it separately avoids building
+ * the concatenated (sets, n_art+1, 2, 50) tensor.  upper_incisor: (2,50) planar contour(s);
+ * set k reads upper_incisor + k * upper_incisor_stride floats (stride 0 = one shared contour).
+ * art_index_host[4] (upper-incisor) is ignored. */
+ASB_API int asb_tract_variables_ref(const float* sets_ptr, int64_t sets, int n_art,
+                            const int32_t* art_index_host, const float* upper_incisor,
+                            int64_t upper_incisor_stride, float* val, int32_t* idx, float* poc,
+                            void* stream);
+
 /* ------------------------------------------------------------------ model */
 
 typedef struct asb_model asb_model;
@@ -119,10 +129,17 @@ ASB_API size_t asb_model_workspace_bytes(const asb_model* m, int B, int T);
 /* ArtSpeech.forward(x, lengths), models.py:126-145.
  * x (B, T_in) int64 tokens (row stride T_in); lengths_host (B) sorted descending, each in
  * [1, T_in]; out (B, T, n_art, 2, n_samples) fp32 contiguous with T = lengths_host[0].
- * Rows past a sequence's length receive the constant padded frame, as the reference does.
- * use_rnn = 0 gives SimpleArtSpeech.forward (models.py:78-96; embedding -> linear). */
+ * Rows past a sequence's length receive the constant padded frame, as the reference does. */
 ASB_API int asb_model_forward(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host, int B,
                       float* out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Per-stage device timing of asb_model_forward (CUDA events on `stream`): enable, run forwards,
+ * then read the accumulated milliseconds and launch counts (synchronises the recorded events).
+ * Stages: 0 gather (embedding + layer-0 projection), 1 GRU layer 0, 2 layer-1 projection GEMM,
+ * 3 GRU layer 1, 4 fused decoder. */
+#define ASB_N_STAGES 5
+ASB_API int asb_model_profile_enable(asb_model* m, int enable);
+ASB_API int asb_model_profile_read(asb_model* m, float* stage_ms_out, int32_t* stage_calls_out, int reset);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,101 @@
+"""Timed CPU baseline: the reference's evaluation path restated with the reference's own CPU ops.
+
+TEST / BENCH INFRASTRUCTURE ONLY (see ``oracle/__init__.py``); used by ``bench.py``'s
+``cpu_baseline`` leg and ``--impl reference`` arm.  The reference checkout does not travel to the
+GPU box, so this "port" reproduces what the reference executes on the host, op for op:
+
+* forward: stock torch CPU ``nn.Embedding`` / ``nn.GRU`` (packed) / ``nn.Linear`` / ``nn.LayerNorm``
+  (``oracle.model.artspeech_forward``; models.py:126-145), fp32;
+* P2CP per sentence with ``torch.cdist`` + two ``min`` (phoneme_to_articulation/metrics.py:41-44,
+  called as evaluation.py:68-72);
+* tract variables per frame, for prediction and target, in a Python loop with ``torch.cdist``,
+  two ``min`` and three ``.item()`` per search (tract_variables.py:23-35 driven by
+  phoneme_to_articulation/__init__.py:242-261), after injecting the upper incisor
+  (evaluation.py:93-109).
+"""
+from __future__ import annotations
+
+import time
+
+import torch
+
+from artspeech_b200 import synthetic
+from oracle import geometry as og
+from oracle import model as omodel
+
+
+def _p2cp_cdist(u, v):
+    """metrics.py:32-46 with reduction 'none' (fp32, torch.cdist as the reference)."""
+    n, m = u.shape[-2], v.shape[-2]
+    dist = torch.cdist(u, v)
+    u2cp, _ = dist.min(axis=-1)
+    v2cp, _ = dist.min(axis=-2)
+    return (torch.sum(u2cp, dim=-1) / n + torch.sum(v2cp, dim=-1) / m) / 2
+
+
+def _tv_cdist(arr1, arr2):
+    """tract_variables.py:23-35."""
+    d = torch.cdist(arr1, arr2)
+    min_d0, argmin_d0 = d.min(dim=0)
+    min_d1, argmin_d1 = min_d0.min(dim=0)
+    i = argmin_d0[argmin_d1].item()
+    j = argmin_d1.item()
+    return min_d1.item(), arr1[i], arr2[j]
+
+
+def _frame_tvs(frame):
+    """tract_variables.py:73-125 for one (11, 2, 50) frame given as name -> (50, 2) views."""
+    d = {n: frame[k].T for k, n in enumerate(synthetic.TV_ARTICULATORS)}
+    s = og.ART_SLICES
+    tongue, uinc, spm = d[og.TONGUE], d[og.UPPER_INCISOR], d[og.SOFT_PALATE_MIDLINE]
+    la = _tv_cdist(d[og.LOWER_LIP], d[og.UPPER_LIP])
+    ttcd = _tv_cdist(tongue[slice(*s["tongue-tip"])], uinc[slice(*s["upper-incisor"])])
+    palate = torch.cat([uinc[slice(*s["hard-palate"])], spm[slice(*s["soft-palate"])]], axis=0)
+    tbcd = _tv_cdist(tongue[slice(*s["tongue-body"])], palate)
+    vel = _tv_cdist(spm[slice(*s["velum"])], d[og.PHARYNX])
+    return la[0], ttcd[0], tbcd[0], vel[0]
+
+
+@torch.no_grad()
+def evaluate_batch_cpu(sd, tokens, lengths, targets):
+    """One evaluation step the way the reference runs it on the host.  Returns
+    (per-utterance mean P2CP (B, N), TV sums pred (4), TV sums target (4), frames)."""
+    outputs = omodel.artspeech_forward(sd, tokens, lengths, torch.float32)         # evaluation.py:57
+    T = outputs.shape[1]
+    targets = targets[:, :T]
+    per_utt = []
+    for so, st, L in zip(outputs, targets, lengths):                               # evaluation.py:68-72
+        L = int(L)
+        p = _p2cp_cdist(so[:L].unsqueeze(0).transpose(-1, -2), st[:L].unsqueeze(0).transpose(-1, -2))
+        per_utt.append(p.mean(dim=1)[0])
+    out11 = synthetic.inject_upper_incisor(outputs)                                # evaluation.py:93-109
+    tgt11 = synthetic.inject_upper_incisor(targets)
+    tv_p = [0.0] * 4
+    tv_t = [0.0] * 4
+    frames = 0
+    for so, st, L in zip(out11, tgt11, lengths):                                   # __init__.py:222-261
+        for f in range(int(L)):
+            a = _frame_tvs(so[f])
+            b = _frame_tvs(st[f])
+            for k in range(4):
+                tv_p[k] += a[k]
+                tv_t[k] += b[k]
+            frames += 1
+    return torch.stack(per_utt), tv_p, tv_t, frames
+
+
+def time_cpu_baseline(sd, batch, seq_len, repeats=1, seed=0, threads=None):
+    """Wall-clock frames/s of ``evaluate_batch_cpu`` on (batch, seq_len) synthetic utterances."""
+    if threads:
+        torch.set_num_threads(threads)
+    tokens = synthetic.tokens(batch, seq_len, 45, seed=seed)
+    lengths = [seq_len] * batch
+    targets = synthetic.contours(batch * seq_len, 10, 50, seed=seed + 1).view(batch, seq_len, 10, 2, 50)
+    evaluate_batch_cpu(sd, tokens[:1, :8], [8], targets[:1, :8])  # warm-up of the op dispatch paths
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        evaluate_batch_cpu(sd, tokens, lengths, targets)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return batch * seq_len / best, best
