@@ -33,6 +33,28 @@ def length_mask(lengths, T, device):
     return torch.arange(T, device=device).view(1, -1) < L  # (B, T), helpers.py:79-91 make_padding_mask
 
 
+def accumulate(p2cp, tv_pred, tv_tgt, lengths):
+    """Per-frame results -> the fp64 accumulator vector (layout above).  Pure tensor ops on the
+    inputs' device; p2cp (B,T,N), tv_* (B,T,4), lengths (B)."""
+    B, T, n = p2cp.shape
+    m = length_mask(lengths, T, p2cp.device).unsqueeze(-1).to(torch.float64)
+    Lf = m.sum(dim=1)                                                 # (B, 1)
+    per_utt = (p2cp.to(torch.float64) * m).sum(dim=1) / Lf            # (B, N) mean over the valid frames
+    acc = torch.zeros(accumulator_size(n), dtype=torch.float64, device=p2cp.device)
+    acc[:n] = per_utt.sum(dim=0)
+    acc[n] = float(B)
+    acc[n + 1:n + 5] = (tv_pred.to(torch.float64) * m).sum(dim=(0, 1))
+    acc[n + 5:n + 9] = (tv_tgt.to(torch.float64) * m).sum(dim=(0, 1))
+    acc[n + 9:n + 13] = ((tv_pred - tv_tgt).abs().to(torch.float64) * m).sum(dim=(0, 1))
+    acc[n + 13] = m.sum()
+    return acc
+
+
+def shard_utterances(n_utterances, rank, world):
+    """Indices of the utterances rank ``rank`` of ``world`` owns (round-robin)."""
+    return list(range(rank, n_utterances, world))
+
+
 @torch.no_grad()
 def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_incisor=None, mark=None):
     """One evaluation step on the model's device.
@@ -52,23 +74,12 @@ def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_inc
     tgt = targets[:, :T]
     if not tgt.is_contiguous():
         tgt = tgt.contiguous()
-    mask = length_mask(lengths, T, outputs.device)
     p2cp = p2cp_distance(outputs, tgt)                                # evaluation.py:72 (all sentences at once)
     mark("p2cp")
     tv_pred, _, _ = tract_variables_batch(outputs, articulators, upper_incisor)   # __init__.py:256
     tv_tgt, _, _ = tract_variables_batch(tgt, articulators, upper_incisor)        # __init__.py:261
     mark("tv")
-    n = outputs.shape[2]
-    m = mask.unsqueeze(-1).to(torch.float64)
-    Lf = m.sum(dim=1)                                                 # (B, 1)
-    per_utt = (p2cp.to(torch.float64) * m).sum(dim=1) / Lf            # (B, N) mean over the valid frames
-    acc = torch.zeros(accumulator_size(n), dtype=torch.float64, device=outputs.device)
-    acc[:n] = per_utt.sum(dim=0)
-    acc[n] = float(outputs.shape[0])
-    acc[n + 1:n + 5] = (tv_pred.to(torch.float64) * m).sum(dim=(0, 1))
-    acc[n + 5:n + 9] = (tv_tgt.to(torch.float64) * m).sum(dim=(0, 1))
-    acc[n + 9:n + 13] = ((tv_pred - tv_tgt).abs().to(torch.float64) * m).sum(dim=(0, 1))
-    acc[n + 13] = m.sum()
+    acc = accumulate(p2cp, tv_pred, tv_tgt, lengths)
     mark("reduce")
     return {"outputs": outputs, "p2cp": p2cp, "tv_pred": tv_pred, "tv_target": tv_tgt, "acc": acc}
 
