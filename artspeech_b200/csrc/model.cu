@@ -92,6 +92,8 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   const size_t o_fc2_w = p.take(sizeof(float) * N * kFc * kFc), o_fc2_b = p.take(sizeof(float) * N * kFc);
   const size_t o_ln2_w = p.take(sizeof(float) * N * kFc), o_ln2_b = p.take(sizeof(float) * N * kFc);
   const size_t o_head_w = p.take(sizeof(float) * N * kHeadPad * kFc), o_head_b = p.take(sizeof(float) * N * kHeadPad);
+  const bool umma = umma_decoder_supported(m);
+  const size_t o_umma = umma ? p.take(sizeof(float) * umma_image_floats(n_art)) : 0;
 
   cudaError_t e = cudaMalloc(&m->arena, p.total);
   if (e != cudaSuccess) {
@@ -117,9 +119,12 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   w.fc2_w = F(o_fc2_w); w.fc2_b = F(o_fc2_b);
   w.ln2_w = F(o_ln2_w); w.ln2_b = F(o_ln2_b);
   w.head_w = F(o_head_w); w.head_b = F(o_head_b);
+  w.umma_image = umma ? F(o_umma) : nullptr;
+  m->decoder_impl = umma ? 1 : 0;
 
   int rc = pack_recurrent_weights(m, src, st);
   if (!rc) rc = pack_dense_weights(m, src, st);
+  if (!rc && umma) rc = pack_umma_image(m, src, st);
   if (!rc) rc = check_cuda(cudaStreamSynchronize(st), "asb_model_create: packing kernels");
   if (rc) {
     cudaFree(m->arena);
@@ -199,9 +204,22 @@ extern "C" int asb_model_forward(asb_model* m, const int64_t* x, int T_in, const
   mark(3);
   if ((rc = launch_recurrent_layer(m, 1, ws.gi, ws.lengths, ws.out1, B, T, st))) return rc;
   mark(4);
-  if ((rc = launch_decoder(m, ws.out1, out, int(M), st))) return rc;
+  if (m->decoder_impl == 1) {
+    if ((rc = launch_decoder_umma(m, ws.out1, out, int(M), st))) return rc;
+  } else {
+    if ((rc = launch_decoder(m, ws.out1, out, int(M), st))) return rc;
+  }
   mark(5);
   if (prof) m->pending.push_back(ev);
+  return ASB_OK;
+}
+
+extern "C" int asb_model_set_decoder(asb_model* m, int impl) {
+  if (!m) return set_error(ASB_ERR_INVALID, "asb_model_set_decoder: null model");
+  if (impl == 1 && !m->w.umma_image)
+    return set_error(ASB_ERR_UNSUPPORTED, "asb_model_set_decoder: the tcgen05 decoder needs fast precision and n_samples = 50");
+  if (impl != 0 && impl != 1) return set_error(ASB_ERR_INVALID, "asb_model_set_decoder: impl must be 0 or 1");
+  m->decoder_impl = impl;
   return ASB_OK;
 }
 

@@ -31,6 +31,8 @@ struct PackedWeights {
   float* fc2_w; float* fc2_b;     // [N][256][256], [N][256]
   float* ln2_w; float* ln2_b;     // [N][256]
   float* head_w; float* head_b;   // [N][128][256] (x rows 0..D-1, y rows D..2D-1, rest zero), [N][128]
+  // pre-swizzled tf32 weight image streamed by the tcgen05 decoder (decoder_umma.cu); fast mode only
+  float* umma_image;
 };
 
 }  // namespace asb
@@ -44,6 +46,7 @@ struct asb_model {
   size_t arena_bytes;
   asb::PackedWeights w;
   // optional per-stage timing (asb_model_profile_*): one event set per profiled forward
+  int decoder_impl = 0;  // 0 = mma.sync (decoder.cu), 1 = tcgen05/TMEM (decoder_umma.cu)
   bool profile = false;
   std::vector<std::array<cudaEvent_t, ASB_N_STAGES + 1>> pending;
   std::vector<std::array<cudaEvent_t, ASB_N_STAGES + 1>> free_sets;
@@ -68,5 +71,11 @@ int launch_linear(const asb_model* m, const float* A, const float* W, const floa
 // rnn_out (M, 2H) -> contours (M, N_art, 2, D): linear.0 + ReLU, then every predictor, sigmoid
 int launch_decoder(const asb_model* m, const float* rnn_out, float* out, int M, cudaStream_t st);
 int pack_dense_weights(asb_model* m, const asb_weights* w, cudaStream_t st);
+
+// ---- tcgen05 decoder (decoder_umma.cu) ----------------------------------------------
+size_t umma_image_floats(int n_art);
+bool umma_decoder_supported(const asb_model* m);
+int pack_umma_image(asb_model* m, const asb_weights* w, cudaStream_t st);
+int launch_decoder_umma(const asb_model* m, const float* rnn_out, float* out, int M, cudaStream_t st);
 
 }  // namespace asb

@@ -140,6 +140,12 @@ class ArtSpeech(nn.Module):
         self._workspace = None
         return super()._apply(fn, *args, **kwargs)
 
+    def set_decoder(self, impl):
+        """"tcgen05" (default in fast precision) or "mma" (mma.sync kernel) for the fused decoder."""
+        dev = self.embedding.weight.device
+        code = {"tcgen05": 1, "mma": 0}[impl]
+        _lib.check(_lib.lib().asb_model_set_decoder(self._ensure_native(dev), code))
+
     # ------------------------------------------------------------------ per-stage timing
     STAGES = ("gather", "gru_l0", "proj_l1", "gru_l1", "decoder")
 

@@ -133,6 +133,10 @@ ASB_API size_t asb_model_workspace_bytes(const asb_model* m, int B, int T);
 ASB_API int asb_model_forward(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host, int B,
                       float* out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Decoder implementation: 1 = tcgen05/TMEM kernel (default in fast precision with n_samples = 50),
+ * 0 = mma.sync kernel (always used in fp32 precision).  Both compute models.py:140-145. */
+ASB_API int asb_model_set_decoder(asb_model* m, int impl);
+
 /* Per-stage device timing of asb_model_forward (CUDA events on `stream`): enable, run forwards,
  * then read the accumulated milliseconds and launch counts (synchronises the recorded events).
  * Stages: 0 gather (embedding + layer-0 projection), 1 GRU layer 0, 2 layer-1 projection GEMM,
