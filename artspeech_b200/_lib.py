@@ -51,6 +51,11 @@ SIGNATURES = {
     "asb_tract_variables_ref": (ctypes.c_int, [_c_f32p, ctypes.c_int64, ctypes.c_int,
                                                ctypes.POINTER(ctypes.c_int32), _c_f32p, ctypes.c_int64, _c_f32p,
                                                ctypes.c_void_p, _c_f32p, ctypes.c_void_p]),
+    "asb_model_forward_resident": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                                  ctypes.POINTER(ctypes.c_int32), ctypes.c_void_p, ctypes.c_int,
+                                                  _c_f32p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]),
+    "asb_eval_accumulate": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                                           ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
     "asb_model_set_decoder": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "asb_model_profile_enable": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "asb_model_profile_read": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_float),

@@ -152,6 +152,12 @@ extern "C" size_t asb_model_workspace_bytes(const asb_model* m, int B, int T) {
 
 extern "C" int asb_model_forward(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host, int B,
                                  float* out, void* workspace, size_t workspace_bytes, void* stream) {
+  return asb_model_forward_resident(m, x, T_in, lengths_host, nullptr, B, out, workspace, workspace_bytes, stream);
+}
+
+extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host,
+                                          const int32_t* lengths_dev, int B, float* out, void* workspace,
+                                          size_t workspace_bytes, void* stream) {
   if (!m || !x || !lengths_host || !out) return set_error(ASB_ERR_INVALID, "asb_model_forward: null argument");
   if (B <= 0 || T_in <= 0) return set_error(ASB_ERR_INVALID, "asb_model_forward: empty batch");
   // pack_padded_sequence(enforce_sorted=True) semantics, models.py:136
@@ -165,16 +171,21 @@ extern "C" int asb_model_forward(asb_model* m, const int64_t* x, int T_in, const
   }
   const int T = lengths_host[0];
   if (T > T_in) return set_error(ASB_ERR_INVALID, "asb_model_forward: lengths[0] = %d exceeds the sequence dimension %d", T, T_in);
-  const Workspace ws = plan_workspace(m, workspace, B, T);
+  Workspace ws = plan_workspace(m, workspace, B, T);
   if (!workspace || workspace_bytes < ws.bytes)
     return set_error(ASB_ERR_WORKSPACE, "asb_model_forward: workspace %zu B < required %zu B", workspace_bytes, ws.bytes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const long long M = (long long)B * T;
   if (M > 0x7fffffffLL / 64) return set_error(ASB_ERR_INVALID, "asb_model_forward: batch too large");
 
-  int rc = check_cuda(cudaMemcpyAsync(ws.lengths, lengths_host, sizeof(int) * (size_t)B, cudaMemcpyHostToDevice, st),
-                      "asb_model_forward: lengths H2D");
-  if (rc) return rc;
+  int rc = ASB_OK;
+  if (lengths_dev) {
+    ws.lengths = const_cast<int*>(lengths_dev);  // caller keeps a device copy (CUDA-graph friendly)
+  } else {
+    rc = check_cuda(cudaMemcpyAsync(ws.lengths, lengths_host, sizeof(int) * (size_t)B, cudaMemcpyHostToDevice, st),
+                    "asb_model_forward: lengths H2D");
+    if (rc) return rc;
+  }
   // padded steps of the recurrent outputs are zero (pad_packed_sequence, models.py:138)
   rc = check_cuda(cudaMemsetAsync(ws.out0, 0, sizeof(float) * (size_t)M * 2 * kH, st), "asb_model_forward: memset");
   if (rc) return rc;

@@ -50,13 +50,29 @@ def accumulate(p2cp, tv_pred, tv_tgt, lengths):
     return acc
 
 
+def accumulate_device(p2cp, tv_pred, tv_tgt, lengths_dev):
+    """Same vector as ``accumulate`` computed by the library (asb_eval_accumulate): two launches,
+    fixed summation order.  All tensors on the GPU; lengths_dev (B) int32."""
+    from . import _lib
+    B, T, n = p2cp.shape
+    dev = p2cp.device
+    scratch = torch.empty(B * (n + 12), dtype=torch.float64, device=dev)
+    acc = torch.empty(accumulator_size(n), dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().asb_eval_accumulate(
+            _lib.ptr(p2cp.contiguous()), _lib.ptr(tv_pred.contiguous()), _lib.ptr(tv_tgt.contiguous()),
+            _lib.ptr(lengths_dev), B, T, n, _lib.ptr(scratch), _lib.ptr(acc), _lib.stream_ptr(dev)))
+    return acc
+
+
 def shard_utterances(n_utterances, rank, world):
     """Indices of the utterances rank ``rank`` of ``world`` owns (round-robin)."""
     return list(range(rank, n_utterances, world))
 
 
 @torch.no_grad()
-def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_incisor=None, mark=None):
+def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_incisor=None, mark=None,
+                   lengths_dev=None):
     """One evaluation step on the model's device.
 
     tokens (B, T) int64, lengths sorted descending, targets (B, T, N, 2, 50) fp32 - all on the GPU.
@@ -67,8 +83,10 @@ def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_inc
     articulators = articulators or synthetic.ARTICULATORS
     if upper_incisor is None:
         upper_incisor = synthetic.UPPER_INCISOR_REF
+    if lengths_dev is None:
+        lengths_dev = torch.as_tensor([int(v) for v in lengths], dtype=torch.int32).to(tokens.device)
     mark("start")
-    outputs = model(tokens, lengths)                                  # evaluation.py:57
+    outputs = model(tokens, lengths, lengths_dev=lengths_dev)         # evaluation.py:57
     mark("forward")
     T = outputs.shape[1]
     tgt = targets[:, :T]
@@ -79,7 +97,7 @@ def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_inc
     tv_pred, _, _ = tract_variables_batch(outputs, articulators, upper_incisor)   # __init__.py:256
     tv_tgt, _, _ = tract_variables_batch(tgt, articulators, upper_incisor)        # __init__.py:261
     mark("tv")
-    acc = accumulate(p2cp, tv_pred, tv_tgt, lengths)
+    acc = accumulate_device(p2cp, tv_pred, tv_tgt, lengths_dev)       # evaluation.py:68-84,142-156
     mark("reduce")
     return {"outputs": outputs, "p2cp": p2cp, "tv_pred": tv_pred, "tv_target": tv_tgt, "acc": acc}
 
@@ -105,3 +123,43 @@ def summarize(acc, n_articulators, articulators=None):
     out["utterances"] = utt
     out["frames"] = frames
     return out
+
+
+class GraphedEvaluator:
+    """``evaluate_batch`` for a fixed (batch, lengths) shape captured once in a CUDA graph and replayed:
+    the step is ~10 short kernels, so eager launches leave the GPU idle between them.  Inputs are
+    copied into static device buffers (``tokens``, ``targets``); results are the static tensors of
+    the captured step (valid until the next replay)."""
+
+    def __init__(self, model, tokens, lengths, targets, articulators=None, upper_incisor=None, warmup=3):
+        dev = model.embedding.weight.device
+        self.model = model
+        self.lengths = [int(v) for v in lengths]
+        self.lengths_dev = torch.as_tensor(self.lengths, dtype=torch.int32).to(dev)
+        self.tokens = tokens.to(dev).clone()
+        self.targets = targets.to(dev).clone()
+        self.upper_incisor = (synthetic.UPPER_INCISOR_REF if upper_incisor is None else upper_incisor).to(dev)
+        self.articulators = articulators
+
+        def run():
+            return evaluate_batch(model, self.tokens, self.lengths, self.targets, self.articulators,
+                                  self.upper_incisor, lengths_dev=self.lengths_dev)
+
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                run()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.result = run()
+
+    def __call__(self, tokens=None, targets=None):
+        if tokens is not None:
+            self.tokens.copy_(tokens, non_blocking=True)
+        if targets is not None:
+            self.targets.copy_(targets, non_blocking=True)
+        self.graph.replay()
+        return self.result

@@ -164,11 +164,13 @@ class ArtSpeech(nn.Module):
         return {name: (float(ms[k]), int(calls[k])) for k, name in enumerate(self.STAGES)}
 
     # ------------------------------------------------------------------ forward
-    def forward(self, x, lengths):
+    def forward(self, x, lengths, lengths_dev=None):
         """
         Args:
             x (torch.tensor): Torch tensor of shape (bs, seq_len), int64 tokens.
             lengths (list): Lengths of the input sequences sorted in decreasing order.
+            lengths_dev (optional, extension): int32 CUDA tensor holding the same lengths; when given
+                no host->device copy is enqueued, which makes the call capturable in a CUDA graph.
 
         Return:
             output (torch.tensor): (bs, max(lengths), n_articulators, 2, n_samples) float32
@@ -202,8 +204,13 @@ class ArtSpeech(nn.Module):
         vocab, n_art, _, _, n_samples = self._dims
         out = torch.empty(B, T, n_art, 2, n_samples, dtype=torch.float32, device=dev)
         c_len = (ctypes.c_int32 * B)(*L)
+        ldev = None
+        if lengths_dev is not None:
+            if lengths_dev.dtype != torch.int32 or lengths_dev.device != dev or lengths_dev.numel() != B:
+                raise ValueError("lengths_dev must be an int32 tensor of shape (bs,) on the model's device")
+            ldev = _lib.ptr(lengths_dev)
         with torch.cuda.device(dev):
-            _lib.check(lib.asb_model_forward(handle, _lib.ptr(xd), T_in, c_len, B, _lib.ptr(out),
-                                             _lib.ptr(self._workspace), self._workspace.numel(),
-                                             _lib.stream_ptr(dev)))
+            _lib.check(lib.asb_model_forward_resident(handle, _lib.ptr(xd), T_in, c_len, ldev, B, _lib.ptr(out),
+                                                      _lib.ptr(self._workspace), self._workspace.numel(),
+                                                      _lib.stream_ptr(dev)))
         return out

@@ -18,7 +18,6 @@ from __future__ import annotations
 import argparse
 import json
 import os
-import subprocess
 import sys
 import threading
 import time
@@ -51,55 +50,60 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
-
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock + throttle reasons sampled every 20 ms through NVML while the timed region runs."""
 
     def __init__(self, index):
         self.index = index
-        self.proc = None
-        self.lines = []
+        self.samples = []
+        self.reasons = set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self.thread = None
+        self.error = None
+
+    def _run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            flags = {
+                "hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown")
+                else nv.nvmlClocksThrottleReasonHwSlowdown,
+                "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown",
+                                               getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0)),
+                "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown",
+                                               getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0)),
+                "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap",
+                                        getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0)),
+            }
+            get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons",
+                                  getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons", None))
+            while not self._stop.is_set():
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                if get_reasons is not None:
+                    r = int(get_reasons(h))
+                    for name, bit in flags.items():
+                        if bit and (r & int(bit)):
+                            self.reasons.add(name)
+                self._stop.wait(0.02)
+        except Exception as exc:  # NVML missing: report it instead of inventing numbers
+            self.error = repr(exc)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
-            self.thread.start()
-        except OSError:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        for line in self.lines:
-            parts = [p.strip() for p in line.split(",")]
-            if len(parts) < 7:
-                continue
-            try:
-                sm.append(float(parts[0])); mx.append(float(parts[1]))
-            except ValueError:
-                continue
-            for name, flag in zip(names, parts[3:7]):
-                if flag.lower().startswith("active"):
-                    reasons.add(name)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        self._stop.set()
+        if self.thread is not None:
+            self.thread.join(timeout=2)
+        sm = sorted(self.samples)
+        out = {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "samples": len(sm),
+               "reasons": sorted(self.reasons)}
+        if self.error:
+            out["error"] = self.error
+        return out
 
 
 def visible_index(local_rank):
@@ -199,33 +203,62 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         step(tokens_d, targets_d)
     torch.cuda.synchronize()
+    l0 = _lib.launch_count()
+    step(tokens_d, targets_d)
+    launches_per_step = _lib.launch_count() - l0
+
+    # The step is ~10 short kernels: replaying it from a CUDA graph removes the host launch gaps.
+    graphed = None
+    if not args.no_graph:
+        graphed = evaluation.GraphedEvaluator(model, tokens_d, lengths, targets_d, upper_incisor=uinc_d)
+
+    def fast_step(tok=None, tgt=None):
+        if graphed is None:
+            return step(tokens_d if tok is None else tok, targets_d if tgt is None else tgt)
+        res = graphed(tok, tgt)
+        evaluation.reduce_accumulators(res["acc"])
+        return res
+
+    for _ in range(max(args.warmup, 3)):
+        fast_step()
+    torch.cuda.synchronize()
 
     # ---------------- device-resident timing (value)
-    model.profile(True)
-    model.read_profile(reset=True)
     sampler = ClockSampler(visible_index(local_rank))
-    launches0 = _lib.launch_count()
     barrier(); torch.cuda.synchronize()
     sampler.start()
     starts, ends = [], []
     for _ in range(args.steps):
         flush.zero_()                                   # evict L2 (not timed)
         s = torch.cuda.Event(enable_timing=True); e = torch.cuda.Event(enable_timing=True)
-        marks = []
         s.record()
-        step(tokens_d, targets_d, make_mark(marks))
+        fast_step()
         e.record()
-        starts.append(s); ends.append(e); stage_events.append(marks)
+        starts.append(s); ends.append(e)
     torch.cuda.synchronize(); barrier()
-    clocks = sampler.stop()
-    launches = _lib.launch_count() - launches0
-    model.profile(False)
     step_ms = [s.elapsed_time(e) for s, e in zip(starts, ends)]
     total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
     total_ms = float(total_ms.item())
     value = world * frames * args.steps / (total_ms * 1e-3)
+    launches = launches_per_step * args.steps
+
+    # ---------------- the same steps launched eagerly with CUDA events around every kernel
+    model.profile(True)
+    model.read_profile(reset=True)
+    eager_ms = []
+    for _ in range(args.steps):
+        flush.zero_()
+        s = torch.cuda.Event(enable_timing=True); e = torch.cuda.Event(enable_timing=True)
+        marks = []
+        s.record()
+        step(tokens_d, targets_d, make_mark(marks))
+        e.record()
+        torch.cuda.synchronize()
+        eager_ms.append(s.elapsed_time(e)); stage_events.append(marks)
+    clocks = sampler.stop()
+    model.profile(False)
 
     # per-stage device times (means over the timed steps)
     prof = model.read_profile(reset=True)
@@ -237,7 +270,8 @@ def run_ours(args):
     for k in agg:
         agg[k] /= args.steps
     stage_ms.update({"p2cp": agg.get("p2cp", 0.0), "tv_pred_and_target": agg.get("tv", 0.0),
-                     "forward_total": agg.get("forward", 0.0), "accumulate": agg.get("reduce", 0.0)})
+                     "forward_total": agg.get("forward", 0.0), "accumulate": agg.get("reduce", 0.0),
+                     "eager_step": sum(eager_ms) / len(eager_ms)})
 
     # ---------------- roofline of the dominant kernel
     kernels = {
@@ -268,14 +302,12 @@ def run_ours(args):
 
     # ---------------- end to end from pinned host buffers (e2e)
     for _ in range(2):
-        r = step(tokens_h.to(dev, non_blocking=True), targets_h.to(dev, non_blocking=True))
+        r = fast_step(tokens_h, targets_h)
         r["acc"].cpu()
     barrier(); torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        tok = tokens_h.to(dev, non_blocking=True)
-        tgt = targets_h.to(dev, non_blocking=True)
-        r = step(tok, tgt)
+        r = fast_step(tokens_h, targets_h)              # H2D of tokens + targets from pinned memory
         acc_h = r["acc"].cpu()                          # D2H of the step's result (synchronises)
     torch.cuda.synchronize()
     e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
@@ -309,7 +341,8 @@ def run_ours(args):
                                    f"per GPU (configs[1]), 10 articulators x 50 points",
                        "precision": args.precision, "frames_per_step_per_gpu": frames,
                        "parallelism": f"utterance-sharded x{world}, one NCCL all-reduce of {N_ART + 14} fp64 per step",
-                       "l2": "256 MiB flush between timed steps; per-step working set > L2"},
+                       "l2": "256 MiB flush between timed steps; per-step working set > L2",
+                       "launch": "CUDA graph replay of the captured step" if graphed is not None else "eager"},
             "stage_ms": {k: round(v, 4) for k, v in stage_ms.items()},
             "roofline": roofline, "cpu_baseline": cpu_baseline,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
@@ -334,6 +367,7 @@ def main():
     ap.add_argument("--cpu-batch", type=int, default=32, help="utterances in the bounded CPU-baseline sample")
     ap.add_argument("--ref-batch", type=int, default=8, help="utterances per step of --impl reference")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly instead of replaying a CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -89,6 +89,16 @@ ASB_API int asb_tract_variables_ref(const float* sets_ptr, int64_t sets, int n_a
                             int64_t upper_incisor_stride, float* val, int32_t* idx, float* poc,
                             void* stream);
 
+/* Length-masked aggregation of one batch's per-frame metrics, as run_test does per sentence
+ * (evaluation.py:68-84,142-156): p2cp (B,T,n_art), tv_pred/tv_target (B,T,4) fp32, lengths_dev (B)
+ * DEVICE int32.  scratch: B*(n_art+12) doubles.  acc (n_art+14 doubles) is OVERWRITTEN with
+ * [0:n) sum over utterances of per-utterance mean P2CP; [n] utterances; [n+1:n+5) sum of predicted
+ * TVs over valid frames; [n+5:n+9) target TVs; [n+9:n+13) |pred-target|; [n+13] valid frames.
+ * Fixed summation order (bit-reproducible). */
+ASB_API int asb_eval_accumulate(const float* p2cp, const float* tv_pred, const float* tv_target,
+                        const int32_t* lengths_dev, int B, int T, int n_art, double* scratch,
+                        double* acc, void* stream);
+
 /* ------------------------------------------------------------------ model */
 
 typedef struct asb_model asb_model;
@@ -132,6 +142,13 @@ ASB_API size_t asb_model_workspace_bytes(const asb_model* m, int B, int T);
  * Rows past a sequence's length receive the constant padded frame, as the reference does. */
 ASB_API int asb_model_forward(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host, int B,
                       float* out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Same, for callers that already hold the lengths on the device (no host->device copy is enqueued,
+ * which makes the call capturable in a CUDA graph).  lengths_host is still used for validation and
+ * for T; lengths_dev (B) int32 must hold the same values. */
+ASB_API int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host,
+                               const int32_t* lengths_dev, int B, float* out, void* workspace,
+                               size_t workspace_bytes, void* stream);
 
 /* Decoder implementation: 1 = tcgen05/TMEM kernel (default in fast precision with n_samples = 50),
  * 0 = mma.sync kernel (always used in fp32 precision).  Both compute models.py:140-145. */

@@ -1,0 +1,59 @@
+"""Device-resident evaluation step: fused accumulation kernel, CUDA-graph replay, TV with an
+external upper incisor - each against the plain torch / oracle computation."""
+import pytest
+import torch
+
+from artspeech_b200 import synthetic
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def setup():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from artspeech_b200 import evaluation, models
+    torch.manual_seed(0)
+    net = models.ArtSpeech(45, 10).cuda().eval()
+    B, T = 19, 33
+    x = synthetic.tokens(B, T, 45, seed=2).cuda()
+    L = synthetic.sorted_lengths(B, 5, T, seed=2)
+    tgt = synthetic.contours(B * T, 10, 50, seed=3).view(B, T, 10, 2, 50).cuda()
+    return evaluation, net, x, L, tgt
+
+
+def test_accumulate_kernel_matches_torch(setup):
+    evaluation, net, x, L, tgt = setup
+    res = evaluation.evaluate_batch(net, x, L, tgt)
+    want = evaluation.accumulate(res["p2cp"], res["tv_pred"], res["tv_target"], L)
+    assert torch.allclose(res["acc"], want, rtol=1e-12, atol=1e-12)
+    again = evaluation.evaluate_batch(net, x, L, tgt)["acc"]
+    assert torch.equal(res["acc"], again)          # fixed summation order: bit-reproducible
+
+
+def test_tv_external_upper_incisor_equals_injected(setup):
+    evaluation, net, x, L, tgt = setup
+    from artspeech_b200.tract_variables import tract_variables_batch
+    a = tract_variables_batch(tgt, synthetic.ARTICULATORS, synthetic.UPPER_INCISOR_REF)
+    b = tract_variables_batch(synthetic.inject_upper_incisor(tgt), synthetic.TV_ARTICULATORS)
+    for u, v in zip(a, b):
+        assert torch.equal(u, v)
+    with pytest.raises(KeyError):
+        tract_variables_batch(tgt, synthetic.ARTICULATORS)   # no upper incisor anywhere
+
+
+def test_graph_replay_equals_eager(setup):
+    evaluation, net, x, L, tgt = setup
+    eager = evaluation.evaluate_batch(net, x, L, tgt)
+    g = evaluation.GraphedEvaluator(net, x, L, tgt)
+    r = g()
+    torch.cuda.synchronize()
+    assert torch.equal(r["outputs"], eager["outputs"])
+    assert torch.equal(r["acc"], eager["acc"])
+    # new inputs through the static buffers
+    x2 = synthetic.tokens(x.shape[0], x.shape[1], 45, seed=9)
+    r2 = g(x2.pin_memory(), None)
+    torch.cuda.synchronize()
+    want = evaluation.evaluate_batch(net, x2.cuda(), L, tgt)
+    assert torch.equal(r2["outputs"], want["outputs"])
+    assert torch.equal(r2["acc"], want["acc"])
