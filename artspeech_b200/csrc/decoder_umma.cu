@@ -31,44 +31,55 @@ constexpr int kChunkK = 32;                 // tf32 per 128-byte swizzle row
 constexpr int kStages = 4;
 constexpr int kStageBytes = 256 * 128;      // 32 KB: up to 256 weight rows x 128 B
 constexpr int kXStride = 129;               // x-hat row stride (floats), conflict-free per-thread rows
-constexpr int kEpiThreads = 128;
-constexpr int kThreads = 192;
+constexpr int kEpiWarps = 8;                // two warps per TMEM lane quarter, each owning half the columns
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kProducerWarp = 8, kMmaWarp = 9;
+constexpr int kThreads = 320;
 
-// weight image (floats)
+// weight image (floats).  LayerNorm affines are folded into the following layer at pack time:
+// W' = W . diag(gamma), b' = b + W . beta, so the kernel only normalises.
 constexpr int kLinParams = 128;
 constexpr int kLinChunk = 128 * kChunkK;    // 4096
 constexpr int kFcChunk = 256 * kChunkK;     // 8192
 constexpr int kHeadChunk = kHeadN * kChunkK;  // 3584
-constexpr int kArtParams = 1920;
+constexpr int kArtParams = 640;             // b1' (256) | b2' (256) | bh' (128, zero padded)
 constexpr int kLinBlock = kLinParams + 8 * kLinChunk;
 constexpr int kArtBlock = kArtParams + 4 * kFcChunk + 8 * kFcChunk + 8 * kHeadChunk;
-// parameter blob offsets (floats)
-constexpr int P_LN0_G = 0, P_LN0_B = 128, P_B1 = 256, P_LN1_G = 512, P_LN1_B = 768, P_B2 = 1024, P_LN2_G = 1280,
-              P_LN2_B = 1536, P_BH = 1792;
+constexpr int P_B1 = 0, P_B2 = 256, P_BH = 512;
 
 // dynamic shared memory layout (bytes, base 1024-aligned)
 constexpr int kOffW = 0;
 constexpr int kOffX = kOffW + kStages * kStageBytes;
 constexpr int kOffP = kOffX + kTileM * kXStride * 4;
 constexpr int kOffLinB = kOffP + 2 * kArtParams * 4;
-constexpr int kOffBar = kOffLinB + kLinParams * 4;
+constexpr int kOffStat = kOffLinB + kLinParams * 4;       // float2 [2 uses][2 halves][128 rows]
+constexpr int kOffBar = kOffStat + 2 * 2 * kTileM * 8;
 constexpr int kSmemBytes = kOffBar + 256 + 1024;  // + barriers + alignment slack
 
-// dst image of W[N][K] (row stride K) as K/32 chunks of [Npad rows][32] with the 128-byte swizzle
-__global__ void pack_umma_kernel(const float* __restrict__ src, float* __restrict__ dst, int n_src, int row0,
-                                 int n_pad, int K) {
+// dst image of (W . diag(scale))[N][K] as K/32 chunks of [Npad rows][32] with the 128-byte swizzle
+__global__ void pack_umma_kernel(const float* __restrict__ src, const float* __restrict__ scale,
+                                 float* __restrict__ dst, int n_src, int row0, int n_pad, int K) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_src * K) return;
   const int ns = i / K, k = i - ns * K;
   const int n = ns + row0;
   const int kc = k >> 5, kk = k & 31;
   const int off = kc * (n_pad * kChunkK) + (n >> 3) * 256 + (n & 7) * 32 + ((((kk >> 2) ^ (n & 7)) << 2) | (kk & 3));
-  dst[off] = __uint_as_float(to_tf32(src[i]));
+  const float w = scale ? src[i] * scale[k] : src[i];
+  dst[off] = __uint_as_float(to_tf32(w));
 }
-__global__ void copy_vec_kernel(const float* __restrict__ src, float* __restrict__ dst, int n) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) dst[i] = src[i];
+// dst[n] = b[n] + sum_k W[n][k] * beta[k]   (beta may be null)
+__global__ void fold_bias_kernel(const float* __restrict__ W, const float* __restrict__ beta,
+                                 const float* __restrict__ b, float* __restrict__ dst, int N, int K) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  double acc = double(b[n]);
+  if (beta)
+    for (int k = 0; k < K; ++k) acc += double(W[(size_t)n * K + k]) * double(beta[k]);
+  dst[n] = float(acc);
 }
+
+__device__ __forceinline__ void bar_sync_epilogue() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 __device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
 
@@ -88,12 +99,13 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
   float* Xs = reinterpret_cast<float*>(smem + kOffX);
   float* Ps = reinterpret_cast<float*>(smem + kOffP);
   float* LinB = reinterpret_cast<float*>(smem + kOffLinB);
+  float2* Stat = reinterpret_cast<float2*>(smem + kOffStat);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
   uint64_t* full = bars;            // [kStages]  weights landed
   uint64_t* empty = bars + 4;       // [kStages]  MMAs that read the stage completed
   uint64_t* pfull = bars + 8;       // [2]        articulator parameters landed
   uint64_t* pempty = bars + 10;     // [2]        epilogue finished with them
-  uint64_t* a_ready = bars + 12;    //            A operand written to TMEM
+  uint64_t* a_ready = bars + 12;    //            A operand + bias-initialised accumulator are in TMEM
   uint64_t* d_ready = bars + 13;    //            accumulator complete
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
 
@@ -106,13 +118,13 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&pfull[s], 1);
-      mbar_init(&pempty[s], 4);
+      mbar_init(&pempty[s], kEpiWarps);
     }
-    mbar_init(a_ready, 4);
+    mbar_init(a_ready, kEpiWarps);
     mbar_init(d_ready, 1);
     fence_mbar_init();
   }
-  if (warp == 5) tmem_alloc(tmem_slot, 512);
+  if (warp == kMmaWarp) tmem_alloc(tmem_slot, 512);
   for (int i = tid; i < kLinParams; i += kThreads) LinB[i] = a.image[i];
   fence_before_sync();
   __syncthreads();
@@ -121,7 +133,7 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
   const uint32_t tmem_d = tmem_base;         // accumulator columns [0, 256)
   const uint32_t tmem_a = tmem_base + 256;   // A operand columns [256, 512)
 
-  if (warp == 4) {
+  if (warp == kProducerWarp) {
     // ===================== producer: weight chunks and articulator parameters =====================
     if (lane == 0) {
       uint32_t c = 0, pa = 0;
@@ -153,7 +165,7 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
       }
     }
     __syncwarp();
-  } else if (warp == 5) {
+  } else if (warp == kMmaWarp) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
       uint32_t c = 0, gcount = 0;
@@ -167,8 +179,8 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
           fence_after_sync();
           const uint64_t bdesc = smem_desc_k_sw128(smem_u32(Ws + s * kStageBytes));
 #pragma unroll
-          for (int ks = 0; ks < 4; ++ks)
-            mma_tf32_ts(tmem_d, tmem_a + j * kChunkK + ks * 8, bdesc + uint64_t(2 * ks), idesc, (j | ks) != 0);
+          for (int ks = 0; ks < 4; ++ks)  // the accumulator was pre-loaded with the bias: always accumulate
+            mma_tf32_ts(tmem_d, tmem_a + j * kChunkK + ks * 8, bdesc + uint64_t(2 * ks), idesc, true);
           commit(&empty[s]);  // frees the stage once these MMAs have read it
           ++c;
         }
@@ -188,11 +200,13 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
     }
     __syncwarp();
   } else {
-    // ===================== epilogue warps: thread = frame = TMEM lane =====================
-    const uint32_t lane_sel = uint32_t(warp * 32) << 16;
+    // ===================== epilogue: thread = (frame = TMEM lane, half of the columns) ============
+    const int quarter = warp & 3, half = warp >> 2;
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
     const uint32_t td = tmem_d + lane_sel, ta = tmem_a + lane_sel;
-    float* xrow = Xs + tid * kXStride;
-    uint32_t gcount = 0, pa = 0;
+    float* xrow = Xs + row * kXStride;
+    uint32_t gcount = 0, pa = 0, use = 0;
     uint32_t r[32];
 
     auto signal_a = [&]() {
@@ -206,48 +220,71 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
       ++gcount;
       fence_after_sync();
     };
-    // relu(D + bias) -> LayerNorm(256) -> tf32 -> A   (single-pass moments, thread-local)
-    auto ln256_to_a = [&](const float* bias, const float* gamma, const float* beta) {
+    // row moments are split over the two column halves: exchange the partial sums through smem
+    auto exchange = [&](float& s, float& ss) {
+      Stat[((use & 1) * 2 + half) * kTileM + row] = make_float2(s, ss);
+      bar_sync_epilogue();
+      const float2 o = Stat[((use & 1) * 2 + (half ^ 1)) * kTileM + row];
+      s += o.x;
+      ss += o.y;
+      ++use;
+    };
+    // pre-load this thread's accumulator columns [col0, col0 + 32 * chunks) with the next layer's bias
+    auto init_d = [&](const float* bias, int col0, int chunks) {
+      bar_sync_epilogue();  // the partner may still be reading columns that change owner
+      for (int c = 0; c < chunks; ++c) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float4 b4 = *reinterpret_cast<const float4*>(bias + col0 + 32 * c + 4 * q);
+          r[4 * q + 0] = __float_as_uint(b4.x);
+          r[4 * q + 1] = __float_as_uint(b4.y);
+          r[4 * q + 2] = __float_as_uint(b4.z);
+          r[4 * q + 3] = __float_as_uint(b4.w);
+        }
+        tmem_st32(td + col0 + 32 * c, r);
+      }
+    };
+    // relu(D) -> LayerNorm(256) without affine (folded into the next layer) -> tf32 -> A
+    auto ln256_to_a = [&]() {
+      const int col0 = half * 128;
       float s = 0.f, ss = 0.f;
 #pragma unroll 1
-      for (int c = 0; c < 8; ++c) {
-        tmem_ld32(td + 32 * c, r);
+      for (int c = 0; c < 4; ++c) {
+        tmem_ld32(td + col0 + 32 * c, r);
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          const float v = fmaxf(__uint_as_float(r[i]) + bias[32 * c + i], 0.f);
+          const float v = fmaxf(__uint_as_float(r[i]), 0.f);
           s += v;
           ss = fmaf(v, v, ss);
         }
       }
+      exchange(s, ss);
       const float mean = s * (1.f / 256.f);
       const float var = fmaxf(ss * (1.f / 256.f) - mean * mean, 0.f);
       const float rstd = rsqrtf(var + 1e-5f);
       const float shift = -mean * rstd;
 #pragma unroll 1
-      for (int c = 0; c < 8; ++c) {
-        tmem_ld32(td + 32 * c, r);
+      for (int c = 0; c < 4; ++c) {
+        tmem_ld32(td + col0 + 32 * c, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float v = fmaxf(__uint_as_float(r[i]) + bias[32 * c + i], 0.f);
-          r[i] = to_tf32(fmaf(fmaf(v, rstd, shift), gamma[32 * c + i], beta[32 * c + i]));
-        }
-        tmem_st32(ta + 32 * c, r);
+        for (int i = 0; i < 32; ++i) r[i] = to_tf32(fmaf(fmaxf(__uint_as_float(r[i]), 0.f), rstd, shift));
+        tmem_st32(ta + col0 + 32 * c, r);
       }
     };
 
     for (int u = blockIdx.x; u < a.n_units; u += gridDim.x) {
       const int tile = u / a.n_groups, grp = u % a.n_groups;
       const int g0 = grp * a.group, g1 = min(a.n_art, g0 + a.group);
-      const long long grow = (long long)tile * kTileM + tid;
+      const long long grow = (long long)tile * kTileM + row;
       const bool live = grow < a.M;
 
-      // ---- input tile -> A (tf32), K = 256
+      // ---- input tile -> A (tf32): this thread converts 128 of its frame's 256 features
       {
-        const float4* src = reinterpret_cast<const float4*>(a.rnn_out + grow * 256);
+        const float4* src = reinterpret_cast<const float4*>(a.rnn_out + grow * 256 + half * 128);
 #pragma unroll 1
-        for (int c = 0; c < 8; ++c) {
+        for (int c = 0; c < 4; ++c) {
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -257,75 +294,84 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
             r[4 * q + 2] = to_tf32(v.z);
             r[4 * q + 3] = to_tf32(v.w);
           }
-          tmem_st32(ta + 32 * c, r);
+          tmem_st32(ta + half * 128 + 32 * c, r);
         }
+        init_d(LinB, half * 64, 2);
         signal_a();
       }
-      // ---- linear.0 epilogue: relu(D + b) -> LayerNorm statistics -> x-hat kept in shared memory
+      // ---- linear.0 epilogue: relu(D) -> LayerNorm(128) statistics -> x-hat kept in shared memory
       wait_d();
       {
-        float s = 0.f;
+        const int col0 = half * 64;
+        float s = 0.f, ss = 0.f;
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          tmem_ld32(td + 32 * c, r);
+        for (int c = 0; c < 2; ++c) {
+          tmem_ld32(td + col0 + 32 * c, r);
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
-            const float v = fmaxf(__uint_as_float(r[i]) + LinB[32 * c + i], 0.f);
-            xrow[32 * c + i] = v;
+            const float v = fmaxf(__uint_as_float(r[i]), 0.f);
+            xrow[col0 + 32 * c + i] = v;
             s += v;
+            ss = fmaf(v, v, ss);
           }
         }
+        exchange(s, ss);
         const float mean = s * (1.f / 128.f);
-        float var = 0.f;
-#pragma unroll 4
-        for (int k = 0; k < 128; ++k) {
-          const float d = xrow[k] - mean;
-          var = fmaf(d, d, var);
-        }
-        const float rstd = rsqrtf(var * (1.f / 128.f) + 1e-5f);
-#pragma unroll 4
-        for (int k = 0; k < 128; ++k) xrow[k] = (xrow[k] - mean) * rstd;
+        const float var = fmaxf(ss * (1.f / 128.f) - mean * mean, 0.f);
+        const float rstd = rsqrtf(var + 1e-5f);
+        const float shift = -mean * rstd;
+#pragma unroll 8
+        for (int k = 0; k < 64; ++k)
+          xrow[col0 + k] = __uint_as_float(to_tf32(fmaf(xrow[col0 + k], rstd, shift)));
       }
 
       for (int art = g0; art < g1; ++art) {
         const uint32_t pb = pa & 1;
         const float* P = Ps + pb * kArtParams;
         mbar_wait(&pfull[pb], (pa >> 1) & 1);
-        // ---- LayerNorm(128) affine of this articulator -> A, K = 128
+        // ---- x-hat -> A (the LayerNorm(128) affine of this articulator lives in its folded W1', b1')
+        {
+          const int col0 = half * 64;
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+          for (int c = 0; c < 2; ++c) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            r[i] = to_tf32(fmaf(xrow[32 * c + i], P[P_LN0_G + 32 * c + i], P[P_LN0_B + 32 * c + i]));
-          tmem_st32(ta + 32 * c, r);
+            for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(xrow[col0 + 32 * c + i]);
+            tmem_st32(ta + col0 + 32 * c, r);
+          }
         }
+        init_d(P + P_B1, half * 128, 4);
         signal_a();
         wait_d();
-        ln256_to_a(P + P_B1, P + P_LN1_G, P + P_LN1_B);
+        ln256_to_a();
+        init_d(P + P_B2, half * 128, 4);
         signal_a();
         wait_d();
-        ln256_to_a(P + P_B2, P + P_LN2_G, P + P_LN2_B);
+        ln256_to_a();
+        init_d(P + P_BH, half * 64, 2);
         signal_a();
         wait_d();
-        // ---- heads: sigmoid(D + b) -> contours in their final layout
+        // ---- heads: sigmoid(D) -> contours in their final layout (this thread: 64 of the 100 columns)
         {
           float* dst = a.out + (grow * a.n_art + art) * 100;
 #pragma unroll 1
-          for (int c = 0; c < 4; ++c) {
-            tmem_ld32(td + 32 * c, r);
-            tmem_ld_wait();
-            if (live) {
+          for (int c = 0; c < 2; ++c) {
+            const int cbase = half * 64 + 32 * c;
+            if (cbase < 100) {  // warp-uniform
+              tmem_ld32(td + cbase, r);
+              tmem_ld_wait();
+              if (live) {
 #pragma unroll
-              for (int q = 0; q < 8; ++q) {
-                const int col = 32 * c + 4 * q;
-                if (col < 100) {
-                  float4 o;
-                  o.x = sigmoid_fast(__uint_as_float(r[4 * q + 0]) + P[P_BH + col + 0]);
-                  o.y = sigmoid_fast(__uint_as_float(r[4 * q + 1]) + P[P_BH + col + 1]);
-                  o.z = sigmoid_fast(__uint_as_float(r[4 * q + 2]) + P[P_BH + col + 2]);
-                  o.w = sigmoid_fast(__uint_as_float(r[4 * q + 3]) + P[P_BH + col + 3]);
-                  *reinterpret_cast<float4*>(dst + col) = o;
+                for (int q = 0; q < 8; ++q) {
+                  const int col = cbase + 4 * q;
+                  if (col < 100) {
+                    float4 o;
+                    o.x = sigmoid_fast(__uint_as_float(r[4 * q + 0]));
+                    o.y = sigmoid_fast(__uint_as_float(r[4 * q + 1]));
+                    o.z = sigmoid_fast(__uint_as_float(r[4 * q + 2]));
+                    o.w = sigmoid_fast(__uint_as_float(r[4 * q + 3]));
+                    *reinterpret_cast<float4*>(dst + col) = o;
+                  }
                 }
               }
             }
@@ -342,7 +388,7 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  if (warp == 5) tmem_dealloc(tmem_base, 512);
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
 }
 
 }  // namespace
@@ -355,15 +401,16 @@ bool umma_decoder_supported(const asb_model* m) {
   return m->precision == ASB_PRECISION_FAST && m->D == 50 && m->H == kH;
 }
 
-static int pack_mat(const float* src, float* dst, int n_src, int row0, int n_pad, int K, cudaStream_t st) {
+static int pack_mat(const float* src, const float* scale, float* dst, int n_src, int row0, int n_pad, int K,
+                    cudaStream_t st) {
   const int n = n_src * K;
-  pack_umma_kernel<<<(n + 255) / 256, 256, 0, st>>>(src, dst, n_src, row0, n_pad, K);
+  pack_umma_kernel<<<(n + 255) / 256, 256, 0, st>>>(src, scale, dst, n_src, row0, n_pad, K);
   ASB_CHECK_LAUNCH("pack_umma_kernel");
   return ASB_OK;
 }
-static int copy_vec(const float* src, float* dst, int n, cudaStream_t st) {
-  copy_vec_kernel<<<(n + 255) / 256, 256, 0, st>>>(src, dst, n);
-  ASB_CHECK_LAUNCH("copy_vec_kernel");
+static int fold_bias(const float* W, const float* beta, const float* b, float* dst, int N, int K, cudaStream_t st) {
+  fold_bias_kernel<<<(N + 127) / 128, 128, 0, st>>>(W, beta, b, dst, N, K);
+  ASB_CHECK_LAUNCH("fold_bias_kernel");
   return ASB_OK;
 }
 
@@ -377,28 +424,23 @@ int pack_umma_image(asb_model* m, const asb_weights* s, cudaStream_t st) {
   float* img = m->w.umma_image;
   const size_t total = umma_image_floats(m->N);
   ASB_TRY(check_cuda(cudaMemsetAsync(img, 0, total * sizeof(float), st), "pack_umma_image: memset"));
-  ASB_TRY(copy_vec(s->linear_b, img, kH, st));
-  ASB_TRY(pack_mat(s->linear_w, img + kLinParams, kH, 0, kH, 2 * kH, st));
+  ASB_TRY(fold_bias(nullptr, nullptr, s->linear_b, img, kH, 0, st));
+  ASB_TRY(pack_mat(s->linear_w, nullptr, img + kLinParams, kH, 0, kH, 2 * kH, st));
   const int D = m->D;
   for (int i = 0; i < m->N; ++i) {
     float* blk = img + kLinBlock + (size_t)i * kArtBlock;
-    ASB_TRY(copy_vec(s->ln0_w[i], blk + P_LN0_G, kH, st));
-    ASB_TRY(copy_vec(s->ln0_b[i], blk + P_LN0_B, kH, st));
-    ASB_TRY(copy_vec(s->fc1_b[i], blk + P_B1, kFc, st));
-    ASB_TRY(copy_vec(s->ln1_w[i], blk + P_LN1_G, kFc, st));
-    ASB_TRY(copy_vec(s->ln1_b[i], blk + P_LN1_B, kFc, st));
-    ASB_TRY(copy_vec(s->fc2_b[i], blk + P_B2, kFc, st));
-    ASB_TRY(copy_vec(s->ln2_w[i], blk + P_LN2_G, kFc, st));
-    ASB_TRY(copy_vec(s->ln2_b[i], blk + P_LN2_B, kFc, st));
-    ASB_TRY(copy_vec(s->xh_b[i], blk + P_BH, D, st));
-    ASB_TRY(copy_vec(s->yh_b[i], blk + P_BH + D, D, st));
+    // LayerNorm affines folded forward: W' = W diag(gamma), b' = b + W beta   (models.py:11-21)
+    ASB_TRY(fold_bias(s->fc1_w[i], s->ln0_b[i], s->fc1_b[i], blk + P_B1, kFc, kH, st));
+    ASB_TRY(fold_bias(s->fc2_w[i], s->ln1_b[i], s->fc2_b[i], blk + P_B2, kFc, kFc, st));
+    ASB_TRY(fold_bias(s->xh_w[i], s->ln2_b[i], s->xh_b[i], blk + P_BH, D, kFc, st));
+    ASB_TRY(fold_bias(s->yh_w[i], s->ln2_b[i], s->yh_b[i], blk + P_BH + D, D, kFc, st));
     float* w1 = blk + kArtParams;
     float* w2 = w1 + 4 * kFcChunk;
     float* wh = w2 + 8 * kFcChunk;
-    ASB_TRY(pack_mat(s->fc1_w[i], w1, kFc, 0, kFc, kH, st));
-    ASB_TRY(pack_mat(s->fc2_w[i], w2, kFc, 0, kFc, kFc, st));
-    ASB_TRY(pack_mat(s->xh_w[i], wh, D, 0, kHeadN, kFc, st));
-    ASB_TRY(pack_mat(s->yh_w[i], wh, D, D, kHeadN, kFc, st));
+    ASB_TRY(pack_mat(s->fc1_w[i], s->ln0_w[i], w1, kFc, 0, kFc, kH, st));
+    ASB_TRY(pack_mat(s->fc2_w[i], s->ln1_w[i], w2, kFc, 0, kFc, kFc, st));
+    ASB_TRY(pack_mat(s->xh_w[i], s->ln2_w[i], wh, D, 0, kHeadN, kFc, st));
+    ASB_TRY(pack_mat(s->yh_w[i], s->ln2_w[i], wh, D, D, kHeadN, kFc, st));
   }
   return ASB_OK;
 }
@@ -419,7 +461,7 @@ int launch_decoder_umma(const asb_model* m, const float* rnn_out, float* out, in
     const int n_groups = (m->N + g - 1) / g;
     const long long units = (long long)n_tiles * n_groups;
     const double waves = double((units + sms - 1) / sms);
-    const double cost = waves * (3000.0 + g * 14000.0);
+    const double cost = waves * (4500.0 + g * 12500.0);
     if (cost < best_cost - 1e-9) {
       best_cost = cost;
       best_g = g;
