@@ -88,3 +88,51 @@ def inject_upper_incisor(x):
 def tv_frames(n_frames, seed=0):
     """(F, 11, 2, 50) contour sets with the upper incisor in place."""
     return inject_upper_incisor(contours(n_frames, 10, 50, seed))
+
+
+# ---- area-function inputs (SURVEY.md 8d) ---------------------------------------------------
+# Default grid of the synthetic area-function workload: build_semipolar_grid((0.5, 0.5), 0, 0,
+# 0.01, pi / 36) -> 117 lines (50 larynx + 17 polar + 50 mouth, area_function.py:83-108).
+AREA_GRID_ARGS = dict(center=(0.5, 0.5), theta_rad=0.0, omega_rad=0.0, linear_step=0.01,
+                      polar_step_rad=math.pi / 36)
+_MOUTH_LEN, _ARC_LEN, _LARYNX_LEN = 0.47, 0.22, 0.47
+
+
+def _tract_path(u, rho, center=(0.5, 0.5)):
+    """Point at path coordinate u and distance rho from the grid's internal side: mouth section
+    (lines hanging from y = cy), quarter fan around the centre, larynx section (lines leaving
+    x = cx); follows the geometry of area_function.py:44-79 for theta = omega = 0."""
+    cx, cy = center
+    a = (_MOUTH_LEN - u).clamp(min=0.0)
+    phi = ((u - _MOUTH_LEN) / _ARC_LEN).clamp(0.0, 1.0) * (math.pi / 2)
+    b = (u - _MOUTH_LEN - _ARC_LEN).clamp(min=0.0)
+    x = cx - a + rho * torch.sin(phi)
+    y = cy - rho * torch.cos(phi) + b
+    return x, y
+
+
+def walls(n_frames, n_points=50, seed=0, noise=0.0005):
+    """Internal and external vocal-tract walls, two (F, n_points, 2) fp32 tensors: a smooth open
+    curve through the grid region at depth rho(u) = U(0.10,0.16) + U(0.01,0.04) sin(...), the
+    external wall offset outward by U(0.02,0.05) +- 0.01 (so 0.01..0.06), both ends of each wall
+    trimmed independently by U(0, 0.08) so that some grid lines meet only one wall, plus
+    N(0, noise^2)."""
+    g = torch.Generator().manual_seed(seed)
+    F = n_frames
+    total = _MOUTH_LEN + _ARC_LEN + _LARYNX_LEN
+    r = lambda lo, hi: lo + (hi - lo) * torch.rand(F, 1, generator=g, dtype=torch.float64)
+    rho0, amp, freq, ph = r(0.10, 0.16), r(0.01, 0.04), r(0.5, 2.0), r(0.0, 2 * math.pi)
+    off0, oamp, ofreq, oph = r(0.02, 0.05), r(0.0, 0.01), r(0.5, 3.0), r(0.0, 2 * math.pi)
+    k = torch.arange(n_points, dtype=torch.float64).view(1, -1) / (n_points - 1)
+    out = []
+    for is_ext in (False, True):
+        u0, u1 = r(0.0, 0.08), total - r(0.0, 0.08)
+        u = u0 + (u1 - u0) * k
+        rho = rho0 + amp * torch.sin(2 * math.pi * freq * u / total + ph)
+        if is_ext:
+            rho = rho + off0 + oamp * torch.sin(2 * math.pi * ofreq * u / total + oph)
+        x, y = _tract_path(u, rho)
+        pts = torch.stack([x, y], dim=-1)
+        pts = pts + noise * torch.randn(pts.shape, generator=g, dtype=torch.float64)
+        out.append(pts.to(torch.float32).contiguous())
+    return out[0], out[1]

@@ -13,10 +13,15 @@ relative to the reference checkout of vribeiro1/artspeech):
                          (stock torch CPU ops; fp32 or fp64) and a from-the-
                          equations GRU used to cross-check ``nn.GRU``.
 * ``oracle.geometry``  - P2CP, Euclidean, Pearson and tract variables.
-* ``oracle.area``      - NumPy fp64 restatement of ``area_function.py``.
-                         PARITY UNPINNED: the reference module cannot run
-                         (shapely / vt_tools absent, ``np.float`` crash) and
-                         has no caller or test in the reference.
+* ``oracle.area``      - NumPy fp64 restatement of ``area_function.py``;
+  ``oracle/area_c.c``    the same chain in plain C for batches (gcc, built by
+  ``oracle.build_c``     ``oracle.build_c`` into oracle/_build/).  Grid, mid_point,
+                         argmatrix and area_function are PINNED bit-exactly to
+                         the reference's own functions (tests/golden/area.npz);
+                         intersect_semipolar_grid and evenly_spaced_fx are
+                         PARITY UNPINNED: their arithmetic is inside shapely /
+                         GEOS and vt_tools, absent here, and the module has no
+                         caller, test or fixture in the reference.
 * ``oracle.reference_loader`` / ``oracle.make_golden`` - import the real
                          reference by file path (only where /root/reference
                          exists) to pin the restatements and to write
@@ -24,5 +29,6 @@ relative to the reference checkout of vribeiro1/artspeech):
 
 Parity status: model / P2CP / TV restatements are pinned against outputs of
 the unmodified reference run in the build container (tests/golden, script
-committed).  Area function: parity unpinned (see above).
+committed).  Area function: grid / area_function pinned, the two GEOS-backed functions
+unpinned (see above).
 """

@@ -122,9 +122,44 @@ def golden_tv():
           np.max(np.abs(val32 - val) / np.maximum(val, 1e-30)))
 
 
+def golden_area():
+    """The parts of area_function.py that run without GEOS: grid, mid_point, argmatrix, rotate and
+    area_function (a9, a11).  a10 / a12 need shapely and stay unpinned (oracle/area.py header)."""
+    import math
+    from oracle import area as oarea
+    af = ref.area_function()
+    grids = {}
+    cases = {"default": synthetic.AREA_GRID_ARGS,
+             "rotated": dict(center=(0.45, 0.55), theta_rad=0.2, omega_rad=-0.15, linear_step=0.02,
+                             polar_step_rad=math.pi / 30)}
+    for name, kw in cases.items():
+        grids[name] = af.build_semipolar_grid(np.array(kw["center"]), kw["theta_rad"], kw["omega_rad"],
+                                              kw["linear_step"], kw["polar_step_rad"])
+    # wall pairs for area_function(): intersections produced by the restatement on synthetic walls
+    wi, we = synthetic.walls(3, seed=11)
+    out = {}
+    for f in range(3):
+        ii, ee = oarea.intersect_semipolar_grid(wi[f].numpy(), we[f].numpy(), grids["default"])
+        dists, fx = af.area_function(ii, ee)
+        dists_b, fx_b = af.area_function(ii, ee, alpha=2.5, beta=1.5)
+        out.update({f"int_{f}": ii, f"ext_{f}": ee, f"dists_{f}": dists, f"fx_{f}": fx,
+                    f"dists_b_{f}": dists_b, f"fx_b_{f}": fx_b})
+    rng = np.random.default_rng(3)
+    p = rng.random((16, 2, 2))
+    mids = np.array([af.mid_point(a, b) for a, b in p])
+    mtx = rng.random((5, 7)); mtx[3, 2] = mtx[1, 4] = -1.0   # tie: first in row-major order wins
+    arg = np.array([af.argmatrix(mtx, "min"), af.argmatrix(mtx, "max")])
+    rot = np.array([af.rotate(np.array([0.3, -0.4]), a) for a in (0.0, 0.7, -2.1)])
+    np.savez_compressed(os.path.join(GOLDEN, "area.npz"), grid_default=grids["default"],
+                        grid_rotated=grids["rotated"], wall_int=wi.numpy(), wall_ext=we.numpy(),
+                        mid_in=p, mid_out=mids, arg_in=mtx, arg_out=arg, rot_out=rot, **out)
+    print("area: grids", grids["default"].shape, grids["rotated"].shape, "K", [len(out[f"fx_{f}"]) for f in range(3)])
+
+
 if __name__ == "__main__":
     assert ref.available(), "reference checkout not found"
     os.makedirs(GOLDEN, exist_ok=True)
     golden_model()
     golden_p2cp()
     golden_tv()
+    golden_area()

@@ -59,3 +59,35 @@ def tract_variables():
     """reference tract_variables.py with the vt_tools constant stub"""
     _stub_vt_tools()
     return _load("_ref_tract_variables", "tract_variables.py")
+
+
+def area_function():
+    """reference area_function.py with its absent imports stubbed:
+    ``funcy.lmap`` = list(map(...)); ``shapely.geometry`` = empty placeholder classes (so only the
+    functions that never touch GEOS can run: rotate, build_semipolar_grid, mid_point, argmatrix,
+    area_function); ``vt_tools.metrics.euclidean`` = sqrt(dx^2 + dy^2) (its published definition,
+    the package itself is un-vendored); ``np.float`` aliased to ``float`` for :130 (NumPy >= 1.24)."""
+    import numpy as np
+    _stub_vt_tools()
+    vt = sys.modules["vt_tools"]
+    if "vt_tools.metrics" not in sys.modules:
+        vm = types.ModuleType("vt_tools.metrics")
+        vm.euclidean = lambda u, v: np.sqrt((u[0] - v[0]) ** 2 + (u[1] - v[1]) ** 2)
+        vm.distance_matrix = None  # only used next to GEOS calls, which cannot run here
+        vt.metrics = vm
+        sys.modules["vt_tools.metrics"] = vm
+    if "funcy" not in sys.modules:
+        fy = types.ModuleType("funcy")
+        fy.lmap = lambda fn, seq: list(map(fn, seq))
+        sys.modules["funcy"] = fy
+    if "shapely" not in sys.modules:
+        sh = types.ModuleType("shapely")
+        sg = types.ModuleType("shapely.geometry")
+        sg.LineString = type("LineString", (), {})
+        sg.Point = type("Point", (), {})
+        sh.geometry = sg
+        sys.modules["shapely"] = sh
+        sys.modules["shapely.geometry"] = sg
+    if not hasattr(np, "float"):
+        np.float = float
+    return _load("_ref_area_function", "area_function.py")
