@@ -51,6 +51,14 @@ SIGNATURES = {
     "asb_tract_variables_ref": (ctypes.c_int, [_c_f32p, ctypes.c_int64, ctypes.c_int,
                                                ctypes.POINTER(ctypes.c_int32), _c_f32p, ctypes.c_int64, _c_f32p,
                                                ctypes.c_void_p, _c_f32p, ctypes.c_void_p]),
+    "asb_area_function": (ctypes.c_int, [_c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_int, ctypes.c_void_p,
+                                         ctypes.c_int, ctypes.c_double, ctypes.c_double, ctypes.c_int, _c_f32p,
+                                         ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
+    "asb_area_from_pairs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int,
+                                           ctypes.c_double, ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p,
+                                           ctypes.c_void_p]),
+    "asb_evenly_spaced_fx": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int,
+                                            ctypes.c_int, _c_f32p, ctypes.c_void_p]),
     "asb_model_forward_resident": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                                   ctypes.POINTER(ctypes.c_int32), ctypes.c_void_p, ctypes.c_int,
                                                   _c_f32p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]),

@@ -89,6 +89,33 @@ ASB_API int asb_tract_variables_ref(const float* sets_ptr, int64_t sets, int n_a
                             int64_t upper_incisor_stride, float* val, int32_t* idx, float* poc,
                             void* stream);
 
+/* intersect_semipolar_grid -> area_function -> evenly_spaced_fx, area_function.py:175-223,
+ * :124-142 (mid_point :113-121), :145-159, for `frames` independent frames.
+ * walls_int / walls_ext: (frames, n_wall, 2) fp32 interleaved (x, y) wall polylines, 2 <= n_wall <= 64;
+ * grid_ends: (n_lines, 2, 2) fp64 DEVICE array, [line][internal|external end][x|y] = first and last
+ * sample of every line of build_semipolar_grid (:31-110), 1 <= n_lines <= 128.
+ * xfx (frames, 2, n_samples) fp32 = [linspace(0, total mid-line length, n_samples); alpha * r^beta
+ * interpolated there] (NaN when fewer than two grid lines touch a wall); K (frames) int32 = number
+ * of grid lines that touch a wall.  Optional (NULL to skip): pts (frames, n_lines, 2, 2) fp64 =
+ * the K selected [internal|external] intersection points in grid order, zero padded (what
+ * intersect_semipolar_grid returns); lines (frames, n_lines) int32 = their grid-line indices, -1 padded.
+ * Decisions (which lines touch, which intersection is kept) are those of fp64 arithmetic. */
+ASB_API int asb_area_function(const float* walls_int, const float* walls_ext, int64_t frames, int n_wall,
+                      const double* grid_ends, int n_lines, double alpha, double beta, int n_samples,
+                      float* xfx, int32_t* K, double* pts, int32_t* lines, void* stream);
+
+/* area_function alone, area_function.py:124-142: already paired wall points int_pts / ext_pts
+ * (frames, K, 2) fp64 -> dists (frames, K) = cumulative distance between successive mid-points
+ * (mid_point :113-121), fx (frames, K) = alpha * (|int - ext| / 2)^beta, both fp64. */
+ASB_API int asb_area_from_pairs(const double* int_pts, const double* ext_pts, int64_t frames, int K,
+                        double alpha, double beta, double* dists, double* fx, void* stream);
+
+/* evenly_spaced_fx alone, area_function.py:145-159: polylines (x, fx) of K points each (x
+ * non-decreasing), fp64 -> out (frames, 2, n_samples) fp32 = [np.linspace(x[0], x[K-1], n_samples);
+ * the piecewise-linear fx there]. */
+ASB_API int asb_evenly_spaced_fx(const double* x, const double* fx, int64_t frames, int K, int n_samples,
+                         float* out, void* stream);
+
 /* Length-masked aggregation of one batch's per-frame metrics, as run_test does per sentence
  * (evaluation.py:68-84,142-156): p2cp (B,T,n_art), tv_pred/tv_target (B,T,4) fp32, lengths_dev (B)
  * DEVICE int32.  scratch: B*(n_art+12) doubles.  acc (n_art+14 doubles) is OVERWRITTEN with

@@ -187,3 +187,16 @@ def test_c_oracle_threads_and_degenerate_frames():
         assert np.array_equal(r1[k], r4[k], equal_nan=True)
     assert r1["K"][3] == 0 and np.all(np.isnan(r1["xfx"][3]))
     assert r1["K"].max() <= 117 and np.all(np.isfinite(r1["xfx"][np.arange(64) != 3]))
+
+
+def test_product_host_helpers_match_reference(ga):
+    """The package's host-side grid builder / helpers (configuration, no CUDA involved)."""
+    from artspeech_b200 import area_function as af
+    assert np.array_equal(af.build_semipolar_grid(**synthetic.AREA_GRID_ARGS), ga["grid_default"])
+    assert np.array_equal(af.build_semipolar_grid(**ROTATED), ga["grid_rotated"])
+    assert np.array_equal(np.array([af.mid_point(a, b) for a, b in ga["mid_in"]]), ga["mid_out"])
+    assert np.array_equal(np.array([af.argmatrix(ga["arg_in"], "min"), af.argmatrix(ga["arg_in"], "max")]),
+                          ga["arg_out"])
+    assert np.array_equal(np.array([af.rotate(np.array([0.3, -0.4]), a) for a in (0.0, 0.7, -2.1)]), ga["rot_out"])
+    ends = af.grid_endpoints(ga["grid_rotated"])
+    assert np.array_equal(ends, oarea.grid_endpoints(**ROTATED))

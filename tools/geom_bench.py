@@ -8,6 +8,7 @@ sys.path.insert(0, ".")
 from artspeech_b200 import _lib, synthetic  # noqa: E402
 import artspeech_b200.metrics as M  # noqa: E402
 import artspeech_b200.tract_variables as TV  # noqa: E402
+import artspeech_b200.area_function as AF  # noqa: E402
 
 
 def timeit(fn, iters=10, warm=3):
@@ -39,6 +40,12 @@ def main():
                                 TV.tract_variables_batch(tgt, synthetic.TV_ARTICULATORS)))
     res["tv_ms"] = med; res["tv_frames_per_s"] = F / med * 1e3
     res["tv_GBs"] = F * 5024 / med * 1e-6
+    wi, we = synthetic.walls(4096, seed=2)
+    wi = wi.cuda().repeat(reps, 1, 1).contiguous(); we = we.cuda().repeat(reps, 1, 1).contiguous()
+    grid = AF.DeviceGrid(AF.build_semipolar_grid(**synthetic.AREA_GRID_ARGS), wi.device)
+    med, best = timeit(lambda: AF.area_function_batch(wi, we, grid))
+    res["area_ms"] = med; res["area_frames_per_s"] = F / med * 1e3
+    res["area_GBs"] = F * 2404 / med * 1e-6
     res["launches"] = _lib.launch_count()
     print(json.dumps(res))
 
