@@ -31,6 +31,9 @@ namespace {
 
 using namespace asb;
 
+#ifndef ASB_AREA_MINB
+#define ASB_AREA_MINB 2
+#endif
 constexpr int kWarps = 8;
 constexpr int kMaxWall = 64;    // vertices per wall (one 64-bit sign mask)
 constexpr int kRounds = 4;      // grid lines per lane
@@ -46,26 +49,34 @@ __device__ __forceinline__ double dist64(double ax, double ay, double bx, double
   return __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
 }
 
-// Shared point of grid line g0g1 and wall segment k (vertices k, k+1), if any.
-__device__ __forceinline__ bool crossing(double g0x, double g0y, double g1x, double g1y, const float2* wall, int k,
+__device__ __forceinline__ double dist2_64(double ax, double ay, double bx, double by) {
+  const double dx = __dsub_rn(ax, bx), dy = __dsub_rn(ay, by);
+  return __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+}
+
+// Shared point of grid line g0g1 and wall segment k (vertices k, k+1), if any.  Branch-free: all
+// four orientations and the division are always evaluated (candidates come from sign changes, so
+// the early-outs are rare) and the special cases are selects, which lets independent calls overlap.
+__device__ __forceinline__ bool crossing(double g0x, double g0y, double g1x, double g1y, const float4* wall, int k,
                                          double& px, double& py) {
-  const float2 a = wall[k], b = wall[k + 1];
-  const double ax = a.x, ay = a.y, bx = b.x, by = b.y;
+  const float4 a = wall[k], b = wall[k + 1];  // (x, x, y, y)
+  const double ax = a.x, ay = a.z, bx = b.x, by = b.z;
   const double d1 = orient64(g0x, g0y, g1x, g1y, ax, ay);
   const double d2 = orient64(g0x, g0y, g1x, g1y, bx, by);
-  if ((d1 > 0 && d2 > 0) || (d1 < 0 && d2 < 0)) return false;
   const double d3 = orient64(ax, ay, bx, by, g0x, g0y);
   const double d4 = orient64(ax, ay, bx, by, g1x, g1y);
-  if ((d3 > 0 && d4 > 0) || (d3 < 0 && d4 < 0)) return false;
-  if (d1 == 0 && d2 == 0 && d3 == 0 && d4 == 0) return false;  // collinear overlap contributes nothing
-  if (d1 == 0) { px = ax; py = ay; return true; }
-  if (d2 == 0) { px = bx; py = by; return true; }
-  if (d3 == 0) { px = g0x; py = g0y; return true; }
-  if (d4 == 0) { px = g1x; py = g1y; return true; }
+  const bool same12 = (d1 > 0 && d2 > 0) || (d1 < 0 && d2 < 0);
+  const bool same34 = (d3 > 0 && d4 > 0) || (d3 < 0 && d4 < 0);
+  const bool allz = d1 == 0 && d2 == 0 && d3 == 0 && d4 == 0;  // collinear overlap contributes nothing
   const double t = __ddiv_rn(d1, __dsub_rn(d1, d2));
   px = __dadd_rn(ax, __dmul_rn(t, __dsub_rn(bx, ax)));
   py = __dadd_rn(ay, __dmul_rn(t, __dsub_rn(by, ay)));
-  return true;
+  // touching: the exact end point, priority d1, d2, d3, d4 (lowest priority applied first)
+  if (d4 == 0) { px = g1x; py = g1y; }
+  if (d3 == 0) { px = g0x; py = g0y; }
+  if (d2 == 0) { px = bx; py = by; }
+  if (d1 == 0) { px = ax; py = ay; }
+  return !same12 && !same34 && !allz;
 }
 
 struct LineCoef {
@@ -73,35 +84,61 @@ struct LineCoef {
   float ma, mc;      // error-bound terms: |ex| + |ey| and |c|
 };
 
+// A wall vertex in shared memory, duplicated for the packed fp32x2 filter: (x, x, y, y).
+typedef float4 WallVtx;
+
 // Sign masks of the signed areas of every vertex of `wall` about the lane's kRounds lines.
 // neg[r] bit k: area < 0; zer[r] bit k: area == 0 (exact fp64 decision for uncertain vertices).
-__device__ __forceinline__ void wall_masks(const float2* wall, int n_wall, const LineCoef (&lc)[kRounds], int lane,
+// Lines are handled two per instruction (FFMA2), vertices two per FMNMX3.
+__device__ __forceinline__ void wall_masks(const WallVtx* wall, int n_wall, const LineCoef (&lc)[kRounds], int lane,
                                            const double* sgrid, float wmax, u64 (&neg)[kRounds], u64 (&zer)[kRounds]) {
+  static_assert(kRounds == 4, "the packed filter handles the lane's lines as two pairs");
+  // area = ex * y + (-(ey * x + c)) = fma(ex, y, fma(-ey, x, -c))
+  const f32x2 ex01 = pack2(lc[0].ex, lc[1].ex), ex23 = pack2(lc[2].ex, lc[3].ex);
+  const f32x2 ney01 = pack2(-lc[0].ey, -lc[1].ey), ney23 = pack2(-lc[2].ey, -lc[3].ey);
+  const f32x2 nc01 = pack2(-lc[0].c, -lc[1].c), nc23 = pack2(-lc[2].c, -lc[3].c);
   unsigned lo[kRounds], hi[kRounds];
   float m[kRounds];
 #pragma unroll
   for (int r = 0; r < kRounds; ++r) { lo[r] = 0u; hi[r] = 0u; m[r] = FLT_MAX; }
+
+  auto vertex_pair = [&](int k, unsigned (&acc)[kRounds]) {
+    const ulonglong2 wa = *reinterpret_cast<const ulonglong2*>(wall + k);      // (x,x), (y,y)
+    const ulonglong2 wb = *reinterpret_cast<const ulonglong2*>(wall + k + 1);
+    float a[kRounds], b[kRounds];
+    unpack2(fma2(ex01, wa.y, fma2(ney01, wa.x, nc01)), a[0], a[1]);
+    unpack2(fma2(ex23, wa.y, fma2(ney23, wa.x, nc23)), a[2], a[3]);
+    unpack2(fma2(ex01, wb.y, fma2(ney01, wb.x, nc01)), b[0], b[1]);
+    unpack2(fma2(ex23, wb.y, fma2(ney23, wb.x, nc23)), b[2], b[3]);
+#pragma unroll
+    for (int r = 0; r < kRounds; ++r) {
+      m[r] = fminf(fminf(m[r], fabsf(a[r])), fabsf(b[r]));
+      acc[r] = __funnelshift_l(__float_as_uint(a[r]), acc[r], 1);
+      acc[r] = __funnelshift_l(__float_as_uint(b[r]), acc[r], 1);
+    }
+  };
+  auto vertex_one = [&](int k, unsigned (&acc)[kRounds]) {
+    const ulonglong2 wa = *reinterpret_cast<const ulonglong2*>(wall + k);
+    float a[kRounds];
+    unpack2(fma2(ex01, wa.y, fma2(ney01, wa.x, nc01)), a[0], a[1]);
+    unpack2(fma2(ex23, wa.y, fma2(ney23, wa.x, nc23)), a[2], a[3]);
+#pragma unroll
+    for (int r = 0; r < kRounds; ++r) {
+      m[r] = fminf(m[r], fabsf(a[r]));
+      acc[r] = __funnelshift_l(__float_as_uint(a[r]), acc[r], 1);
+    }
+  };
+
   const int n0 = n_wall < 32 ? n_wall : 32;
-#pragma unroll 8
-  for (int k = 0; k < n0; ++k) {
-    const float2 w = wall[k];
-#pragma unroll
-    for (int r = 0; r < kRounds; ++r) {
-      const float det = __fmaf_rn(lc[r].ex, w.y, -__fmaf_rn(lc[r].ey, w.x, lc[r].c));
-      m[r] = fminf(m[r], fabsf(det));
-      lo[r] = __funnelshift_l(__float_as_uint(det), lo[r], 1);
-    }
-  }
-#pragma unroll 6
-  for (int k = 32; k < n_wall; ++k) {
-    const float2 w = wall[k];
-#pragma unroll
-    for (int r = 0; r < kRounds; ++r) {
-      const float det = __fmaf_rn(lc[r].ex, w.y, -__fmaf_rn(lc[r].ey, w.x, lc[r].c));
-      m[r] = fminf(m[r], fabsf(det));
-      hi[r] = __funnelshift_l(__float_as_uint(det), hi[r], 1);
-    }
-  }
+  int k = 0;
+#pragma unroll 4
+  for (; k + 1 < n0; k += 2) vertex_pair(k, lo);
+  if (k < n0) vertex_one(k, lo);
+  k = 32;
+#pragma unroll 3
+  for (; k + 1 < n_wall; k += 2) vertex_pair(k, hi);
+  if (k < n_wall) vertex_one(k, hi);
+
   const int n1 = n_wall - n0;
 #pragma unroll
   for (int r = 0; r < kRounds; ++r) {
@@ -115,12 +152,12 @@ __device__ __forceinline__ void wall_masks(const float2* wall, int n_wall, const
       // rare: some vertex is too close to this line for fp32; decide those in fp64
       const double* g = sgrid + 4 * (r * 32 + lane);
       const double g0x = g[0], g0y = g[1], g1x = g[2], g1y = g[3];
-      for (int k = 0; k < n_wall; ++k) {
-        const float2 w = wall[k];
-        const float det = __fmaf_rn(lc[r].ex, w.y, -__fmaf_rn(lc[r].ey, w.x, lc[r].c));
+      for (int q = 0; q < n_wall; ++q) {
+        const WallVtx w = wall[q];
+        const float det = __fmaf_rn(lc[r].ex, w.z, __fmaf_rn(-lc[r].ey, w.x, -lc[r].c));
         if (fabsf(det) < bound) {
-          const double d = orient64(g0x, g0y, g1x, g1y, (double)w.x, (double)w.y);
-          const u64 bit = 1ull << k;
+          const double d = orient64(g0x, g0y, g1x, g1y, (double)w.x, (double)w.z);
+          const u64 bit = 1ull << q;
           neg[r] = d < 0 ? (neg[r] | bit) : (neg[r] & ~bit);
           zer[r] = d == 0 ? (zer[r] | bit) : zer[r];
         }
@@ -135,28 +172,59 @@ __device__ __forceinline__ u64 candidates(u64 neg, u64 zer, int n_wall) {
 }
 
 // evenly_spaced_fx (:145-159): the polyline (x, fx) of K >= 2 points evaluated at
-// np.linspace(x[0], x[K-1], n_samples); out (2, n_samples) fp32.  One warp.
-__device__ __forceinline__ void resample(const double* x, const double* fx, int K, int n_samples, float* out,
-                                         int lane) {
+// np.linspace(x[0], x[K-1], n_samples); out (2, n_samples) fp32.  One warp.  A lane takes kPerLane
+// consecutive abscissae: one binary search for the first, then the segment index only advances.
+// The ordinates go through `stage` (kStage floats of shared memory) so that the global writes are
+// coalesced; the abscissae are recomputed by the writing lane.
+constexpr int kPerLane = 8;
+constexpr int kStage = 32 * kPerLane;
+
+template <bool kSlope>
+__device__ __forceinline__ void resample(const double* x, const double* fx, const double* slope, int K,
+                                         int n_samples, float* out, int lane, float* stage) {
   const double x0 = x[0], x1 = x[K - 1];
   const double step = __ddiv_rn(__dsub_rn(x1, x0), (double)(n_samples - 1));
-  for (int s = lane; s < n_samples; s += 32) {
-    const double xv = (s == n_samples - 1) ? x1 : __dadd_rn(x0, __dmul_rn((double)s, step));
-    // first segment k with x[k] <= xv <= x[k+1]  ==  smallest k with x[k+1] >= xv
-    int lo = 0, hi = K - 2;
-    while (lo < hi) {
-      const int mid = (lo + hi) >> 1;
-      if (x[mid + 1] >= xv) hi = mid; else lo = mid + 1;
+  const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int base = 0; base < n_samples; base += kStage) {
+    const int s0 = base + lane * kPerLane;
+    int seg = -1;
+#pragma unroll 1
+    for (int i = 0; i < kPerLane; ++i) {
+      const int s = s0 + i;
+      if (s >= n_samples) break;
+      const double xv = (s == n_samples - 1) ? x1 : __dadd_rn(x0, __dmul_rn((double)s, step));
+      // first segment k with x[k] <= xv <= x[k+1]  ==  smallest k with x[k+1] >= xv
+      if (seg < 0) {
+        int lo = 0, hi = K - 2;
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (x[mid + 1] >= xv) hi = mid; else lo = mid + 1;
+        }
+        seg = lo;
+      } else {
+        while (seg < K - 2 && x[seg + 1] < xv) ++seg;
+      }
+      const double da = x[seg], db = x[seg + 1];
+      double yv;
+      if (db == da || xv == da) yv = fx[seg];
+      else if (xv == db) yv = fx[seg + 1];
+      else if (kSlope)
+        yv = __dadd_rn(fx[seg], __dmul_rn(__dsub_rn(xv, da), slope[seg]));
+      else
+        yv = __dadd_rn(fx[seg], __dmul_rn(__ddiv_rn(__dsub_rn(xv, da), __dsub_rn(db, da)),
+                                          __dsub_rn(fx[seg + 1], fx[seg])));
+      if (!(da <= xv && xv <= db)) yv = qnan;  // outside the polyline
+      const int q = lane * kPerLane + i;
+      stage[q ^ (lane >> 2)] = (float)yv;     // xor swizzle: lanes 8 floats apart land in different banks
     }
-    const double da = x[lo], db = x[lo + 1];
-    double yv;
-    if (db == da || xv == da) yv = fx[lo];
-    else if (xv == db) yv = fx[lo + 1];
-    else
-      yv = __dadd_rn(fx[lo], __dmul_rn(__ddiv_rn(__dsub_rn(xv, da), __dsub_rn(db, da)), __dsub_rn(fx[lo + 1], fx[lo])));
-    if (!(da <= xv && xv <= db)) yv = __longlong_as_double(0x7ff8000000000000LL);  // outside the polyline
-    out[s] = (float)xv;
-    out[n_samples + s] = (float)yv;
+    __syncwarp();
+    for (int q = lane; q < kStage && base + q < n_samples; q += 32) {
+      const int s = base + q;
+      const double xv = (s == n_samples - 1) ? x1 : __dadd_rn(x0, __dmul_rn((double)s, step));
+      out[s] = (float)xv;
+      out[n_samples + s] = stage[q ^ ((q / kPerLane) >> 2)];
+    }
+    __syncwarp();
   }
 }
 
@@ -175,11 +243,10 @@ struct AreaArgs {
   int* lines;
 };
 
-__global__ void __launch_bounds__(kWarps * 32) area_function_kernel(const AreaArgs p) {
+__global__ void __launch_bounds__(kWarps * 32, ASB_AREA_MINB) area_function_kernel(const AreaArgs p) {
   __shared__ __align__(16) double sgrid[kMaxLines * 4];
-  __shared__ __align__(16) float2 swall[kWarps][2][kMaxWall];
+  __shared__ __align__(16) WallVtx swall[kWarps][2][kMaxWall];
   __shared__ __align__(16) double smid[kWarps][2][kMaxLines];
-  __shared__ __align__(16) double sdist[kWarps][kMaxLines];
   __shared__ __align__(16) double sfx[kWarps][kMaxLines];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -204,11 +271,11 @@ __global__ void __launch_bounds__(kWarps * 32) area_function_kernel(const AreaAr
     }
   }
 
-  float2* wI = swall[warp][0];
-  float2* wE = swall[warp][1];
+  WallVtx* wI = swall[warp][0];
+  WallVtx* wE = swall[warp][1];
   double* mx = smid[warp][0];
   double* my = smid[warp][1];
-  double* dist = sdist[warp];
+  double* dist = mx;  // the cumulative distances overwrite the mid-point abscissae once those are consumed
   double* fxs = sfx[warp];
   const int nw = p.n_wall;
   const unsigned lt_mask = (1u << lane) - 1u;
@@ -220,7 +287,7 @@ __global__ void __launch_bounds__(kWarps * 32) area_function_kernel(const AreaAr
       const int which = q >= nw;
       const int k = q - which * nw;
       const float2 v = __ldg((which ? p.we : p.wi) + f * nw + k);
-      swall[warp][which][k] = v;
+      swall[warp][which][k] = make_float4(v.x, v.x, v.y, v.y);
       wmax = fmaxf(wmax, fmaxf(fabsf(v.x), fabsf(v.y)));
     }
 #pragma unroll
@@ -232,7 +299,7 @@ __global__ void __launch_bounds__(kWarps * 32) area_function_kernel(const AreaAr
     wall_masks(wI, nw, lc, lane, sgrid, wmax, negI, zerI);
     wall_masks(wE, nw, lc, lane, sgrid, wmax, negE, zerE);
 
-    const double eFx = wE[0].x, eFy = wE[0].y, eLx = wE[nw - 1].x, eLy = wE[nw - 1].y;
+    const double eFx = wE[0].x, eFy = wE[0].z, eLx = wE[nw - 1].x, eLy = wE[nw - 1].z;
 
     // ---- 3./4. per line: intersections, selection, compaction
     int base = 0;
@@ -243,7 +310,33 @@ __global__ void __launch_bounds__(kWarps * 32) area_function_kernel(const AreaAr
       const u64 cE = candidates(negE[r], zerE[r], nw);
       bool anyI = false, anyE = false;
       double ix = 0, iy = 0, ox = 0, oy = 0;  // selected internal / external point
-      if (cI | cE) {
+      // Distances are only compared, so the selection works on squared distances.
+      const int nI = __popcll(cI), nE = __popcll(cE);
+      if (__all_sync(0xffffffffu, nI <= 1 && nE <= 1)) {
+        // fast path (the usual case): at most one candidate segment per wall on every lane's line;
+        // both intersections are evaluated side by side, everything else is selects
+        if (nI | nE) {
+          const double* g = sgrid + 4 * l;
+          const double g0x = g[0], g0y = g[1], g1x = g[2], g1y = g[3];
+          double px, py, qx, qy;
+          const bool okP = crossing(g0x, g0y, g1x, g1y, wI, nI ? __ffsll((long long)cI) - 1 : 0, px, py);
+          const bool okQ = crossing(g0x, g0y, g1x, g1y, wE, nE ? __ffsll((long long)cE) - 1 : 0, qx, qy);
+          anyI = nI && okP;
+          anyE = nE && okQ;
+          ix = px; iy = py; ox = qx; oy = qy;
+          if (anyI != anyE) {
+            // one wall only (:199-221): the met point against the ends of the EXTERNAL wall
+            const double mx_ = anyI ? px : qx, my_ = anyI ? py : qy;
+            const bool first = dist2_64(mx_, my_, eFx, eFy) <= dist2_64(mx_, my_, eLx, eLy);
+            if (anyI) {
+              ox = first ? eFx : eLx; oy = first ? eFy : eLy;
+            } else {
+              const WallVtx v = first ? wI[0] : wI[nw - 1];
+              ix = v.x; iy = v.z;
+            }
+          }
+        }
+      } else if (cI | cE) {
         const double* g = sgrid + 4 * l;
         const double g0x = g[0], g0y = g[1], g1x = g[2], g1y = g[3];
         double b1 = INFINITY, b2 = INFINITY;
@@ -257,7 +350,7 @@ __global__ void __launch_bounds__(kWarps * 32) area_function_kernel(const AreaAr
             double qx, qy;
             if (!crossing(g0x, g0y, g1x, g1y, wE, kj, qx, qy)) continue;
             anyE = true;
-            const double d = dist64(px, py, qx, qy);
+            const double d = dist2_64(px, py, qx, qy);
             if (d < b1) { b1 = d; ix = px; iy = py; }                          // rows = internal points
             if (d < b2 || (d == b2 && kj < j2)) { b2 = d; j2 = kj; ox = qx; oy = qy; }  // rows = external
           }
@@ -268,7 +361,7 @@ __global__ void __launch_bounds__(kWarps * 32) area_function_kernel(const AreaAr
           for (u64 ci = cI; ci; ci &= ci - 1) {
             double px, py;
             if (!crossing(g0x, g0y, g1x, g1y, wI, __ffsll((long long)ci) - 1, px, py)) continue;
-            const double dF = dist64(px, py, eFx, eFy), dL = dist64(px, py, eLx, eLy);
+            const double dF = dist2_64(px, py, eFx, eFy), dL = dist2_64(px, py, eLx, eLy);
             if (dF < best) { best = dF; ix = px; iy = py; ox = eFx; oy = eFy; }
             if (dL < best) { best = dL; ix = px; iy = py; ox = eLx; oy = eLy; }
           }
@@ -279,9 +372,9 @@ __global__ void __launch_bounds__(kWarps * 32) area_function_kernel(const AreaAr
             double qx, qy;
             if (!crossing(g0x, g0y, g1x, g1y, wE, __ffsll((long long)ce) - 1, qx, qy)) continue;
             anyE = true;
-            const double dF = dist64(qx, qy, eFx, eFy), dL = dist64(qx, qy, eLx, eLy);
-            if (dF < best) { best = dF; ox = qx; oy = qy; ix = wI[0].x; iy = wI[0].y; }
-            if (dL < best) { best = dL; ox = qx; oy = qy; ix = wI[nw - 1].x; iy = wI[nw - 1].y; }
+            const double dF = dist2_64(qx, qy, eFx, eFy), dL = dist2_64(qx, qy, eLx, eLy);
+            if (dF < best) { best = dF; ox = qx; oy = qy; ix = wI[0].x; iy = wI[0].z; }
+            if (dL < best) { best = dL; ox = qx; oy = qy; ix = wI[nw - 1].x; iy = wI[nw - 1].z; }
           }
         }
       }
@@ -292,8 +385,9 @@ __global__ void __launch_bounds__(kWarps * 32) area_function_kernel(const AreaAr
         // mid_point :113-121 and radius / alpha * r^beta :126-133
         mx[k] = __dadd_rn(fmin(ix, ox), __dmul_rn(fabs(__dsub_rn(ix, ox)), 0.5));
         my[k] = __dadd_rn(fmin(iy, oy), __dmul_rn(fabs(__dsub_rn(iy, oy)), 0.5));
-        const double radius = __dmul_rn(dist64(ix, iy, ox, oy), 0.5);
-        fxs[k] = __dmul_rn(p.alpha, p.beta == 2.0 ? __dmul_rn(radius, radius) : pow(radius, p.beta));
+        const double d2 = dist2_64(ix, iy, ox, oy);   // (|int - ext| / 2)^2 = d2 / 4: no square root for beta = 2
+        fxs[k] = __dmul_rn(p.alpha, p.beta == 2.0 ? __dmul_rn(d2, 0.25)
+                                                  : pow(__dmul_rn(__dsqrt_rn(d2), 0.5), p.beta));
         if (p.pts) {
           double* o = p.pts + (f * p.n_lines + k) * 4;
           reinterpret_cast<double2*>(o)[0] = make_double2(ix, iy);
@@ -337,6 +431,7 @@ __global__ void __launch_bounds__(kWarps * 32) area_function_kernel(const AreaAr
     }
     double excl = __shfl_up_sync(0xffffffffu, incl, 1);
     if (lane == 0) excl = 0.0;
+    __syncwarp();  // every lane has read its mid-points; dist aliases mx
 #pragma unroll
     for (int q = 0; q < kRounds; ++q) {
       const int k = lane * kRounds + q;
@@ -344,8 +439,19 @@ __global__ void __launch_bounds__(kWarps * 32) area_function_kernel(const AreaAr
     }
     __syncwarp();
 
-    // ---- 5. evenly_spaced_fx (:145-159)
-    resample(dist, fxs, K, p.n_samples, out, lane);
+    // ---- 5. evenly_spaced_fx (:145-159); the walls are consumed, their shared memory holds the
+    // per-segment slopes (one division per segment instead of one per sample) and the staging row
+    double* slope = reinterpret_cast<double*>(wI);
+#pragma unroll
+    for (int q = 0; q < kRounds; ++q) {
+      const int k = lane * kRounds + q;
+      if (k < K - 1) {
+        const double w = __dsub_rn(dist[k + 1], dist[k]);
+        slope[k] = (w == 0.0) ? 0.0 : __ddiv_rn(__dsub_rn(fxs[k + 1], fxs[k]), w);
+      }
+    }
+    __syncwarp();
+    resample<true>(dist, fxs, slope, K, p.n_samples, out, lane, reinterpret_cast<float*>(wE));
     __syncwarp();
   }
 }
@@ -392,7 +498,8 @@ evenly_spaced_kernel(const double* __restrict__ x, const double* __restrict__ fx
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long f = (long long)blockIdx.x * kWarps + warp;
   if (f >= frames) return;
-  resample(x + f * K, fx + f * K, K, n_samples, out + f * 2 * (long long)n_samples, lane);
+  __shared__ float stage[kWarps][kStage];
+  resample<false>(x + f * K, fx + f * K, nullptr, K, n_samples, out + f * 2 * (long long)n_samples, lane, stage[warp]);
 }
 
 }  // namespace
