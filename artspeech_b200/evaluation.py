@@ -163,3 +163,55 @@ class GraphedEvaluator:
             self.targets.copy_(targets, non_blocking=True)
         self.graph.replay()
         return self.result
+
+
+class StreamedEvaluator:
+    """Evaluation of a SEQUENCE of host batches with the copies overlapped with the compute.
+
+    The reference's ``run_test`` loop (evaluation.py:53-128) takes one batch at a time from the
+    DataLoader, moves it to the device, runs it and moves the results back.  Here ``depth`` captured
+    steps (``GraphedEvaluator``) alternate: while step i runs, the host->device copy of step i+1
+    (tokens + target contours from pinned memory) proceeds on a copy stream, and the accumulator
+    vector of each step comes back with an asynchronous device->host copy into pinned memory.
+    Every step still copies its own inputs in and its own result out; only the waiting is hidden.
+    """
+
+    def __init__(self, model, tokens, lengths, targets, articulators=None, upper_incisor=None, depth=2):
+        dev = model.embedding.weight.device
+        self.device = dev
+        self.depth = depth
+        self.slots = [GraphedEvaluator(model, tokens, lengths, targets, articulators, upper_incisor)
+                      for _ in range(depth)]
+        n = self.slots[0].result["acc"].numel()
+        self.acc_host = [torch.empty(n, dtype=torch.float64).pin_memory() for _ in range(depth)]
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.copied = [torch.cuda.Event() for _ in range(depth)]
+        self.done = [torch.cuda.Event() for _ in range(depth)]
+
+    def run(self, batches):
+        """batches: iterable of (tokens, targets) pinned host tensors of the captured shape.
+        Returns the list of per-step accumulator vectors (fp64 CPU tensors, summed over ranks)."""
+        out = []
+        cur = torch.cuda.current_stream(self.device)
+        n_steps = 0
+        for i, (tok, tgt) in enumerate(batches):
+            s = i % self.depth
+            slot = self.slots[s]
+            if i >= self.depth:
+                self.done[s].synchronize()        # step i - depth finished: its slot and host buffer are free
+                out.append(self.acc_host[s].clone())
+            with torch.cuda.stream(self.copy_stream):
+                slot.tokens.copy_(tok, non_blocking=True)
+                slot.targets.copy_(tgt, non_blocking=True)
+                self.copied[s].record(self.copy_stream)
+            cur.wait_event(self.copied[s])
+            slot.graph.replay()
+            reduce_accumulators(slot.result["acc"])
+            self.acc_host[s].copy_(slot.result["acc"], non_blocking=True)
+            self.done[s].record(cur)
+            n_steps = i + 1
+        for i in range(max(0, n_steps - self.depth), n_steps):
+            s = i % self.depth
+            self.done[s].synchronize()
+            out.append(self.acc_host[s].clone())
+        return out

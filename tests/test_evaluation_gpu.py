@@ -57,3 +57,27 @@ def test_graph_replay_equals_eager(setup):
     want = evaluation.evaluate_batch(net, x2.cuda(), L, tgt)
     assert torch.equal(r2["outputs"], want["outputs"])
     assert torch.equal(r2["acc"], want["acc"])
+
+
+def test_streamed_evaluator_matches_step_by_step():
+    """StreamedEvaluator (copy of step i+1 overlapped with step i) returns, for every step, exactly
+    the accumulator vector of the plain step on the same batch."""
+    import torch
+    from artspeech_b200 import evaluation, models, synthetic
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(0)
+    net = models.ArtSpeech(45, 10, precision="fast").to(dev).eval()
+    B, T = 6, 17
+    L = [17, 17, 12, 9, 4, 2]
+    batches = []
+    for k in range(5):
+        tok = synthetic.tokens(B, T, 45, seed=10 + k).pin_memory()
+        tgt = synthetic.contours(B * T, 10, 50, seed=20 + k).view(B, T, 10, 2, 50).pin_memory()
+        batches.append((tok, tgt))
+    want = [evaluation.evaluate_batch(net, t.to(dev), L, g.to(dev))["acc"].cpu() for t, g in batches]
+    st = evaluation.StreamedEvaluator(net, batches[0][0].to(dev), L, batches[0][1].to(dev), depth=2)
+    got = st.run(batches)
+    assert len(got) == 5
+    for a, b in zip(got, want):
+        assert torch.equal(a, b)
+    assert len(st.run(batches[:1])) == 1 and torch.equal(st.run(batches[:1])[0], want[0])
