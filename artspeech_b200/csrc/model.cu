@@ -94,6 +94,8 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   const size_t o_head_w = p.take(sizeof(float) * N * kHeadPad * kFc), o_head_b = p.take(sizeof(float) * N * kHeadPad);
   const bool umma = umma_decoder_supported(m);
   const size_t o_umma = umma ? p.take(sizeof(float) * umma_image_floats(n_art)) : 0;
+  const bool proj = proj_umma_supported(m);
+  const size_t o_proj = proj ? p.take(sizeof(float) * proj_image_floats(m)) : 0;
 
   cudaError_t e = cudaMalloc(&m->arena, p.total);
   if (e != cudaSuccess) {
@@ -120,11 +122,13 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   w.ln2_w = F(o_ln2_w); w.ln2_b = F(o_ln2_b);
   w.head_w = F(o_head_w); w.head_b = F(o_head_b);
   w.umma_image = umma ? F(o_umma) : nullptr;
+  w.proj_image = proj ? F(o_proj) : nullptr;
   m->decoder_impl = umma ? 1 : 0;
 
   int rc = pack_recurrent_weights(m, src, st);
   if (!rc) rc = pack_dense_weights(m, src, st);
   if (!rc && umma) rc = pack_umma_image(m, src, st);
+  if (!rc && proj) rc = pack_proj_image(m, st);
   if (!rc) rc = check_cuda(cudaStreamSynchronize(st), "asb_model_create: packing kernels");
   if (rc) {
     cudaFree(m->arena);
@@ -211,7 +215,11 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
   mark(1);
   if ((rc = launch_recurrent_layer(m, 0, ws.gi, ws.lengths, ws.out0, B, T, st))) return rc;
   mark(2);
-  if ((rc = launch_linear(m, ws.out0, m->w.wih1, m->w.bih1, ws.gi, int(M), 2 * m->G * kH, 2 * kH, st))) return rc;
+  if (m->w.proj_image && m->decoder_impl == 1) {  // the tcgen05 kernels are selected together
+    if ((rc = launch_proj_umma(m, ws.out0, ws.gi, int(M), st))) return rc;
+  } else {
+    if ((rc = launch_linear(m, ws.out0, m->w.wih1, m->w.bih1, ws.gi, int(M), 2 * m->G * kH, 2 * kH, st))) return rc;
+  }
   mark(3);
   if ((rc = launch_recurrent_layer(m, 1, ws.gi, ws.lengths, ws.out1, B, T, st))) return rc;
   mark(4);

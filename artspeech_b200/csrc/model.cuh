@@ -33,6 +33,8 @@ struct PackedWeights {
   float* head_w; float* head_b;   // [N][128][256] (x rows 0..D-1, y rows D..2D-1, rest zero), [N][128]
   // pre-swizzled tf32 weight image streamed by the tcgen05 decoder (decoder_umma.cu); fast mode only
   float* umma_image;
+  // pre-swizzled tf32 image of wih1 for the tcgen05 layer-1 projection (proj_umma.cu); fast mode only
+  float* proj_image;
 };
 
 }  // namespace asb
@@ -77,5 +79,11 @@ size_t umma_image_floats(int n_art);
 bool umma_decoder_supported(const asb_model* m);
 int pack_umma_image(asb_model* m, const asb_weights* w, cudaStream_t st);
 int launch_decoder_umma(const asb_model* m, const float* rnn_out, float* out, int M, cudaStream_t st);
+
+// ---- tcgen05 layer-1 input projection (proj_umma.cu) --------------------------------
+size_t proj_image_floats(const asb_model* m);
+bool proj_umma_supported(const asb_model* m);
+int pack_proj_image(asb_model* m, cudaStream_t st);   // after pack_dense_weights (reads w.wih1)
+int launch_proj_umma(const asb_model* m, const float* A, float* C, int M, cudaStream_t st);
 
 }  // namespace asb
