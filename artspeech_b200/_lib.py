@@ -65,6 +65,7 @@ SIGNATURES = {
     "asb_eval_accumulate": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                            ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
     "asb_model_set_decoder": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "asb_model_set_recurrent": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "asb_model_profile_enable": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "asb_model_profile_read": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_float),
                                               ctypes.POINTER(ctypes.c_int32), ctypes.c_int]),

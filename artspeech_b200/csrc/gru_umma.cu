@@ -1,0 +1,252 @@
+// Recurrent layer on tcgen05 tensor cores with W_hh resident in shared memory for all T steps.
+//
+// Same computation as gru.cu's fast kernel (nn.GRU cell of models.py:111 with packed-sequence
+// semantics): per step gh^T[G*H x batch] = W_hh[G*H x H] . h^T[H x batch], gates fused behind it.
+//
+// Blackwell mapping
+//   * one CTA = 2*CPT (4, 8 or 16) batch rows of one direction - as few as still fill one wave of
+//     SMs, because the gate math (6 MUFU per unit and row) is what bounds a step; W_hh (bf16, G tiles of 128 x 128, K-major with the
+//     128-byte swizzle) is copied ONCE into shared memory (96 KB for the GRU) by bulk async copies
+//     from an image pre-swizzled at model creation and stays there for the whole sequence;
+//   * per step one thread issues G x 8 tcgen05.mma (kind::f16, bf16 in, fp32 accumulate, M = 128
+//     gate rows, N = 16 batch rows, K = 16): A = W_hh tile (smem), B = h as bf16 (smem, 4 KB),
+//     D = G x 16 columns of tensor memory, lane = hidden unit;
+//   * the 8 epilogue warps (thread = hidden unit, 8 batch columns) read D with tcgen05.ld - the r,
+//     z, n pre-activations of one (unit, row) sit in the same lane, so the gate math is
+//     thread-local -, keep h in fp32 registers, write h as bf16 back into the B operand and
+//     the fp32 output row, and hand over to the MMA thread through one mbarrier; the input
+//     pre-activations of the next step are prefetched while the MMAs run.
+#include <cuda_bf16.h>
+
+#include "model.cuh"
+#include "umma.cuh"
+
+namespace {
+
+using namespace asb;
+using namespace asb::umma;
+
+constexpr int kRows = 16;                    // the MMA's N (columns past the CTA's rows stay zero)
+constexpr int kTileBytes = 128 * kH * 2;     // one gate tile of W_hh in bf16: 32 KB
+constexpr int kAtomBytes = 128 * 128;        // 128 rows x 64 bf16
+constexpr int kHsBytes = 2 * kRows * 128;    // h as the B operand: 2 k-atoms x 16 rows x 128 B
+constexpr int kEpiWarps = 8;
+constexpr int kCtlWarp = 8;
+constexpr int kThreads = 288;
+
+__device__ __forceinline__ float sigmoid_f(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+__device__ __forceinline__ float tanh_f(float x) { return 2.f * sigmoid_f(2.f * x) - 1.f; }
+
+// byte offset of element (row, k) inside a K-major, 128-byte-swizzled bf16 operand whose k-atoms
+// (64 elements) are `atom_bytes` apart
+__host__ __device__ constexpr uint32_t sw128_bf16(uint32_t row, uint32_t k, uint32_t atom_bytes) {
+  return (k >> 6) * atom_bytes + (row >> 3) * 1024u + (row & 7u) * 128u +
+         ((((k & 63u) >> 3) ^ (row & 7u)) << 4) + (k & 7u) * 2u;
+}
+
+// whh (G*128, 128) fp32 -> bf16 image [gate][k-atom][128 rows][128 B swizzled]
+__global__ void pack_whh_umma_kernel(const float* __restrict__ whh, __nv_bfloat16* __restrict__ img, int G) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= G * kH * kH) return;
+  const int row = i / kH, k = i - row * kH;
+  const int gate = row / kH, m = row - gate * kH;
+  const uint32_t off = gate * kTileBytes + sw128_bf16(m, k, kAtomBytes);
+  img[off / 2] = __float2bfloat16_rn(whh[i]);
+}
+
+struct RnnArgs {
+  const __nv_bfloat16* img[2];   // per direction
+  const float* bhhn[2];          // GRU: b_hh of the n gate
+  const float* gi;               // (B*T, 2, G*H)
+  const int* lengths;            // (B) sorted descending
+  float* out;                    // (B, T, 2H), pre-zeroed
+  int B, T;
+};
+
+// CPT = batch columns per epilogue thread; the CTA owns 2 * CPT batch rows
+template <int G, int CPT>
+__global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem =
+      reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  unsigned char* Wsm = smem;                         // G x 32 KB
+  unsigned char* Hs = smem + G * kTileBytes;         // 4 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(Hs + kHsBytes);
+  uint64_t* w_full = bars;       // weights landed
+  uint64_t* h_ready = bars + 1;  // h (bf16) of this step is in shared memory, D has been read
+  uint64_t* d_ready = bars + 2;  // this step's MMAs completed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int dir = blockIdx.y;
+  const int b0 = blockIdx.x * 2 * CPT;
+  const int Lmax = a.lengths[b0];   // sorted descending: the tile's first row is its longest
+  constexpr int GH = G * kH;
+
+  if (tid == 0) {
+    mbar_init(w_full, 1);
+    mbar_init(h_ready, kEpiWarps);
+    mbar_init(d_ready, 1);
+    fence_mbar_init();
+  }
+  if (warp == kCtlWarp) tmem_alloc(tmem_slot, 64);
+  for (int i = tid; i < kHsBytes / 4; i += kThreads) reinterpret_cast<uint32_t*>(Hs)[i] = 0u;   // h0 = 0
+  fence_proxy_async();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_d = *tmem_slot;
+
+  if (warp == kCtlWarp) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(w_full, G * kTileBytes);
+      const unsigned char* src = reinterpret_cast<const unsigned char*>(a.img[dir]);
+      for (int j = 0; j < G * 2; ++j) bulk_g2s(Wsm + j * kAtomBytes, src + (size_t)j * kAtomBytes, kAtomBytes, w_full);
+      mbar_wait(w_full, 0);
+      const uint32_t idesc = idesc_bf16_m128(kRows);
+      const uint64_t adesc0 = smem_desc_k_sw128(smem_u32(Wsm));
+      const uint64_t bdesc0 = smem_desc_k_sw128(smem_u32(Hs));
+      for (int s = 0; s < Lmax; ++s) {
+        mbar_wait(h_ready, s & 1);
+        fence_after_sync();
+#pragma unroll
+        for (int g = 0; g < G; ++g)
+#pragma unroll
+          for (int kt = 0; kt < 8; ++kt) {
+            // k-step kt: atom kt / 4, 32 bytes (2 descriptor units) per step inside the atom
+            const uint64_t ad = adesc0 + uint64_t((g * kTileBytes + (kt >> 2) * kAtomBytes) >> 4) + uint64_t(2 * (kt & 3));
+            const uint64_t bd = bdesc0 + uint64_t(((kt >> 2) * kRows * 128) >> 4) + uint64_t(2 * (kt & 3));
+            mma_bf16_ss(tmem_d + g * kRows, ad, bd, idesc, kt != 0);
+          }
+        commit(d_ready);
+      }
+    }
+    __syncwarp();
+  } else {
+    // thread = (hidden unit u = TMEM lane, CPT of the CTA's 2 * CPT batch rows)
+    const int quarter = warp & 3, colhalf = warp >> 2;
+    const int u = quarter * 32 + lane;
+    const uint32_t taddr = tmem_d + (uint32_t(quarter * 32) << 16) + colhalf * CPT;
+    const float bn = a.bhhn[dir][u];
+    int len[CPT];
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      const int b = b0 + colhalf * CPT + j;
+      len[j] = b < a.B ? a.lengths[b] : 0;
+    }
+    float h[CPT];
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) h[j] = 0.f;
+
+    float gin[CPT][G];
+    auto load_gi = [&](int t) {
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) {
+        if (t < len[j]) {
+          const float* p = a.gi + (((long long)(b0 + colhalf * CPT + j) * a.T + t) * 2 + dir) * GH + u;
+#pragma unroll
+          for (int g = 0; g < G; ++g) gin[j][g] = __ldg(p + g * kH);
+        } else {
+#pragma unroll
+          for (int g = 0; g < G; ++g) gin[j][g] = 0.f;
+        }
+      }
+    };
+    if (Lmax > 0) load_gi(dir ? Lmax - 1 : 0);
+    // h0 (zeros) is in place: first hand-over to the MMA thread
+    __syncwarp();
+    if (lane == 0) mbar_arrive(h_ready);
+
+    for (int s = 0; s < Lmax; ++s) {
+      const int t = dir ? Lmax - 1 - s : s;
+      float gc[CPT][G];
+#pragma unroll
+      for (int j = 0; j < CPT; ++j)
+#pragma unroll
+        for (int g = 0; g < G; ++g) gc[j][g] = gin[j][g];
+      if (s + 1 < Lmax) load_gi(dir ? t - 1 : t + 1);   // in flight while the MMAs run
+
+      mbar_wait(d_ready, s & 1);
+      fence_after_sync();
+      uint32_t d[G][CPT];
+#pragma unroll
+      for (int g = 0; g < G; ++g) tmem_ldn(taddr + g * kRows, d[g]);
+      tmem_ld_wait();
+
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) {
+        const float r = sigmoid_f(gc[j][0] + __uint_as_float(d[0][j]));
+        const float z = sigmoid_f(gc[j][1] + __uint_as_float(d[1][j]));
+        const float nn = tanh_f(gc[j][2] + r * (__uint_as_float(d[2][j]) + bn));
+        const float hn = nn + z * (h[j] - nn);
+        const bool valid = t < len[j];
+        h[j] = valid ? hn : h[j];
+        const int n = colhalf * CPT + j;
+        *reinterpret_cast<__nv_bfloat16*>(Hs + sw128_bf16(n, u, kRows * 128)) = __float2bfloat16_rn(h[j]);
+        if (valid) a.out[((long long)(b0 + n) * a.T + t) * (2 * kH) + dir * kH + u] = h[j];
+      }
+      fence_proxy_async();     // the generic-proxy writes of h must be visible to the tensor core
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(h_ready);
+    }
+  }
+
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  if (warp == kCtlWarp) tmem_dealloc(tmem_d, 64);
+}
+
+}  // namespace
+
+namespace asb {
+
+size_t whh_umma_bytes(const asb_model* m) { return (size_t)m->G * kTileBytes; }
+
+bool rnn_umma_supported(const asb_model* m) { return m->precision == ASB_PRECISION_FAST && m->G == 3 && m->H == kH; }
+
+int pack_whh_umma(asb_model* m, const asb_weights* src, cudaStream_t st) {
+  for (int layer = 0; layer < 2; ++layer)
+    for (int dir = 0; dir < 2; ++dir) {
+      const int n = m->G * kH * kH;
+      pack_whh_umma_kernel<<<(n + 255) / 256, 256, 0, st>>>(
+          src->rnn_w_hh[layer][dir], reinterpret_cast<__nv_bfloat16*>(m->w.whh_umma[layer][dir]), m->G);
+      ASB_CHECK_LAUNCH("pack_whh_umma_kernel");
+    }
+  return ASB_OK;
+}
+
+int launch_rnn_umma(const asb_model* m, int layer, const float* gi, const int* lengths, float* out, int B, int T,
+                    cudaStream_t st) {
+  const int smem = 3 * kTileBytes + kHsBytes + 64 + 1024;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(rnn_umma_kernel<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(rnn_umma_kernel<3, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(rnn_umma_kernel<3, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return check_cuda(e, "rnn_umma_kernel smem attribute");
+    configured = true;
+  }
+  RnnArgs a;
+  for (int d = 0; d < 2; ++d) {
+    a.img[d] = reinterpret_cast<const __nv_bfloat16*>(m->w.whh_umma[layer][d]);
+    a.bhhn[d] = m->w.bhh_n[layer][d];
+  }
+  a.gi = gi; a.lengths = lengths; a.out = out; a.B = B; a.T = T;
+  // fewest rows per CTA that still fit one wave of the machine (the gate math bounds a step)
+  const int sms = sm_count();
+  if (2 * ((B + 3) / 4) <= sms) {
+    rnn_umma_kernel<3, 2><<<dim3((B + 3) / 4, 2), kThreads, smem, st>>>(a);
+  } else if (2 * ((B + 7) / 8) <= sms) {
+    rnn_umma_kernel<3, 4><<<dim3((B + 7) / 8, 2), kThreads, smem, st>>>(a);
+  } else {
+    rnn_umma_kernel<3, 8><<<dim3((B + 15) / 16, 2), kThreads, smem, st>>>(a);
+  }
+  ASB_CHECK_LAUNCH("rnn_umma_kernel");
+  return ASB_OK;
+}
+
+}  // namespace asb

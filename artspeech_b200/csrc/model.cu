@@ -94,6 +94,11 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   const size_t o_head_w = p.take(sizeof(float) * N * kHeadPad * kFc), o_head_b = p.take(sizeof(float) * N * kHeadPad);
   const bool umma = umma_decoder_supported(m);
   const size_t o_umma = umma ? p.take(sizeof(float) * umma_image_floats(n_art)) : 0;
+  const bool rnnu = rnn_umma_supported(m);
+  size_t o_whhu[2][2] = {{0, 0}, {0, 0}};
+  if (rnnu)
+    for (int l = 0; l < 2; ++l)
+      for (int d = 0; d < 2; ++d) o_whhu[l][d] = p.take(whh_umma_bytes(m));
   const bool proj = proj_umma_supported(m);
   const size_t o_proj = proj ? p.take(sizeof(float) * proj_image_floats(m)) : 0;
 
@@ -123,12 +128,15 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   w.head_w = F(o_head_w); w.head_b = F(o_head_b);
   w.umma_image = umma ? F(o_umma) : nullptr;
   w.proj_image = proj ? F(o_proj) : nullptr;
+  for (int l = 0; l < 2; ++l)
+    for (int d = 0; d < 2; ++d) w.whh_umma[l][d] = rnnu ? static_cast<void*>(b + o_whhu[l][d]) : nullptr;
   m->decoder_impl = umma ? 1 : 0;
 
   int rc = pack_recurrent_weights(m, src, st);
   if (!rc) rc = pack_dense_weights(m, src, st);
   if (!rc && umma) rc = pack_umma_image(m, src, st);
   if (!rc && proj) rc = pack_proj_image(m, st);
+  if (!rc && rnnu) rc = pack_whh_umma(m, src, st);
   if (!rc) rc = check_cuda(cudaStreamSynchronize(st), "asb_model_create: packing kernels");
   if (rc) {
     cudaFree(m->arena);
@@ -213,7 +221,11 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
   mark(0);
   if ((rc = launch_gather_gi0(m, tok, T_in, ws.gi, B, T, st))) return rc;
   mark(1);
-  if ((rc = launch_recurrent_layer(m, 0, ws.gi, ws.lengths, ws.out0, B, T, st))) return rc;
+  if (m->rnn_impl == 1 && m->w.whh_umma[0][0]) {
+    if ((rc = launch_rnn_umma(m, 0, ws.gi, ws.lengths, ws.out0, B, T, st))) return rc;
+  } else {
+    if ((rc = launch_recurrent_layer(m, 0, ws.gi, ws.lengths, ws.out0, B, T, st))) return rc;
+  }
   mark(2);
   if (m->w.proj_image && m->decoder_impl == 1) {  // the tcgen05 kernels are selected together
     if ((rc = launch_proj_umma(m, ws.out0, ws.gi, int(M), st))) return rc;
@@ -221,7 +233,11 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
     if ((rc = launch_linear(m, ws.out0, m->w.wih1, m->w.bih1, ws.gi, int(M), 2 * m->G * kH, 2 * kH, st))) return rc;
   }
   mark(3);
-  if ((rc = launch_recurrent_layer(m, 1, ws.gi, ws.lengths, ws.out1, B, T, st))) return rc;
+  if (m->rnn_impl == 1 && m->w.whh_umma[0][0]) {
+    if ((rc = launch_rnn_umma(m, 1, ws.gi, ws.lengths, ws.out1, B, T, st))) return rc;
+  } else {
+    if ((rc = launch_recurrent_layer(m, 1, ws.gi, ws.lengths, ws.out1, B, T, st))) return rc;
+  }
   mark(4);
   if (m->decoder_impl == 1) {
     if ((rc = launch_decoder_umma(m, ws.out1, out, int(M), st))) return rc;
@@ -230,6 +246,15 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
   }
   mark(5);
   if (prof) m->pending.push_back(ev);
+  return ASB_OK;
+}
+
+extern "C" int asb_model_set_recurrent(asb_model* m, int impl) {
+  if (!m) return set_error(ASB_ERR_INVALID, "asb_model_set_recurrent: null model");
+  if (impl == 1 && !m->w.whh_umma[0][0])
+    return set_error(ASB_ERR_UNSUPPORTED, "asb_model_set_recurrent: the tcgen05 recurrent kernel needs fast precision and the GRU cell");
+  if (impl != 0 && impl != 1) return set_error(ASB_ERR_INVALID, "asb_model_set_recurrent: impl must be 0 or 1");
+  m->rnn_impl = impl;
   return ASB_OK;
 }
 

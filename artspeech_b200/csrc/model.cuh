@@ -35,6 +35,9 @@ struct PackedWeights {
   float* umma_image;
   // pre-swizzled tf32 image of wih1 for the tcgen05 layer-1 projection (proj_umma.cu); fast mode only
   float* proj_image;
+  // bf16 W_hh images (K-major, 128-byte swizzle) kept in shared memory by the tcgen05 recurrent
+  // kernel (gru_umma.cu); fast mode only
+  void* whh_umma[2][2];
 };
 
 }  // namespace asb
@@ -48,7 +51,8 @@ struct asb_model {
   size_t arena_bytes;
   asb::PackedWeights w;
   // optional per-stage timing (asb_model_profile_*): one event set per profiled forward
-  int decoder_impl = 0;  // 0 = mma.sync (decoder.cu), 1 = tcgen05/TMEM (decoder_umma.cu)
+  int decoder_impl = 0;  // 0 = mma.sync (decoder.cu), 1 = tcgen05/TMEM (decoder_umma.cu, proj_umma.cu)
+  int rnn_impl = 0;      // 0 = register-resident mma.sync (gru.cu, the faster one), 1 = tcgen05 (gru_umma.cu)
   bool profile = false;
   std::vector<std::array<cudaEvent_t, ASB_N_STAGES + 1>> pending;
   std::vector<std::array<cudaEvent_t, ASB_N_STAGES + 1>> free_sets;
@@ -85,5 +89,12 @@ size_t proj_image_floats(const asb_model* m);
 bool proj_umma_supported(const asb_model* m);
 int pack_proj_image(asb_model* m, cudaStream_t st);   // after pack_dense_weights (reads w.wih1)
 int launch_proj_umma(const asb_model* m, const float* A, float* C, int M, cudaStream_t st);
+
+// ---- tcgen05 recurrent layer (gru_umma.cu) -------------------------------------------
+size_t whh_umma_bytes(const asb_model* m);
+bool rnn_umma_supported(const asb_model* m);
+int pack_whh_umma(asb_model* m, const asb_weights* w, cudaStream_t st);
+int launch_rnn_umma(const asb_model* m, int layer, const float* gi, const int* lengths, float* out, int B, int T,
+                    cudaStream_t st);
 
 }  // namespace asb

@@ -75,7 +75,8 @@ def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_inc
                    lengths_dev=None):
     """One evaluation step on the model's device.
 
-    tokens (B, T) int64, lengths sorted descending, targets (B, T, N, 2, 50) fp32 - all on the GPU.
+    tokens (B, T) int64, lengths sorted descending, targets (B, T, N, 2, 50) fp32, on the GPU (host
+    tensors are copied to the model's device first).
     Returns dict(outputs, p2cp (B,T,N), tv_pred (B,T,4), tv_target (B,T,4), acc (N+14,) fp64).
     ``mark(name)``, if given, is called at the stage boundaries (bench.py records CUDA events there).
     """
@@ -83,8 +84,11 @@ def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_inc
     articulators = articulators or synthetic.ARTICULATORS
     if upper_incisor is None:
         upper_incisor = synthetic.UPPER_INCISOR_REF
+    dev = model.embedding.weight.device
+    tokens = tokens.to(dev, non_blocking=True)        # host batches (pinned) are copied here
+    targets = targets.to(dev, non_blocking=True)
     if lengths_dev is None:
-        lengths_dev = torch.as_tensor([int(v) for v in lengths], dtype=torch.int32).to(tokens.device)
+        lengths_dev = torch.as_tensor([int(v) for v in lengths], dtype=torch.int32).to(dev)
     mark("start")
     outputs = model(tokens, lengths, lengths_dev=lengths_dev)         # evaluation.py:57
     mark("forward")

@@ -146,6 +146,13 @@ class ArtSpeech(nn.Module):
         code = {"tcgen05": 1, "mma": 0}[impl]
         _lib.check(_lib.lib().asb_model_set_decoder(self._ensure_native(dev), code))
 
+    def set_recurrent(self, impl):
+        """"mma" (default: W_hh in registers, mma.sync) or "tcgen05" (W_hh in shared memory,
+        tcgen05.mma with the gates behind tcgen05.ld) for the two GRU layers; fast precision only."""
+        dev = self.embedding.weight.device
+        code = {"tcgen05": 1, "mma": 0}[impl]
+        _lib.check(_lib.lib().asb_model_set_recurrent(self._ensure_native(dev), code))
+
     # ------------------------------------------------------------------ per-stage timing
     STAGES = ("gather", "gru_l0", "proj_l1", "gru_l1", "decoder")
 

@@ -178,8 +178,15 @@ ASB_API int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_in,
                                size_t workspace_bytes, void* stream);
 
 /* Decoder implementation: 1 = tcgen05/TMEM kernel (default in fast precision with n_samples = 50),
- * 0 = mma.sync kernel (always used in fp32 precision).  Both compute models.py:140-145. */
+ * 0 = mma.sync kernel (always used in fp32 precision).  Both compute models.py:140-145.  The
+ * layer-1 input projection follows the same switch (tcgen05 proj_umma.cu / mma.sync linear256). */
 ASB_API int asb_model_set_decoder(asb_model* m, int impl);
+
+/* Recurrent-layer implementation (fast precision): 0 = W_hh resident in registers, mma.sync bf16
+ * (default: 0.91 us per time step at batch 256 on B200), 1 = W_hh resident in shared memory,
+ * tcgen05.mma kind::f16 with the gates fused behind tcgen05.ld (1.27 us per step: the 96 KB A
+ * operand is re-read from shared memory every step).  Both compute models.py:111,136-138. */
+ASB_API int asb_model_set_recurrent(asb_model* m, int impl);
 
 /* Per-stage device timing of asb_model_forward (CUDA events on `stream`): enable, run forwards,
  * then read the accumulated milliseconds and launch counts (synchronises the recorded events).

@@ -111,3 +111,29 @@ def test_errors_and_state_dict(mods):
     assert (a - b).abs().max().item() > 1e-4
     with pytest.raises(NotImplementedError):
         net(x, [9, 5, 3])                  # autograd enabled: training is not implemented
+
+
+def test_tcgen05_recurrent_kernel_matches_register_resident_kernel(mods):
+    """gru_umma.cu (W_hh in shared memory, tcgen05.mma, 4/8/16 rows per CTA) against gru.cu."""
+    import torch
+    from artspeech_b200 import models, synthetic
+    from oracle import model as omodel
+    sd = omodel.randomize_affine(omodel.make_state_dict(45, 10, seed=0), seed=2)
+    net = models.ArtSpeech(45, 10, precision="fast")
+    net.load_state_dict(sd)
+    net = net.cuda().eval()
+    for (B, T) in [(5, 23), (256, 40), (700, 12), (1300, 9)]:     # 4, 4, 8 and 16 rows per CTA
+        x = synthetic.tokens(B, T, 45, seed=B)
+        L = synthetic.sorted_lengths(B, max(1, T // 4), T, seed=B)
+        with torch.no_grad():
+            net.set_recurrent("mma")
+            a = net(x.cuda(), L)
+            net.set_recurrent("tcgen05")
+            b = net(x.cuda(), L)
+            net.set_recurrent("mma")
+        torch.cuda.synchronize()
+        assert not torch.isnan(b).any()
+        assert float((a - b).abs().max()) <= 1e-3, (B, T, float((a - b).abs().max()))
+        nb = min(B, 6)
+        want = omodel.artspeech_forward(sd, x[:nb], L[:nb], torch.float32)
+        assert float((b[:nb, :want.shape[1]].cpu() - want).abs().max()) <= 2e-3
