@@ -137,3 +137,35 @@ def test_tcgen05_recurrent_kernel_matches_register_resident_kernel(mods):
         nb = min(B, 6)
         want = omodel.artspeech_forward(sd, x[:nb], L[:nb], torch.float32)
         assert float((b[:nb, :want.shape[1]].cpu() - want).abs().max()) <= 2e-3
+
+
+@pytest.mark.parametrize("precision,tol", [("fast", 2e-3), ("fp32", 1e-5)])
+def test_config4_long_sequence(mods, precision, tol):
+    """BASELINE configs[3]: batch 64, length 1024 - 1024 dependent recurrent steps per direction.
+    Rows are independent, so the oracle (fp32 CPU forward) is run on 6 of the 64 rows."""
+    import torch
+    from artspeech_b200 import models, synthetic
+    from oracle import model as omodel
+    sd = omodel.randomize_affine(omodel.make_state_dict(45, 10, seed=0), seed=4)
+    net = models.ArtSpeech(45, 10, precision=precision)
+    net.load_state_dict(sd)
+    net = net.cuda().eval()
+    B, T = 64, 1024
+    x = synthetic.tokens(B, T, 45, seed=44)
+    L = synthetic.sorted_lengths(B, 300, T, seed=44)
+    with torch.no_grad():
+        out = net(x.cuda(), L)
+    torch.cuda.synchronize()
+    assert tuple(out.shape) == (B, T, 10, 2, 50) and not torch.isnan(out).any()
+    rows = [0, 1, 17, 40, 62, 63]
+    for b in rows:
+        lb = int(L[b])
+        want = omodel.artspeech_forward(sd, x[b:b + 1], [lb], torch.float32)
+        err = float((out[b:b + 1, :lb].cpu() - want).abs().max())
+        assert err <= tol, (precision, b, err)
+    # padded steps hold the constant padded frame (the decoder applied to a zero GRU output)
+    b = 63
+    lb = int(L[b])
+    if lb < T:
+        pad = out[b, lb:]
+        assert float((pad - pad[0:1]).abs().max()) == 0.0
