@@ -58,16 +58,17 @@ __global__ void transpose_whh_kernel(const float* __restrict__ whh, float* __res
 }
 
 // tab0[dir][v][row] = sum_e E[v][e] * W_ih[row][e] + b_ih[row] (+ b_hh[row] for r, z)
+// GH = gates * H; rows below `fold` also take b_hh (GRU: r, z; LSTM: every gate)
 __global__ void build_tab0_kernel(const float* __restrict__ emb, const float* __restrict__ wih,
                                   const float* __restrict__ bih, const float* __restrict__ bhh,
-                                  float* __restrict__ tab, int V, int E) {
+                                  float* __restrict__ tab, int V, int E, int GH, int fold) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= V * kGH) return;
-  const int v = i / kGH, row = i - v * kGH;
+  if (i >= V * GH) return;
+  const int v = i / GH, row = i - v * GH;
   double acc = 0.0;
   for (int e = 0; e < E; ++e) acc += double(emb[v * E + e]) * double(wih[row * E + e]);
   float r = float(acc) + bih[row];
-  if (row < 2 * kH) r += bhh[row];
+  if (row < fold) r += bhh[row];
   tab[i] = r;
 }
 
@@ -78,18 +79,18 @@ __global__ void copy_slice_kernel(const float* __restrict__ src, float* __restri
 
 // gi[(b*T + t)][dir][:] = tab0[dir][x[b][t]][:]   (one float4 per thread)
 __global__ void gather_gi0_kernel(const float* __restrict__ tab, const long long* __restrict__ x, int T_in,
-                                  float* __restrict__ gi, int B, int T, int V) {
+                                  float* __restrict__ gi, int B, int T, int V, int GH) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long long total = (long long)B * T * 2 * (kGH / 4);
+  const long long total = (long long)B * T * 2 * (GH / 4);
   if (i >= total) return;
-  const int q = int(i % (kGH / 4));
-  const long long rest = i / (kGH / 4);
+  const int q = int(i % (GH / 4));
+  const long long rest = i / (GH / 4);
   const int dir = int(rest & 1);
   const long long bt = rest >> 1;
   const int b = int(bt / T), t = int(bt - (long long)b * T);
   long long tok = x[(long long)b * T_in + t];
   tok = tok < 0 ? 0 : (tok >= V ? V - 1 : tok);
-  const float4 val = __ldg(reinterpret_cast<const float4*>(tab + ((long long)dir * V + tok) * kGH) + q);
+  const float4 val = __ldg(reinterpret_cast<const float4*>(tab + ((long long)dir * V + tok) * GH) + q);
   reinterpret_cast<float4*>(gi)[i] = val;
 }
 
@@ -286,9 +287,10 @@ gru_fp32_kernel(const float* __restrict__ wt_fwd, const float* __restrict__ wt_b
 namespace asb {
 
 int launch_gather_gi0(const asb_model* m, const long long* x, int T_in, float* gi, int B, int T, cudaStream_t st) {
-  const long long total = (long long)B * T * 2 * (kGH / 4);
+  const int GH = m->G * kH;
+  const long long total = (long long)B * T * 2 * (GH / 4);
   const long long blocks = (total + 255) / 256;
-  gather_gi0_kernel<<<unsigned(blocks), 256, 0, st>>>(m->w.tab0, x, T_in, gi, B, T, m->V);
+  gather_gi0_kernel<<<unsigned(blocks), 256, 0, st>>>(m->w.tab0, x, T_in, gi, B, T, m->V, GH);
   ASB_CHECK_LAUNCH("gather_gi0_kernel");
   return ASB_OK;
 }
@@ -296,6 +298,8 @@ int launch_gather_gi0(const asb_model* m, const long long* x, int T_in, float* g
 int launch_recurrent_layer(const asb_model* m, int layer, const float* gi, const int* lengths, float* out, int B,
                            int T, cudaStream_t st) {
   const PackedWeights& w = m->w;
+  if (m->G != kG)
+    return set_error(ASB_ERR_UNSUPPORTED, "the mma.sync / fp32 recurrent kernels implement the GRU cell only");
   if (m->precision == ASB_PRECISION_FP32) {
     static bool configured = false;
     const int smem = (kH * kGH + 2 * 8 * kH) * int(sizeof(float));
@@ -328,11 +332,14 @@ int launch_recurrent_layer(const asb_model* m, int layer, const float* gi, const
 int pack_recurrent_weights(asb_model* m, const asb_weights* src, cudaStream_t st) {
   PackedWeights& w = m->w;
   for (int dir = 0; dir < 2; ++dir) {
-    const int n = m->V * kGH;
+    const int GH = m->G * kH;
+    const int n = m->V * GH;
     build_tab0_kernel<<<(n + 255) / 256, 256, 0, st>>>(src->embedding, src->rnn_w_ih[0][dir], src->rnn_b_ih[0][dir],
-                                                        src->rnn_b_hh[0][dir], w.tab0 + (size_t)dir * n, m->V, m->E);
+                                                        src->rnn_b_hh[0][dir], w.tab0 + (size_t)dir * n, m->V, m->E,
+                                                        GH, m->G == kG ? 2 * kH : GH);
     ASB_CHECK_LAUNCH("build_tab0_kernel");
   }
+  if (m->G != kG) return ASB_OK;  // LSTM: only the tcgen05 kernel (gru_umma.cu) has it; b_hh is folded entirely
   for (int layer = 0; layer < 2; ++layer)
     for (int dir = 0; dir < 2; ++dir) {
       const int nf = 8 * kG * 8 * 32 * 4;

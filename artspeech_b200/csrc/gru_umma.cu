@@ -127,16 +127,16 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
     const int quarter = warp & 3, colhalf = warp >> 2;
     const int u = quarter * 32 + lane;
     const uint32_t taddr = tmem_d + (uint32_t(quarter * 32) << 16) + colhalf * CPT;
-    const float bn = a.bhhn[dir][u];
+    const float bn = (G == 3) ? a.bhhn[dir][u] : 0.f;
     int len[CPT];
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
       const int b = b0 + colhalf * CPT + j;
       len[j] = b < a.B ? a.lengths[b] : 0;
     }
-    float h[CPT];
+    float h[CPT], cs[CPT];   // cs: LSTM cell state (unused by the GRU)
 #pragma unroll
-    for (int j = 0; j < CPT; ++j) h[j] = 0.f;
+    for (int j = 0; j < CPT; ++j) h[j] = cs[j] = 0.f;
 
     float gin[CPT][G];
     auto load_gi = [&](int t) {
@@ -175,11 +175,22 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
 
 #pragma unroll
       for (int j = 0; j < CPT; ++j) {
-        const float r = sigmoid_f(gc[j][0] + __uint_as_float(d[0][j]));
-        const float z = sigmoid_f(gc[j][1] + __uint_as_float(d[1][j]));
-        const float nn = tanh_f(gc[j][2] + r * (__uint_as_float(d[2][j]) + bn));
-        const float hn = nn + z * (h[j] - nn);
         const bool valid = t < len[j];
+        float hn;
+        if (G == 3) {   // GRU, gate rows r, z, n
+          const float r = sigmoid_f(gc[j][0] + __uint_as_float(d[0][j]));
+          const float z = sigmoid_f(gc[j][1] + __uint_as_float(d[1][j]));
+          const float nn = tanh_f(gc[j][2] + r * (__uint_as_float(d[2][j]) + bn));
+          hn = nn + z * (h[j] - nn);
+        } else {        // LSTM, gate rows i, f, g, o (torch.nn.LSTM order): c' = f c + i g, h' = o tanh(c')
+          const float ig = sigmoid_f(gc[j][0] + __uint_as_float(d[0][j]));
+          const float fg = sigmoid_f(gc[j][1] + __uint_as_float(d[1][j]));
+          const float gg = tanh_f(gc[j][2] + __uint_as_float(d[2][j]));
+          const float og = sigmoid_f(gc[j][G - 1] + __uint_as_float(d[G - 1][j]));
+          const float cn = fmaf(fg, cs[j], ig * gg);
+          cs[j] = valid ? cn : cs[j];
+          hn = og * tanh_f(cn);
+        }
         h[j] = valid ? hn : h[j];
         const int n = colhalf * CPT + j;
         *reinterpret_cast<__nv_bfloat16*>(Hs + sw128_bf16(n, u, kRows * 128)) = __float2bfloat16_rn(h[j]);
@@ -204,7 +215,9 @@ namespace asb {
 
 size_t whh_umma_bytes(const asb_model* m) { return (size_t)m->G * kTileBytes; }
 
-bool rnn_umma_supported(const asb_model* m) { return m->precision == ASB_PRECISION_FAST && m->G == 3 && m->H == kH; }
+bool rnn_umma_supported(const asb_model* m) {
+  return m->precision == ASB_PRECISION_FAST && (m->G == 3 || m->G == 4) && m->H == kH;
+}
 
 int pack_whh_umma(asb_model* m, const asb_weights* src, cudaStream_t st) {
   for (int layer = 0; layer < 2; ++layer)
@@ -217,36 +230,41 @@ int pack_whh_umma(asb_model* m, const asb_weights* src, cudaStream_t st) {
   return ASB_OK;
 }
 
-int launch_rnn_umma(const asb_model* m, int layer, const float* gi, const int* lengths, float* out, int B, int T,
-                    cudaStream_t st) {
-  const int smem = 3 * kTileBytes + kHsBytes + 64 + 1024;
+template <int G>
+static int launch_rnn_umma_g(const asb_model* m, const RnnArgs& a, int B, cudaStream_t st) {
+  const int smem = G * kTileBytes + kHsBytes + 64 + 1024;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(rnn_umma_kernel<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = cudaFuncSetAttribute(rnn_umma_kernel<G, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(rnn_umma_kernel<3, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      e = cudaFuncSetAttribute(rnn_umma_kernel<G, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(rnn_umma_kernel<3, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      e = cudaFuncSetAttribute(rnn_umma_kernel<G, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return check_cuda(e, "rnn_umma_kernel smem attribute");
     configured = true;
   }
+  // fewest rows per CTA that still fit one wave of the machine (the gate math bounds a step)
+  const int sms = sm_count();
+  if (2 * ((B + 3) / 4) <= sms) {
+    rnn_umma_kernel<G, 2><<<dim3((B + 3) / 4, 2), kThreads, smem, st>>>(a);
+  } else if (2 * ((B + 7) / 8) <= sms) {
+    rnn_umma_kernel<G, 4><<<dim3((B + 7) / 8, 2), kThreads, smem, st>>>(a);
+  } else {
+    rnn_umma_kernel<G, 8><<<dim3((B + 15) / 16, 2), kThreads, smem, st>>>(a);
+  }
+  ASB_CHECK_LAUNCH("rnn_umma_kernel");
+  return ASB_OK;
+}
+
+int launch_rnn_umma(const asb_model* m, int layer, const float* gi, const int* lengths, float* out, int B, int T,
+                    cudaStream_t st) {
   RnnArgs a;
   for (int d = 0; d < 2; ++d) {
     a.img[d] = reinterpret_cast<const __nv_bfloat16*>(m->w.whh_umma[layer][d]);
     a.bhhn[d] = m->w.bhh_n[layer][d];
   }
   a.gi = gi; a.lengths = lengths; a.out = out; a.B = B; a.T = T;
-  // fewest rows per CTA that still fit one wave of the machine (the gate math bounds a step)
-  const int sms = sm_count();
-  if (2 * ((B + 3) / 4) <= sms) {
-    rnn_umma_kernel<3, 2><<<dim3((B + 3) / 4, 2), kThreads, smem, st>>>(a);
-  } else if (2 * ((B + 7) / 8) <= sms) {
-    rnn_umma_kernel<3, 4><<<dim3((B + 7) / 8, 2), kThreads, smem, st>>>(a);
-  } else {
-    rnn_umma_kernel<3, 8><<<dim3((B + 15) / 16, 2), kThreads, smem, st>>>(a);
-  }
-  ASB_CHECK_LAUNCH("rnn_umma_kernel");
-  return ASB_OK;
+  return m->G == 3 ? launch_rnn_umma_g<3>(m, a, B, st) : launch_rnn_umma_g<4>(m, a, B, st);
 }
 
 }  // namespace asb

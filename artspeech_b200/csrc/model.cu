@@ -57,8 +57,10 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   if (!src || !out) return set_error(ASB_ERR_INVALID, "asb_model_create: null argument");
   *out = nullptr;
   if (hidden != kH) return set_error(ASB_ERR_UNSUPPORTED, "asb_model_create: hidden_size must be %d (got %d)", kH, hidden);
-  if (cell != ASB_CELL_GRU)
-    return set_error(ASB_ERR_UNSUPPORTED, "asb_model_create: only the GRU cell (every shipped config) is built; LSTM is not");
+  if (cell != ASB_CELL_GRU && cell != ASB_CELL_LSTM)
+    return set_error(ASB_ERR_INVALID, "asb_model_create: cell must be ASB_CELL_GRU or ASB_CELL_LSTM");
+  if (cell == ASB_CELL_LSTM && precision != ASB_PRECISION_FAST)
+    return set_error(ASB_ERR_UNSUPPORTED, "asb_model_create: the LSTM cell exists in fast precision only (tcgen05 recurrent kernel)");
   if (vocab <= 0 || n_art <= 0 || embed_dim <= 0 || n_samples <= 0 || 2 * n_samples > kHeadPad)
     return set_error(ASB_ERR_INVALID, "asb_model_create: bad sizes (vocab %d, n_art %d, embed %d, n_samples %d <= %d)",
                      vocab, n_art, embed_dim, n_samples, kHeadPad / 2);
@@ -131,6 +133,7 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   for (int l = 0; l < 2; ++l)
     for (int d = 0; d < 2; ++d) w.whh_umma[l][d] = rnnu ? static_cast<void*>(b + o_whhu[l][d]) : nullptr;
   m->decoder_impl = umma ? 1 : 0;
+  m->rnn_impl = (cell == ASB_CELL_LSTM) ? 1 : 0;   // the LSTM cell exists only in the tcgen05 kernel
 
   int rc = pack_recurrent_weights(m, src, st);
   if (!rc) rc = pack_dense_weights(m, src, st);
@@ -254,6 +257,8 @@ extern "C" int asb_model_set_recurrent(asb_model* m, int impl) {
   if (impl == 1 && !m->w.whh_umma[0][0])
     return set_error(ASB_ERR_UNSUPPORTED, "asb_model_set_recurrent: the tcgen05 recurrent kernel needs fast precision and the GRU cell");
   if (impl != 0 && impl != 1) return set_error(ASB_ERR_INVALID, "asb_model_set_recurrent: impl must be 0 or 1");
+  if (impl == 0 && m->G != ASB_CELL_GRU)
+    return set_error(ASB_ERR_UNSUPPORTED, "asb_model_set_recurrent: the mma.sync kernel implements the GRU cell only");
   m->rnn_impl = impl;
   return ASB_OK;
 }

@@ -62,14 +62,20 @@ class _NativeHandle:
 
 class ArtSpeech(nn.Module):
     """models.py:99-145.  ``precision``: "fast" (bf16 recurrent GEMM, tf32 elsewhere, fp32
-    accumulate/state; contours within 2e-3 of the fp32 reference) or "fp32" (within 1e-5)."""
+    accumulate/state; contours within 2e-3 of the fp32 reference) or "fp32" (within 1e-5).
+    ``rnn``: "gru" (the reference's cell, models.py:111) or "lstm" (the other member of RNNType,
+    phoneme_to_articulation/__init__.py:47-49; same state_dict keys as nn.LSTM; fast precision only)."""
 
     def __init__(self, vocab_size, n_articulators, embed_dim=64, hidden_size=128, n_samples=50, dropout=0.,
-                 precision="fast"):
+                 precision="fast", rnn="gru"):
         super().__init__()
+        cells = {"gru": (nn.GRU, _lib.CELL_GRU), "lstm": (nn.LSTM, _lib.CELL_LSTM)}
+        if str(rnn).lower() not in cells:
+            raise ValueError(f"rnn must be one of {sorted(cells)}")
+        rnn_cls, self._cell = cells[str(rnn).lower()]
         self.embedding = nn.Embedding(vocab_size, embed_dim)
-        self.rnn = nn.GRU(embed_dim, hidden_size, num_layers=2, bidirectional=True, dropout=dropout,
-                          batch_first=True)
+        self.rnn = rnn_cls(embed_dim, hidden_size, num_layers=2, bidirectional=True, dropout=dropout,
+                           batch_first=True)
         self.linear = nn.Sequential(nn.Linear(2 * hidden_size, hidden_size), nn.ReLU())
         self.predictors = nn.ModuleList([
             ArticulatorPredictor(hidden_size, n_samples) for _ in range(n_articulators)
@@ -130,7 +136,7 @@ class ArtSpeech(nn.Module):
         handle = ctypes.c_void_p()
         with torch.cuda.device(dev):
             _lib.check(_lib.lib().asb_model_create(
-                ctypes.byref(w), vocab, n_art, embed, hidden, n_samples, _lib.CELL_GRU,
+                ctypes.byref(w), vocab, n_art, embed, hidden, n_samples, self._cell,
                 PRECISIONS[self.precision], _lib.stream_ptr(dev), ctypes.byref(handle)))
         self._native = _NativeHandle(handle, key)
         return handle
@@ -148,7 +154,8 @@ class ArtSpeech(nn.Module):
 
     def set_recurrent(self, impl):
         """"mma" (default: W_hh in registers, mma.sync) or "tcgen05" (W_hh in shared memory,
-        tcgen05.mma with the gates behind tcgen05.ld) for the two GRU layers; fast precision only."""
+        tcgen05.mma with the gates behind tcgen05.ld) for the two recurrent layers; fast precision
+        only.  The LSTM cell exists in the tcgen05 kernel alone (selected automatically)."""
         dev = self.embedding.weight.device
         code = {"tcgen05": 1, "mma": 0}[impl]
         _lib.check(_lib.lib().asb_model_set_recurrent(self._ensure_native(dev), code))

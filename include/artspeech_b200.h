@@ -130,8 +130,9 @@ ASB_API int asb_eval_accumulate(const float* p2cp, const float* tv_pred, const f
 
 typedef struct asb_model asb_model;
 
-#define ASB_CELL_GRU 3
-#define ASB_CELL_LSTM 4
+#define ASB_CELL_GRU 3  /* nn.GRU, gate rows r, z, n (models.py:111) - both precisions                       */
+#define ASB_CELL_LSTM 4 /* nn.LSTM, gate rows i, f, g, o (RNNType.LSTM, phoneme_to_articulation/__init__.py:47-49)
+                           - ASB_PRECISION_FAST only; ASB_PRECISION_FP32 returns ASB_ERR_UNSUPPORTED */
 #define ASB_PRECISION_FAST 0 /* bf16 recurrent GEMM, tf32 elsewhere, fp32 accumulate/state (2e-3 gate) */
 #define ASB_PRECISION_FP32 1 /* 3xTF32 / FFMA everywhere (1e-5 gate)                                  */
 

@@ -169,3 +169,65 @@ def test_config4_long_sequence(mods, precision, tol):
     if lb < T:
         pad = out[b, lb:]
         assert float((pad - pad[0:1]).abs().max()) == 0.0
+
+
+def test_lstm_cell_matches_nn_lstm_oracle(mods):
+    """RNNType.LSTM (phoneme_to_articulation/__init__.py:47-49): the 4-gate instantiation of the
+    tcgen05 recurrent kernel against the nn.LSTM-based oracle (stock cell and cell equations)."""
+    import torch
+    from artspeech_b200 import models, synthetic
+    from oracle import model as omodel
+    sd = omodel.randomize_affine(omodel.make_state_dict(45, 10, seed=0, cell="lstm"), seed=5)
+    net = models.ArtSpeech(45, 10, precision="fast", rnn="lstm")
+    assert sorted(net.state_dict()) == sorted(sd)
+    net.load_state_dict(sd)
+    net = net.cuda().eval()
+    for (B, T) in [(1, 1), (5, 23), (256, 40), (700, 12), (1300, 9)]:   # 4, 4, 4, 8 and 16 rows per CTA
+        x = synthetic.tokens(B, T, 45, seed=B)
+        L = synthetic.sorted_lengths(B, max(1, T // 4), T, seed=B)
+        with torch.no_grad():
+            out = net(x.cuda(), L)
+        torch.cuda.synchronize()
+        assert not torch.isnan(out).any()
+        nb = min(B, 6)
+        want = omodel.artspeech_forward(sd, x[:nb], L[:nb], torch.float32)
+        err = float((out[:nb, :want.shape[1]].cpu() - want).abs().max())
+        assert err <= 2e-3, (B, T, err)
+        if B == 5:
+            eq = omodel.artspeech_forward(sd, x[:nb], L[:nb], torch.float64, rnn="equations")
+            assert float((out[:nb, :eq.shape[1]].cpu().double() - eq).abs().max()) <= 2e-3
+    # the mma.sync decoder / projection pair works with the 4-gate layout as well
+    with torch.no_grad():
+        a = net(x.cuda(), L)
+        net.set_decoder("mma")
+        b = net(x.cuda(), L)
+        net.set_decoder("tcgen05")
+    assert float((a - b).abs().max()) <= 1e-3
+    with pytest.raises(ValueError):
+        net.set_recurrent("mma")           # GRU-only kernel
+    net32 = models.ArtSpeech(45, 10, precision="fp32", rnn="lstm").cuda().eval()
+    with pytest.raises(ValueError), torch.no_grad():
+        net32(x.cuda(), L)                 # the LSTM cell exists in fast precision only
+
+
+def test_lstm_config4_long_sequence(mods):
+    """configs[3] with the LSTM cell: 1024 dependent steps keep the bf16-operand recurrence in gate."""
+    import torch
+    from artspeech_b200 import models, synthetic
+    from oracle import model as omodel
+    sd = omodel.randomize_affine(omodel.make_state_dict(45, 10, seed=0, cell="lstm"), seed=6)
+    net = models.ArtSpeech(45, 10, precision="fast", rnn="lstm")
+    net.load_state_dict(sd)
+    net = net.cuda().eval()
+    B, T = 64, 1024
+    x = synthetic.tokens(B, T, 45, seed=45)
+    L = synthetic.sorted_lengths(B, 300, T, seed=45)
+    with torch.no_grad():
+        out = net(x.cuda(), L)
+    torch.cuda.synchronize()
+    assert tuple(out.shape) == (B, T, 10, 2, 50) and not torch.isnan(out).any()
+    for b in [0, 31, 63]:
+        lb = int(L[b])
+        want = omodel.artspeech_forward(sd, x[b:b + 1], [lb], torch.float32)
+        err = float((out[b:b + 1, :lb].cpu() - want).abs().max())
+        assert err <= 2e-3, (b, err)
