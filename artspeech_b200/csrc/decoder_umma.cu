@@ -6,19 +6,56 @@
 //
 // Blackwell mapping
 //   * every GEMM is D[128 x N] = A[128 x K] . W[N x K]^T with tcgen05.mma kind::tf32 (fp32 accumulate):
-//     A (the activations) lives in TENSOR MEMORY (columns 256..511, one tf32 per column, lane = frame),
-//     D accumulates in tensor memory (columns 0..255), W is streamed from L2 into shared memory by
-//     1-D bulk async copies (UBLKCP) from a weight image that is pre-swizzled (128-byte swizzle,
-//     K-major) at model-creation time, so no tensor map is needed.
-//   * warp roles: warps 0-3 = epilogue (thread = frame = TMEM lane: bias, ReLU, LayerNorm, sigmoid are
-//     all thread-local, no cross-thread reduction), warp 4 = weight/parameter producer, warp 5 = MMA
-//     issuer (one elected thread).  Pipelines: weight ring full/empty mbarriers (tcgen05.commit frees
-//     a stage), per-articulator parameter double buffer, A-ready (epilogue -> MMA) and D-ready
-//     (tcgen05.commit -> epilogue) barriers.
+//     A (the activations) lives in TENSOR MEMORY (one tf32 per column, lane = frame), D accumulates
+//     in tensor memory, W is streamed from L2 into shared memory by 1-D bulk async copies (UBLKCP)
+//     from a weight image that is pre-swizzled (128-byte swizzle, K-major) at model-creation time,
+//     so no tensor map is needed.
+//   * the 512 TMEM columns are two 256-column regions that swap roles from layer to layer: a GEMM
+//     reads A from one region and accumulates into the other; the epilogue then turns that
+//     accumulator IN PLACE into the next GEMM's A operand, 32 columns at a time, and signals each
+//     32-column K chunk on its own mbarrier - so the next GEMM starts on chunk 0 while the epilogue
+//     is still converting chunks 1..7 (the tensor pipe and the epilogue warps overlap inside one
+//     tile).  The in-place single pass is possible because the LayerNorms are DEFERRED: with
+//     W' = W diag(gamma), b' = b + W beta folded at pack time,
+//        W' ((x - mean) rstd) + b' = rstd (W' x) + (b' - rstd mean (W' 1)),
+//     so the GEMM consumes the un-normalised relu output x (rounded to tf32 like before), the row
+//     moments are accumulated while x is produced, and the following epilogue applies rstd and the
+//     rank-1 mean term (W' 1 = row sums of the rounded weights, precomputed) as two FMAs.
+//   * warp roles: warps 0-7 = epilogue (thread = frame = TMEM lane, the two warps of a lane quarter
+//     own alternate 32-column chunks), warp 8 = weight/parameter producer, warp 9 = MMA issuer
+//     (one elected thread).  Pipelines: weight ring full/empty mbarriers (tcgen05.commit frees a
+//     stage), per-articulator parameter double buffer, per-K-chunk A-ready barriers (epilogue ->
+//     MMA) and a two-deep D-ready barrier (tcgen05.commit -> epilogue).  The A operand of the next
+//     articulator's first GEMM is written while the heads GEMM of the current one runs.
 //   * work unit = (128-frame tile, group of articulators); units are distributed round-robin over a
 //     persistent grid of one CTA per SM.
 #include "model.cuh"
 #include "umma.cuh"
+
+// timing ablations for tools/decoder_variants.py (results are wrong when set): 1 = epilogue without
+// arithmetic, 2 = epilogue without TMEM traffic either, 3 = no MMAs issued, 4 = no weight streaming
+#ifndef ASB_DEC_ABLATE
+#define ASB_DEC_ABLATE 0
+#endif
+
+#ifdef ASB_DEC_TRACE
+// timeline of CTA 0 (tools/decoder_trace.py): [role][event] = (tag, clock64) for the MMA thread (0),
+// lane 0 of epilogue warp 0 (1) and of epilogue warp 4 (2)
+__device__ long long g_dec_trace[3 * 4096];
+#define TR(role, tag)                                                     \
+  do {                                                                    \
+    if (blockIdx.x == 0 && lane == 0 && tr_n < 2047) {                    \
+      g_dec_trace[(role) * 4096 + 2 * tr_n] = (tag);                      \
+      g_dec_trace[(role) * 4096 + 2 * tr_n + 1] = clock64();              \
+      ++tr_n;                                                             \
+    }                                                                     \
+  } while (0)
+extern "C" __attribute__((visibility("default"))) int asb_debug_decoder_trace(long long* host_out) {
+  return int(cudaMemcpyFromSymbol(host_out, g_dec_trace, sizeof(g_dec_trace)));
+}
+#else
+#define TR(role, tag) do { } while (0)
+#endif
 
 namespace {
 
@@ -32,7 +69,6 @@ constexpr int kStages = 4;
 constexpr int kStageBytes = 256 * 128;      // 32 KB: up to 256 weight rows x 128 B
 constexpr int kXStride = 129;               // x-hat row stride (floats), conflict-free per-thread rows
 constexpr int kEpiWarps = 8;                // two warps per TMEM lane quarter, each owning half the columns
-constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kProducerWarp = 8, kMmaWarp = 9;
 constexpr int kThreads = 320;
 
@@ -42,10 +78,10 @@ constexpr int kLinParams = 128;
 constexpr int kLinChunk = 128 * kChunkK;    // 4096
 constexpr int kFcChunk = 256 * kChunkK;     // 8192
 constexpr int kHeadChunk = kHeadN * kChunkK;  // 3584
-constexpr int kArtParams = 640;             // b1' (256) | b2' (256) | bh' (128, zero padded)
+constexpr int kArtParams = 1024;            // b1' (256) | b2' (256) | W2'1 (256) | bh' (128, zero padded) | Wh'1 (128)
 constexpr int kLinBlock = kLinParams + 8 * kLinChunk;
 constexpr int kArtBlock = kArtParams + 4 * kFcChunk + 8 * kFcChunk + 8 * kHeadChunk;
-constexpr int P_B1 = 0, P_B2 = 256, P_BH = 512;
+constexpr int P_B1 = 0, P_B2 = 256, P_WS2 = 512, P_BH = 768, P_WSH = 896;
 
 // dynamic shared memory layout (bytes, base 1024-aligned)
 constexpr int kOffW = 0;
@@ -68,6 +104,16 @@ __global__ void pack_umma_kernel(const float* __restrict__ src, const float* __r
   const float w = scale ? src[i] * scale[k] : src[i];
   dst[off] = __uint_as_float(to_tf32(w));
 }
+// dst[n] = sum_k tf32(W[n][k] * scale[k]): row sums of the folded weights exactly as the tensor cores
+// see them (the mean term of the deferred LayerNorm)
+__global__ void fold_wsum_kernel(const float* __restrict__ W, const float* __restrict__ scale,
+                                 float* __restrict__ dst, int N, int K) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  double acc = 0.0;
+  for (int k = 0; k < K; ++k) acc += double(__uint_as_float(to_tf32(W[(size_t)n * K + k] * scale[k])));
+  dst[n] = float(acc);
+}
 // dst[n] = b[n] + sum_k W[n][k] * beta[k]   (beta may be null)
 __global__ void fold_bias_kernel(const float* __restrict__ W, const float* __restrict__ beta,
                                  const float* __restrict__ b, float* __restrict__ dst, int N, int K) {
@@ -83,6 +129,13 @@ __device__ __forceinline__ void bar_sync_epilogue() { asm volatile("bar.sync 1, 
 
 __device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
 
+// parameters are read with explicit shared-space loads (all threads read the same address: broadcast)
+__device__ __forceinline__ float4 lds4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+
 struct UmmaArgs {
   const float* image;    // weight image
   const float* rnn_out;  // (M, 256)
@@ -91,10 +144,15 @@ struct UmmaArgs {
   int n_art, D, group, n_groups, n_units;
 };
 
+// TMEM regions.  With p = parity of the articulator counter, P = region p, Q = the other one:
+//   linear.0 : A0 = Q[0,256)    -> D0 = P[0,128)                (epilogue: x-hat -> shared memory)
+//   FC1      : A1 = P[128,256)  -> D1 = Q[0,256)   in place ->  A2 = Q
+//   FC2      : A2 = Q           -> D2 = P[0,256)   in place ->  A3 = P
+//   heads    : A3 = P           -> D3 = Q[0,112)
+// and the next articulator (parity flipped) puts its A1 into Q[128,256) while the heads GEMM runs.
 __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArgs a) {
   extern __shared__ unsigned char smem_raw[];
-  unsigned char* smem =
-      reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // keeps the shared address space
   unsigned char* Ws = smem + kOffW;
   float* Xs = reinterpret_cast<float*>(smem + kOffX);
   float* Ps = reinterpret_cast<float*>(smem + kOffP);
@@ -105,11 +163,15 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
   uint64_t* empty = bars + 4;       // [kStages]  MMAs that read the stage completed
   uint64_t* pfull = bars + 8;       // [2]        articulator parameters landed
   uint64_t* pempty = bars + 10;     // [2]        epilogue finished with them
-  uint64_t* a_ready = bars + 12;    //            A operand + bias-initialised accumulator are in TMEM
-  uint64_t* d_ready = bars + 13;    //            accumulator complete
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+  uint64_t* chunk = bars + 12;      // [8]        32-column K chunk j of the A operand is in TMEM (K = 256 GEMMs)
+  uint64_t* a1bar = bars + 20;      // [4]        the same for the A operand of FC1 (K = 128)
+  uint64_t* d_ready = bars + 24;    // [2]        accumulator complete (alternating)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 26);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // CTAs walk the articulators of a unit in different (rotated) orders: all SMs streaming the same
+  // 32 KB weight chunk at the same moment would queue on the few L2 slices that hold it
+  auto rotated = [&](int g0, int g1, int k) { return g0 + (k + int(blockIdx.x)) % (g1 - g0); };
 
   if (tid == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -119,9 +181,10 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
     for (int s = 0; s < 2; ++s) {
       mbar_init(&pfull[s], 1);
       mbar_init(&pempty[s], kEpiWarps);
+      mbar_init(&d_ready[s], 1);
     }
-    mbar_init(a_ready, kEpiWarps);
-    mbar_init(d_ready, 1);
+    for (int j = 0; j < 8; ++j) mbar_init(&chunk[j], 4);   // the four lane quarters of the owning half
+    for (int j = 0; j < 4; ++j) mbar_init(&a1bar[j], 4);
     fence_mbar_init();
   }
   if (warp == kMmaWarp) tmem_alloc(tmem_slot, 512);
@@ -130,14 +193,13 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
   __syncthreads();
   fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_d = tmem_base;         // accumulator columns [0, 256)
-  const uint32_t tmem_a = tmem_base + 256;   // A operand columns [256, 512)
 
   if (warp == kProducerWarp) {
     // ===================== producer: weight chunks and articulator parameters =====================
     if (lane == 0) {
       uint32_t c = 0, pa = 0;
       auto push = [&](const float* src, uint32_t bytes) {
+        if (ASB_DEC_ABLATE == 4) return;
         const uint32_t s = c % kStages;
         mbar_wait(&empty[s], ((c / kStages) & 1) ^ 1);
         mbar_arrive_expect_tx(&full[s], bytes);
@@ -148,7 +210,8 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
         const int grp = u % a.n_groups;
         const int g0 = grp * a.group, g1 = min(a.n_art, g0 + a.group);
         for (int j = 0; j < 8; ++j) push(a.image + kLinParams + j * kLinChunk, kLinChunk * 4);
-        for (int art = g0; art < g1; ++art) {
+        for (int k = 0; k < g1 - g0; ++k) {
+          const int art = rotated(g0, g1, k);
           const float* blk = a.image + kLinBlock + (size_t)art * kArtBlock;
           const uint32_t pb = pa & 1;
           mbar_wait(&pempty[pb], ((pa >> 1) & 1) ^ 1);
@@ -168,109 +231,165 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
   } else if (warp == kMmaWarp) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      uint32_t c = 0, gcount = 0;
-      auto gemm = [&](uint32_t n, int k_chunks) {
-        mbar_wait(a_ready, gcount & 1);
-        fence_after_sync();
+      uint32_t c = 0, gcount = 0, artc = 0, ph_chunk = 0, ph_a1 = 0;
+      int tr_n = 0;
+      (void)tr_n;
+      // K chunk j is issued as soon as its 32 A columns are in TMEM and its weights are in shared
+      // memory.  `whole_cta`: the accumulator region still holds columns that warps of BOTH halves
+      // may be reading (the previous heads output), so the first (overwriting) MMA also waits for
+      // chunk 1, which the other half signals only after it has finished reading.
+      auto gemm = [&](uint32_t d_tmem, uint32_t a_tmem, uint32_t n, int k_chunks, uint64_t* abar, uint32_t& ph,
+                      bool whole_cta) {
         const uint32_t idesc = idesc_tf32_m128(n);
+        TR(0, 100 + n);
         for (int j = 0; j < k_chunks; ++j) {
+          mbar_wait(&abar[j], (ph >> j) & 1);
+          TR(0, 10 + j);
+          if (j == 0 && whole_cta) mbar_wait(&abar[1], (ph >> 1) & 1);
+          ph ^= 1u << j;
+          fence_after_sync();
           const uint32_t s = c % kStages;
-          mbar_wait(&full[s], (c / kStages) & 1);
+          if (ASB_DEC_ABLATE != 4) mbar_wait(&full[s], (c / kStages) & 1);
           fence_after_sync();
           const uint64_t bdesc = smem_desc_k_sw128(smem_u32(Ws + s * kStageBytes));
 #pragma unroll
-          for (int ks = 0; ks < 4; ++ks)  // the accumulator was pre-loaded with the bias: always accumulate
-            mma_tf32_ts(tmem_d, tmem_a + j * kChunkK + ks * 8, bdesc + uint64_t(2 * ks), idesc, true);
-          commit(&empty[s]);  // frees the stage once these MMAs have read it
+          for (int ks = 0; ks < (ASB_DEC_ABLATE == 3 ? 0 : 4); ++ks)
+            mma_tf32_ts(d_tmem, a_tmem + j * kChunkK + ks * 8, bdesc + uint64_t(2 * ks), idesc, (j | ks) != 0);
+          if (ASB_DEC_ABLATE != 4) commit(&empty[s]);  // frees the stage once these MMAs have read it
           ++c;
         }
-        commit(d_ready);
+        commit(&d_ready[gcount & 1]);
+        TR(0, 99);
         ++gcount;
       };
       for (int u = blockIdx.x; u < a.n_units; u += gridDim.x) {
         const int grp = u % a.n_groups;
         const int g0 = grp * a.group, g1 = min(a.n_art, g0 + a.group);
-        gemm(128, 8);                       // linear.0          K = 256
-        for (int art = g0; art < g1; ++art) {
-          gemm(256, 4);                     // Linear(128, 256)
-          gemm(256, 8);                     // Linear(256, 256)
-          gemm(kHeadN, 8);                  // x/y heads
+        {
+          const uint32_t P = tmem_base + (artc & 1) * 256, Q = tmem_base + ((artc & 1) ^ 1) * 256;
+          gemm(P, Q, 128, 8, chunk, ph_chunk, true);            // linear.0          K = 256
+        }
+        for (int k = 0; k < g1 - g0; ++k) {
+          const uint32_t P = tmem_base + (artc & 1) * 256, Q = tmem_base + ((artc & 1) ^ 1) * 256;
+          gemm(Q, P + 128, 256, 4, a1bar, ph_a1, false);        // Linear(128, 256)
+          gemm(P, Q, 256, 8, chunk, ph_chunk, true);            // Linear(256, 256)
+          gemm(Q, P, kHeadN, 8, chunk, ph_chunk, false);        // x/y heads
+          ++artc;
         }
       }
     }
     __syncwarp();
   } else {
-    // ===================== epilogue: thread = (frame = TMEM lane, half of the columns) ============
+    // ===================== epilogue: thread = (frame = TMEM lane, alternate 32-column chunks) ======
     const int quarter = warp & 3, half = warp >> 2;
     const int row = quarter * 32 + lane;
     const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
-    const uint32_t td = tmem_d + lane_sel, ta = tmem_a + lane_sel;
     float* xrow = Xs + row * kXStride;
-    uint32_t gcount = 0, pa = 0, use = 0;
+    const uint32_t ps_addr = smem_u32(Ps), linb_addr = smem_u32(LinB);
+    uint32_t gcount = 0, pa = 0, use = 0, artc = 0;
     uint32_t r[32];
+    int tr_n = 0;
+    (void)tr_n;
+    const int tr_role = 1 + half;
+    (void)tr_role;
 
-    auto signal_a = [&]() {
+    auto wait_d = [&]() {
+      mbar_wait(&d_ready[gcount & 1], (gcount >> 1) & 1);
+      ++gcount;
+      fence_after_sync();
+      if (quarter == 0) TR(tr_role, 200);
+    };
+    // the A columns just stored are complete for this warp's 32 lanes: one arrival per warp
+    auto signal = [&](uint64_t* bar) {
       tmem_st_wait();
       fence_before_sync();
       __syncwarp();
-      if (lane == 0) mbar_arrive(a_ready);
+      if (lane == 0) mbar_arrive(bar);
+      if (quarter == 0) TR(tr_role, 201);
     };
-    auto wait_d = [&]() {
-      mbar_wait(d_ready, gcount & 1);
-      ++gcount;
-      fence_after_sync();
-    };
-    // row moments are split over the two column halves: exchange the partial sums through smem
-    auto exchange = [&](float& s, float& ss) {
+    // row moments are split over the two halves: each half publishes its partial sums after a layer
+    // and reads the partner's before the next one (ordered by the chunk -> MMA -> D-ready chain)
+    float own_s = 0.f, own_ss = 0.f;
+    auto publish = [&](float s, float ss) {
+      own_s = s;
+      own_ss = ss;
       Stat[((use & 1) * 2 + half) * kTileM + row] = make_float2(s, ss);
-      bar_sync_epilogue();
+    };
+    auto moments = [&](float inv_n, float& rstd, float& nm) {
       const float2 o = Stat[((use & 1) * 2 + (half ^ 1)) * kTileM + row];
-      s += o.x;
-      ss += o.y;
       ++use;
+      const float mean = (own_s + o.x) * inv_n;
+      const float var = fmaxf((own_ss + o.y) * inv_n - mean * mean, 0.f);
+      rstd = rsqrtf(var + 1e-5f);
+      nm = -mean * rstd;
     };
-    // pre-load this thread's accumulator columns [col0, col0 + 32 * chunks) with the next layer's bias
-    auto init_d = [&](const float* bias, int col0, int chunks) {
-      bar_sync_epilogue();  // the partner may still be reading columns that change owner
-      for (int c = 0; c < chunks; ++c) {
+    // accumulator -> relu(rs * D + (b + nm * ws)) -> moments, tf32 -> the same columns, chunk by chunk.
+    // The TMEM load of the next chunk is in flight while this one is converted; the arithmetic is
+    // packed fp32x2 (FFMA2 / FADD2) except the relu and the integer rounding.
+    uint32_t r2[32];
+    auto convert_in_place = [&](uint32_t region, uint32_t b_addr, uint32_t ws_addr, float rs, float nm,
+                                bool deferred) {
+      const f32x2 rs2 = pack2(rs, rs), nm2 = pack2(nm, nm), one2 = pack2(1.f, 1.f);
+      f32x2 sa = pack2(0.f, 0.f), sb = sa, qa = sa, qb = sa;
+      auto body = [&](uint32_t(&buf)[32], int ch) {
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const float4 b4 = *reinterpret_cast<const float4*>(bias + col0 + 32 * c + 4 * q);
-          r[4 * q + 0] = __float_as_uint(b4.x);
-          r[4 * q + 1] = __float_as_uint(b4.y);
-          r[4 * q + 2] = __float_as_uint(b4.z);
-          r[4 * q + 3] = __float_as_uint(b4.w);
+        for (int q = 0; q < (ASB_DEC_ABLATE == 1 || ASB_DEC_ABLATE == 2 ? 0 : 8); ++q) {
+          const float4 b4 = lds4(b_addr + (32 * ch + 4 * q) * 4);
+          f32x2 k01 = pack2(b4.x, b4.y), k23 = pack2(b4.z, b4.w);
+          if (deferred) {
+            const float4 w4 = lds4(ws_addr + (32 * ch + 4 * q) * 4);
+            k01 = fma2(nm2, pack2(w4.x, w4.y), k01);
+            k23 = fma2(nm2, pack2(w4.z, w4.w), k23);
+          }
+          float v0, v1, v2, v3;
+          unpack2(fma2(rs2, pack2(__uint_as_float(buf[4 * q + 0]), __uint_as_float(buf[4 * q + 1])), k01), v0, v1);
+          unpack2(fma2(rs2, pack2(__uint_as_float(buf[4 * q + 2]), __uint_as_float(buf[4 * q + 3])), k23), v2, v3);
+          v0 = fmaxf(v0, 0.f);
+          v1 = fmaxf(v1, 0.f);
+          v2 = fmaxf(v2, 0.f);
+          v3 = fmaxf(v3, 0.f);
+          const f32x2 p01 = pack2(v0, v1), p23 = pack2(v2, v3);
+          sa = fma2(p01, one2, sa);
+          sb = fma2(p23, one2, sb);
+          qa = fma2(p01, p01, qa);
+          qb = fma2(p23, p23, qb);
+          buf[4 * q + 0] = to_tf32_finite(v0);
+          buf[4 * q + 1] = to_tf32_finite(v1);
+          buf[4 * q + 2] = to_tf32_finite(v2);
+          buf[4 * q + 3] = to_tf32_finite(v3);
         }
-        tmem_st32(td + col0 + 32 * c, r);
+        if (ASB_DEC_ABLATE != 2) tmem_st32(region + 32 * ch, buf);
+        signal(&chunk[ch]);
+      };
+      if (ASB_DEC_ABLATE != 2) tmem_ld32(region + 32 * half, r);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int ch = 2 * c + half;
+        tmem_ld_wait();
+        if (c & 1) {
+          if (c < 3 && ASB_DEC_ABLATE != 2) tmem_ld32(region + 32 * (ch + 2), r);
+          body(r2, ch);
+        } else {
+          if (c < 3 && ASB_DEC_ABLATE != 2) tmem_ld32(region + 32 * (ch + 2), r2);
+          body(r, ch);
+        }
       }
+      float s0, s1, s2, s3, q0, q1, q2, q3;
+      unpack2(sa, s0, s1);
+      unpack2(sb, s2, s3);
+      unpack2(qa, q0, q1);
+      unpack2(qb, q2, q3);
+      publish((s0 + s1) + (s2 + s3), (q0 + q1) + (q2 + q3));
     };
-    // relu(D) -> LayerNorm(256) without affine (folded into the next layer) -> tf32 -> A
-    auto ln256_to_a = [&]() {
-      const int col0 = half * 128;
-      float s = 0.f, ss = 0.f;
+    // x-hat (shared memory) -> A operand of FC1 in region[128, 256)
+    auto write_a1 = [&](uint32_t region) {
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        tmem_ld32(td + col0 + 32 * c, r);
-        tmem_ld_wait();
+      for (int c = 0; c < 2; ++c) {
+        const int ch = 2 * c + half;
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float v = fmaxf(__uint_as_float(r[i]), 0.f);
-          s += v;
-          ss = fmaf(v, v, ss);
-        }
-      }
-      exchange(s, ss);
-      const float mean = s * (1.f / 256.f);
-      const float var = fmaxf(ss * (1.f / 256.f) - mean * mean, 0.f);
-      const float rstd = rsqrtf(var + 1e-5f);
-      const float shift = -mean * rstd;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        tmem_ld32(td + col0 + 32 * c, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) r[i] = to_tf32(fmaf(fmaxf(__uint_as_float(r[i]), 0.f), rstd, shift));
-        tmem_st32(ta + col0 + 32 * c, r);
+        for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(xrow[32 * ch + i]);
+        tmem_st32(region + 128 + 32 * ch, r);
+        signal(&a1bar[ch]);
       }
     };
 
@@ -280,96 +399,99 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
       const long long grow = (long long)tile * kTileM + row;
       const bool live = grow < a.M;
 
-      // ---- input tile -> A (tf32): this thread converts 128 of its frame's 256 features
+      // ---- input tile -> A0 (tf32) in Q: this thread converts 128 of its frame's 256 features
       {
-        const float4* src = reinterpret_cast<const float4*>(a.rnn_out + grow * 256 + half * 128);
+        const uint32_t P = tmem_base + lane_sel + (artc & 1) * 256, Q = tmem_base + lane_sel + ((artc & 1) ^ 1) * 256;
+        const float4* src = reinterpret_cast<const float4*>(a.rnn_out + grow * 256);
 #pragma unroll 1
         for (int c = 0; c < 4; ++c) {
+          const int ch = 2 * c + half;
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (live) v = __ldg(src + 8 * c + q);
+            if (live) v = __ldg(src + 8 * ch + q);
             r[4 * q + 0] = to_tf32(v.x);
             r[4 * q + 1] = to_tf32(v.y);
             r[4 * q + 2] = to_tf32(v.z);
             r[4 * q + 3] = to_tf32(v.w);
           }
-          tmem_st32(ta + half * 128 + 32 * c, r);
+          tmem_st32(Q + 32 * ch, r);
+          signal(&chunk[ch]);
         }
-        init_d(LinB, half * 64, 2);
-        signal_a();
-      }
-      // ---- linear.0 epilogue: relu(D) -> LayerNorm(128) statistics -> x-hat kept in shared memory
-      wait_d();
-      {
-        const int col0 = half * 64;
+        // ---- linear.0 epilogue: relu(D0 + b) -> LayerNorm(128) -> x-hat (tf32) kept in shared memory
+        wait_d();
         float s = 0.f, ss = 0.f;
 #pragma unroll 1
         for (int c = 0; c < 2; ++c) {
-          tmem_ld32(td + col0 + 32 * c, r);
+          const int ch = 2 * c + half;
+          tmem_ld32(P + 32 * ch, r);
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const float v = fmaxf(__uint_as_float(r[i]), 0.f);
-            xrow[col0 + 32 * c + i] = v;
-            s += v;
-            ss = fmaf(v, v, ss);
+          for (int q = 0; q < 8; ++q) {
+            const float4 b4 = lds4(linb_addr + (32 * ch + 4 * q) * 4);
+            const float v0 = fmaxf(__uint_as_float(r[4 * q + 0]) + b4.x, 0.f);
+            const float v1 = fmaxf(__uint_as_float(r[4 * q + 1]) + b4.y, 0.f);
+            const float v2 = fmaxf(__uint_as_float(r[4 * q + 2]) + b4.z, 0.f);
+            const float v3 = fmaxf(__uint_as_float(r[4 * q + 3]) + b4.w, 0.f);
+            xrow[32 * ch + 4 * q + 0] = v0;
+            xrow[32 * ch + 4 * q + 1] = v1;
+            xrow[32 * ch + 4 * q + 2] = v2;
+            xrow[32 * ch + 4 * q + 3] = v3;
+            s += (v0 + v1) + (v2 + v3);
+            ss = fmaf(v0, v0, fmaf(v1, v1, fmaf(v2, v2, fmaf(v3, v3, ss))));
           }
         }
-        exchange(s, ss);
-        const float mean = s * (1.f / 128.f);
-        const float var = fmaxf(ss * (1.f / 128.f) - mean * mean, 0.f);
-        const float rstd = rsqrtf(var + 1e-5f);
-        const float shift = -mean * rstd;
+        publish(s, ss);
+        bar_sync_epilogue();   // once per unit: the partner's partial sums are needed right away
+        float rstd, nm;
+        moments(1.f / 128.f, rstd, nm);
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+          const int ch = 2 * c + half;
 #pragma unroll 8
-        for (int k = 0; k < 64; ++k)
-          xrow[col0 + k] = __uint_as_float(to_tf32(fmaf(xrow[col0 + k], rstd, shift)));
+          for (int k = 0; k < 32; ++k)
+            xrow[32 * ch + k] = __uint_as_float(to_tf32_finite(fmaf(xrow[32 * ch + k], rstd, nm)));
+        }
+        write_a1(P);
       }
 
-      for (int art = g0; art < g1; ++art) {
+      for (int k = 0; k < g1 - g0; ++k) {
+        const int art = rotated(g0, g1, k);
+        const uint32_t P = tmem_base + lane_sel + (artc & 1) * 256, Q = tmem_base + lane_sel + ((artc & 1) ^ 1) * 256;
         const uint32_t pb = pa & 1;
-        const float* P = Ps + pb * kArtParams;
+        const uint32_t prm = ps_addr + pb * kArtParams * 4;
         mbar_wait(&pfull[pb], (pa >> 1) & 1);
-        // ---- x-hat -> A (the LayerNorm(128) affine of this articulator lives in its folded W1', b1')
-        {
-          const int col0 = half * 64;
-#pragma unroll 1
-          for (int c = 0; c < 2; ++c) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(xrow[col0 + 32 * c + i]);
-            tmem_st32(ta + col0 + 32 * c, r);
-          }
-        }
-        init_d(P + P_B1, half * 128, 4);
-        signal_a();
-        wait_d();
-        ln256_to_a();
-        init_d(P + P_B2, half * 128, 4);
-        signal_a();
-        wait_d();
-        ln256_to_a();
-        init_d(P + P_BH, half * 64, 2);
-        signal_a();
-        wait_d();
-        // ---- heads: sigmoid(D) -> contours in their final layout (this thread: 64 of the 100 columns)
+        float rstd, nm;
+        wait_d();                                             // FC1 done: D1 in Q
+        convert_in_place(Q, prm + P_B1 * 4, 0u, 1.f, 0.f, false);
+        wait_d();                                             // FC2 done: D2 in P
+        moments(1.f / 256.f, rstd, nm);
+        convert_in_place(P, prm + P_B2 * 4, prm + P_WS2 * 4, rstd, nm, true);
+        if (k + 1 < g1 - g0) write_a1(Q);                      // next articulator's FC1 operand, under the heads GEMM
+        wait_d();                                             // heads done: D3 in Q[0, 112)
+        moments(1.f / 256.f, rstd, nm);
+        if (quarter == 0) TR(tr_role, 300);
+        // ---- heads: sigmoid(rstd * D3 + ...) -> contours in their final layout
         {
           float* dst = a.out + (grow * a.n_art + art) * 100;
 #pragma unroll 1
           for (int c = 0; c < 2; ++c) {
-            const int cbase = half * 64 + 32 * c;
+            const int cbase = 32 * (2 * c + half);
             if (cbase < 100) {  // warp-uniform
-              tmem_ld32(td + cbase, r);
+              tmem_ld32(Q + cbase, r);
               tmem_ld_wait();
               if (live) {
 #pragma unroll
                 for (int q = 0; q < 8; ++q) {
                   const int col = cbase + 4 * q;
                   if (col < 100) {
+                    const float4 b4 = lds4(prm + (P_BH + col) * 4);
+                    const float4 w4 = lds4(prm + (P_WSH + col) * 4);
                     float4 o;
-                    o.x = sigmoid_fast(__uint_as_float(r[4 * q + 0]));
-                    o.y = sigmoid_fast(__uint_as_float(r[4 * q + 1]));
-                    o.z = sigmoid_fast(__uint_as_float(r[4 * q + 2]));
-                    o.w = sigmoid_fast(__uint_as_float(r[4 * q + 3]));
+                    o.x = sigmoid_fast(fmaf(rstd, __uint_as_float(r[4 * q + 0]), fmaf(nm, w4.x, b4.x)));
+                    o.y = sigmoid_fast(fmaf(rstd, __uint_as_float(r[4 * q + 1]), fmaf(nm, w4.y, b4.y)));
+                    o.z = sigmoid_fast(fmaf(rstd, __uint_as_float(r[4 * q + 2]), fmaf(nm, w4.z, b4.z)));
+                    o.w = sigmoid_fast(fmaf(rstd, __uint_as_float(r[4 * q + 3]), fmaf(nm, w4.w, b4.w)));
                     *reinterpret_cast<float4*>(dst + col) = o;
                   }
                 }
@@ -380,7 +502,9 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
         fence_before_sync();
         __syncwarp();
         if (lane == 0) mbar_arrive(&pempty[pb]);
+        if (quarter == 0) TR(tr_role, 301);
         ++pa;
+        ++artc;
       }
     }
   }
@@ -406,6 +530,11 @@ static int pack_mat(const float* src, const float* scale, float* dst, int n_src,
   const int n = n_src * K;
   pack_umma_kernel<<<(n + 255) / 256, 256, 0, st>>>(src, scale, dst, n_src, row0, n_pad, K);
   ASB_CHECK_LAUNCH("pack_umma_kernel");
+  return ASB_OK;
+}
+static int fold_wsum(const float* W, const float* scale, float* dst, int N, int K, cudaStream_t st) {
+  fold_wsum_kernel<<<(N + 127) / 128, 128, 0, st>>>(W, scale, dst, N, K);
+  ASB_CHECK_LAUNCH("fold_wsum_kernel");
   return ASB_OK;
 }
 static int fold_bias(const float* W, const float* beta, const float* b, float* dst, int N, int K, cudaStream_t st) {
@@ -434,6 +563,9 @@ int pack_umma_image(asb_model* m, const asb_weights* s, cudaStream_t st) {
     ASB_TRY(fold_bias(s->fc2_w[i], s->ln1_b[i], s->fc2_b[i], blk + P_B2, kFc, kFc, st));
     ASB_TRY(fold_bias(s->xh_w[i], s->ln2_b[i], s->xh_b[i], blk + P_BH, D, kFc, st));
     ASB_TRY(fold_bias(s->yh_w[i], s->ln2_b[i], s->yh_b[i], blk + P_BH + D, D, kFc, st));
+    ASB_TRY(fold_wsum(s->fc2_w[i], s->ln1_w[i], blk + P_WS2, kFc, kFc, st));
+    ASB_TRY(fold_wsum(s->xh_w[i], s->ln2_w[i], blk + P_WSH, D, kFc, st));
+    ASB_TRY(fold_wsum(s->yh_w[i], s->ln2_w[i], blk + P_WSH + D, D, kFc, st));
     float* w1 = blk + kArtParams;
     float* w2 = w1 + 4 * kFcChunk;
     float* wh = w2 + 8 * kFcChunk;

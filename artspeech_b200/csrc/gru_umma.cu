@@ -67,8 +67,7 @@ struct RnnArgs {
 template <int G, int CPT>
 __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) {
   extern __shared__ unsigned char smem_raw[];
-  unsigned char* smem =
-      reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // keeps the shared address space
   unsigned char* Wsm = smem;                         // G x 32 KB
   unsigned char* Hs = smem + G * kTileBytes;         // 4 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(Hs + kHsBytes);

@@ -65,8 +65,7 @@ struct ProjArgs {
 
 __global__ void __launch_bounds__(kThreads, 1) proj_umma_kernel(const ProjArgs a) {
   extern __shared__ unsigned char smem_raw[];
-  unsigned char* smem =
-      reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // keeps the shared address space
   float* Ws = reinterpret_cast<float*>(smem + kOffW);
   float* Bs = reinterpret_cast<float*>(smem + kOffBias);
   float* Ts = reinterpret_cast<float*>(smem + kOffTile);

@@ -137,5 +137,9 @@ __device__ __forceinline__ uint32_t to_tf32(float x) {
   return r;
 }
 
+// the same rounding (nearest, ties away) for FINITE values in two integer instructions instead of the
+// three cvt.rna.tf32.f32 expands to (its NaN/Inf guard is not needed behind a relu / LayerNorm)
+__device__ __forceinline__ uint32_t to_tf32_finite(float x) { return (__float_as_uint(x) + 0x1000u) & 0xffffe000u; }
+
 }  // namespace umma
 }  // namespace asb

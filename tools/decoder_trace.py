@@ -1,0 +1,35 @@
+"""Timeline of CTA 0 of the tcgen05 decoder (library built by tools/build_variant.py with -DASB_DEC_TRACE)."""
+import ctypes
+import os
+import sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from artspeech_b200 import _lib
+_lib.LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_var_dec_trace.so")
+from artspeech_b200 import models, synthetic
+
+net = models.ArtSpeech(45, 10, precision="fast").cuda().eval()
+x = synthetic.tokens(256, 100, 45, seed=5).cuda()
+L = [100] * 256
+with torch.no_grad():
+    for _ in range(3):
+        net(x, L)
+torch.cuda.synchronize()
+buf = (ctypes.c_longlong * (3 * 4096))()
+fn = _lib.lib().asb_debug_decoder_trace
+fn.argtypes = [ctypes.POINTER(ctypes.c_longlong)]
+assert fn(buf) == 0
+ev = []
+for role in range(3):
+    for i in range(2047):
+        tag, t = buf[role * 4096 + 2 * i], buf[role * 4096 + 2 * i + 1]
+        if t == 0:
+            break
+        ev.append((t, role, tag))
+ev.sort()
+t0 = ev[0][0]
+names = {99: "commit D", 200: "D ready seen", 201: "chunk signalled", 300: "heads begin", 301: "heads end"}
+limit = int(sys.argv[1]) if len(sys.argv) > 1 else 260
+for t, role, tag in ev[:limit]:
+    what = names.get(tag, f"gemm N={tag - 100} begin" if tag >= 100 else f"A chunk {tag - 10} ready")
+    print(f"{t - t0:8d}  {'MMA ' if role == 0 else 'EPI' + str(role - 1)}  {what}")
