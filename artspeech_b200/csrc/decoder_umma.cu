@@ -23,12 +23,15 @@
 //     rank-1 mean term (W' 1 = row sums of the rounded weights, precomputed) as two FMAs.
 //   * warp roles: warps 0-7 = epilogue (thread = frame = TMEM lane, the two warps of a lane quarter
 //     own alternate 32-column chunks), warp 8 = weight/parameter producer, warp 9 = MMA issuer
-//     (one elected thread).  Pipelines: weight ring full/empty mbarriers (tcgen05.commit frees a
-//     stage), per-articulator parameter double buffer, per-K-chunk A-ready barriers (epilogue ->
-//     MMA) and a two-deep D-ready barrier (tcgen05.commit -> epilogue).  The A operand of the next
-//     articulator's first GEMM is written while the heads GEMM of the current one runs.
-//   * work unit = (128-frame tile, group of articulators); units are distributed round-robin over a
-//     persistent grid of one CTA per SM.
+//     (converged warp, one elected lane), warps 10-13 = output (heads accumulator -> sigmoid ->
+//     global memory, off the epilogue's critical path).  Pipelines: 4-stage 32 KB weight ring with
+//     full/empty mbarriers (tcgen05.commit frees a stage), per-articulator parameter double buffer,
+//     per-K-chunk A-ready barriers (epilogue -> MMA), one D-complete barrier per layer
+//     (tcgen05.commit -> epilogue / output warps) and a heads-accumulator-read barrier (output ->
+//     MMA).  The A operand of the next articulator's first GEMM is written while the heads GEMM of
+//     the current one runs.
+//   * work = the (tile, articulator) pairs, tile-major, cut into one contiguous range per CTA of a
+//     persistent grid (one CTA per SM); see UnitIter.
 #include "model.cuh"
 #include "umma.cuh"
 
@@ -40,8 +43,8 @@
 
 #ifdef ASB_DEC_TRACE
 // timeline of CTA 0 (tools/decoder_trace.py): [role][event] = (tag, clock64) for the MMA thread (0),
-// lane 0 of epilogue warp 0 (1) and of epilogue warp 4 (2)
-__device__ long long g_dec_trace[3 * 4096];
+// lane 0 of epilogue warp 0 (1) and of epilogue warp 4 (2), the producer thread (3), lane 0 of the output warps (4..7)
+__device__ long long g_dec_trace[8 * 4096];
 #define TR(role, tag)                                                     \
   do {                                                                    \
     if (blockIdx.x == 0 && lane == 0 && tr_n < 2047) {                    \
@@ -53,8 +56,10 @@ __device__ long long g_dec_trace[3 * 4096];
 extern "C" __attribute__((visibility("default"))) int asb_debug_decoder_trace(long long* host_out) {
   return int(cudaMemcpyFromSymbol(host_out, g_dec_trace, sizeof(g_dec_trace)));
 }
+#define TR_DECL int tr_n = 0
 #else
 #define TR(role, tag) do { } while (0)
+#define TR_DECL do { } while (0)
 #endif
 
 namespace {
@@ -65,12 +70,13 @@ using namespace asb::umma;
 constexpr int kTileM = 128;
 constexpr int kHeadN = 112;                 // 2 * 50 head rows padded to a multiple of 16
 constexpr int kChunkK = 32;                 // tf32 per 128-byte swizzle row
-constexpr int kStages = 4;
-constexpr int kStageBytes = 256 * 128;      // 32 KB: up to 256 weight rows x 128 B
+constexpr int kStages = 4;                  // weight ring: 32 KB stages = one 256-row K chunk or two 128- / 112-row ones
+constexpr int kStageBytes = 256 * 128;
 constexpr int kXStride = 129;               // x-hat row stride (floats), conflict-free per-thread rows
 constexpr int kEpiWarps = 8;                // two warps per TMEM lane quarter, each owning half the columns
 constexpr int kProducerWarp = 8, kMmaWarp = 9;
-constexpr int kThreads = 320;
+constexpr int kHeadWarp0 = 10, kHeadWarps = 4;   // warps 10..13: output warps, TMEM lane quarter = warp % 4
+constexpr int kThreads = 32 * (kHeadWarp0 + kHeadWarps);
 
 // weight image (floats).  LayerNorm affines are folded into the following layer at pack time:
 // W' = W . diag(gamma), b' = b + W . beta, so the kernel only normalises.
@@ -88,9 +94,9 @@ constexpr int kOffW = 0;
 constexpr int kOffX = kOffW + kStages * kStageBytes;
 constexpr int kOffP = kOffX + kTileM * kXStride * 4;
 constexpr int kOffLinB = kOffP + 2 * kArtParams * 4;
-constexpr int kOffStat = kOffLinB + kLinParams * 4;       // float2 [2 uses][2 halves][128 rows]
-constexpr int kOffBar = kOffStat + 2 * 2 * kTileM * 8;
-constexpr int kSmemBytes = kOffBar + 256 + 1024;  // + barriers + alignment slack
+constexpr int kOffStat = kOffLinB + kLinParams * 4;       // float2 [8][128 rows]: see Stat0/1/2 in the kernel
+constexpr int kOffBar = kOffStat + 8 * kTileM * 8;
+constexpr int kSmemBytes = kOffBar + 512 + 1024;  // + barriers + alignment slack
 
 // dst image of (W . diag(scale))[N][K] as K/32 chunks of [Npad rows][32] with the 128-byte swizzle
 __global__ void pack_umma_kernel(const float* __restrict__ src, const float* __restrict__ scale,
@@ -107,27 +113,34 @@ __global__ void pack_umma_kernel(const float* __restrict__ src, const float* __r
 // dst[n] = sum_k tf32(W[n][k] * scale[k]): row sums of the folded weights exactly as the tensor cores
 // see them (the mean term of the deferred LayerNorm)
 __global__ void fold_wsum_kernel(const float* __restrict__ W, const float* __restrict__ scale,
-                                 float* __restrict__ dst, int N, int K) {
+                                 float* __restrict__ dst, int N, int K, double out_scale) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   double acc = 0.0;
   for (int k = 0; k < K; ++k) acc += double(__uint_as_float(to_tf32(W[(size_t)n * K + k] * scale[k])));
-  dst[n] = float(acc);
+  dst[n] = float(acc * out_scale);
 }
 // dst[n] = b[n] + sum_k W[n][k] * beta[k]   (beta may be null)
 __global__ void fold_bias_kernel(const float* __restrict__ W, const float* __restrict__ beta,
-                                 const float* __restrict__ b, float* __restrict__ dst, int N, int K) {
+                                 const float* __restrict__ b, float* __restrict__ dst, int N, int K,
+                                 double out_scale) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   double acc = double(b[n]);
   if (beta)
     for (int k = 0; k < K; ++k) acc += double(W[(size_t)n * K + k]) * double(beta[k]);
-  dst[n] = float(acc);
+  dst[n] = float(acc * out_scale);
 }
 
 __device__ __forceinline__ void bar_sync_epilogue() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
-__device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+// 1 / (1 + 2^t): the sigmoid of z with t = -log2(e) z (the factor is folded into the head parameters)
+__device__ __forceinline__ float sigmoid_exp2(float t) {
+  float e, y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(1.f + e));
+  return y;
+}
 
 // parameters are read with explicit shared-space loads (all threads read the same address: broadcast)
 __device__ __forceinline__ float4 lds4(uint32_t addr) {
@@ -141,15 +154,35 @@ struct UmmaArgs {
   const float* rnn_out;  // (M, 256)
   float* out;            // (M, n_art, 2, D)
   long long M;
-  int n_art, D, group, n_groups, n_units;
+  int n_art, D;
+  long long n_items;    // (tile, articulator) pairs = tiles * n_art
+};
+
+// Work distribution: the (tile, articulator) pairs, tile-major, are cut into gridDim.x contiguous
+// ranges of equal length; a range is walked as units = (tile, run of articulators of that tile), and
+// linear.0 is (re)computed once per unit.  Every warp role iterates the same sequence.
+struct UnitIter {
+  long long item, hi;
+  int n_art;
+  __device__ UnitIter(const UmmaArgs& a)
+      : item(a.n_items * blockIdx.x / gridDim.x), hi(a.n_items * (blockIdx.x + 1) / gridDim.x), n_art(a.n_art) {}
+  __device__ bool next(int& tile, int& g0, int& g1) {
+    if (item >= hi) return false;
+    tile = int(item / n_art);
+    g0 = int(item - (long long)tile * n_art);
+    g1 = int(min((long long)n_art, g0 + (hi - item)));
+    item += g1 - g0;
+    return true;
+  }
 };
 
 // TMEM regions.  With p = parity of the articulator counter, P = region p, Q = the other one:
 //   linear.0 : A0 = Q[0,256)    -> D0 = P[0,128)                (epilogue: x-hat -> shared memory)
 //   FC1      : A1 = P[128,256)  -> D1 = Q[0,256)   in place ->  A2 = Q
 //   FC2      : A2 = Q           -> D2 = P[0,256)   in place ->  A3 = P
-//   heads    : A3 = P           -> D3 = Q[0,112)
-// and the next articulator (parity flipped) puts its A1 into Q[128,256) while the heads GEMM runs.
+//   heads    : A3 = P           -> D3 = Q[0,112)                (read by the output warps)
+// and the next articulator (parity flipped) puts its A1 into Q[128,256) while the heads GEMM runs;
+// its FC1 and the first FC2 epilogue chunks overlap the output warps' sigmoid + stores.
 __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArgs a) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // keeps the shared address space
@@ -157,21 +190,21 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
   float* Xs = reinterpret_cast<float*>(smem + kOffX);
   float* Ps = reinterpret_cast<float*>(smem + kOffP);
   float* LinB = reinterpret_cast<float*>(smem + kOffLinB);
-  float2* Stat = reinterpret_cast<float2*>(smem + kOffStat);
+  float2* Stat0 = reinterpret_cast<float2*>(smem + kOffStat);   // [2 halves][128]  LayerNorm(128) partial moments
+  float2* Stat1 = Stat0 + 2 * kTileM;                           // [2 halves][128]  after FC1
+  float2* Stat2 = Stat1 + 2 * kTileM;                           // [2 articulator parities][2 halves][128]  after FC2
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
   uint64_t* full = bars;            // [kStages]  weights landed
-  uint64_t* empty = bars + 4;       // [kStages]  MMAs that read the stage completed
-  uint64_t* pfull = bars + 8;       // [2]        articulator parameters landed
-  uint64_t* pempty = bars + 10;     // [2]        epilogue finished with them
-  uint64_t* chunk = bars + 12;      // [8]        32-column K chunk j of the A operand is in TMEM (K = 256 GEMMs)
-  uint64_t* a1bar = bars + 20;      // [4]        the same for the A operand of FC1 (K = 128)
-  uint64_t* d_ready = bars + 24;    // [2]        accumulator complete (alternating)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 26);
+  uint64_t* empty = bars + 8;       // [kStages]  MMAs that read the stage completed
+  uint64_t* pfull = bars + 16;      // [2]        articulator parameters landed
+  uint64_t* pempty = bars + 18;     // [2]        epilogue and output warps finished with them
+  uint64_t* chunk = bars + 20;      // [8]        32-column K chunk j of the A operand is in TMEM (K = 256 GEMMs)
+  uint64_t* a1bar = bars + 28;      // [4]        the same for the A operand of FC1 (K = 128)
+  uint64_t* dbar = bars + 32;       // [4]        accumulator of linear.0 / FC1 / FC2 / heads complete
+  uint64_t* d3_free = bars + 36;    //            the output warps have read the heads accumulator
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 37);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  // CTAs walk the articulators of a unit in different (rotated) orders: all SMs streaming the same
-  // 32 KB weight chunk at the same moment would queue on the few L2 slices that hold it
-  auto rotated = [&](int g0, int g1, int k) { return g0 + (k + int(blockIdx.x)) % (g1 - g0); };
 
   if (tid == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -180,11 +213,12 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&pfull[s], 1);
-      mbar_init(&pempty[s], kEpiWarps);
-      mbar_init(&d_ready[s], 1);
+      mbar_init(&pempty[s], kEpiWarps + kHeadWarps);
     }
     for (int j = 0; j < 8; ++j) mbar_init(&chunk[j], 4);   // the four lane quarters of the owning half
     for (int j = 0; j < 4; ++j) mbar_init(&a1bar[j], 4);
+    for (int j = 0; j < 4; ++j) mbar_init(&dbar[j], 1);
+    mbar_init(d3_free, kHeadWarps);
     fence_mbar_init();
   }
   if (warp == kMmaWarp) tmem_alloc(tmem_slot, 512);
@@ -198,20 +232,33 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
     // ===================== producer: weight chunks and articulator parameters =====================
     if (lane == 0) {
       uint32_t c = 0, pa = 0;
-      auto push = [&](const float* src, uint32_t bytes) {
+      TR_DECL;
+      auto push = [&](const float* src, uint32_t bytes) {   // one bulk copy per stage (split copies measured slower)
         if (ASB_DEC_ABLATE == 4) return;
-        const uint32_t s = c % kStages;
-        mbar_wait(&empty[s], ((c / kStages) & 1) ^ 1);
-        mbar_arrive_expect_tx(&full[s], bytes);
-        bulk_g2s(Ws + s * kStageBytes, src, bytes, &full[s]);
+        const uint32_t st = c % kStages;
+        mbar_wait(&empty[st], ((c / kStages) & 1) ^ 1);
+        mbar_arrive_expect_tx(&full[st], bytes);
+        bulk_g2s(Ws + st * kStageBytes, src, bytes, &full[st]);
+        TR(3, 400 + st);
         ++c;
       };
-      for (int u = blockIdx.x; u < a.n_units; u += gridDim.x) {
-        const int grp = u % a.n_groups;
-        const int g0 = grp * a.group, g1 = min(a.n_art, g0 + a.group);
-        for (int j = 0; j < 8; ++j) push(a.image + kLinParams + j * kLinChunk, kLinChunk * 4);
+      UnitIter units(a);
+      int tile, g0, g1;
+      while (units.next(tile, g0, g1)) {
+        {   // pull the NEXT unit's input tile towards L2 while this unit is being computed
+          UnitIter peek = units;
+          int t2, h0, h1;
+          if (peek.next(t2, h0, h1) && t2 != tile) {
+            const long long row0 = (long long)t2 * kTileM;
+            const long long rows = min((long long)kTileM, a.M - row0);
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.rnn_out + row0 * 256),
+                         "r"(uint32_t(rows * 256 * 4))
+                         : "memory");
+          }
+        }
+        for (int j = 0; j < 4; ++j) push(a.image + kLinParams + 2 * j * kLinChunk, 2 * kLinChunk * 4);
         for (int k = 0; k < g1 - g0; ++k) {
-          const int art = rotated(g0, g1, k);
+          const int art = g0 + k;
           const float* blk = a.image + kLinBlock + (size_t)art * kArtBlock;
           const uint32_t pb = pa & 1;
           mbar_wait(&pempty[pb], ((pa >> 1) & 1) ^ 1);
@@ -223,62 +270,150 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
           const float* wh = w2 + 8 * kFcChunk;
           for (int j = 0; j < 4; ++j) push(w1 + j * kFcChunk, kFcChunk * 4);
           for (int j = 0; j < 8; ++j) push(w2 + j * kFcChunk, kFcChunk * 4);
-          for (int j = 0; j < 8; ++j) push(wh + j * kHeadChunk, kHeadChunk * 4);
+          for (int j = 0; j < 4; ++j) push(wh + 2 * j * kHeadChunk, 2 * kHeadChunk * 4);   // 14 KB chunks stay 1 KB aligned
         }
       }
     }
     __syncwarp();
   } else if (warp == kMmaWarp) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      uint32_t c = 0, gcount = 0, artc = 0, ph_chunk = 0, ph_a1 = 0;
-      int tr_n = 0;
-      (void)tr_n;
-      // K chunk j is issued as soon as its 32 A columns are in TMEM and its weights are in shared
-      // memory.  `whole_cta`: the accumulator region still holds columns that warps of BOTH halves
-      // may be reading (the previous heads output), so the first (overwriting) MMA also waits for
-      // chunk 1, which the other half signals only after it has finished reading.
-      auto gemm = [&](uint32_t d_tmem, uint32_t a_tmem, uint32_t n, int k_chunks, uint64_t* abar, uint32_t& ph,
-                      bool whole_cta) {
+    // ===================== MMA issuer: the whole warp walks the loop, one elected lane issues =====
+    {
+      uint32_t c = 0, artc = 0, ph_chunk = 0, ph_a1 = 0;
+      TR_DECL;
+      // K chunk j is issued as soon as its 32 A columns are in TMEM and its weight stage is in shared
+      // memory.  The whole warp walks the loop and one ELECTED lane issues (tools/micro/umma_rate.cu:
+      // behind `lane == 0` every MMA is wrapped in an R2UR/ELECT loop and costs ~300 clk to issue; this
+      // form issues 4 MMAs + commit + the waits in ~340 clk, hidden behind the 4 x 127 clk an N = 256
+      // chunk executes).  A stage costs one full-wait and one commit.
+      auto gemm = [&](uint32_t d_tmem, uint32_t a_tmem, uint32_t n, int k_chunks, int per_stage, uint32_t sub_bytes,
+                      uint64_t* abar, uint32_t& ph, uint64_t* done) {
         const uint32_t idesc = idesc_tf32_m128(n);
         TR(0, 100 + n);
-        for (int j = 0; j < k_chunks; ++j) {
+        auto await = [&](int j, uint32_t stage_ctr) {
           mbar_wait(&abar[j], (ph >> j) & 1);
-          TR(0, 10 + j);
-          if (j == 0 && whole_cta) mbar_wait(&abar[1], (ph >> 1) & 1);
           ph ^= 1u << j;
+          if (j % per_stage == 0 && ASB_DEC_ABLATE != 4) mbar_wait(&full[stage_ctr % kStages], (stage_ctr / kStages) & 1);
           fence_after_sync();
-          const uint32_t s = c % kStages;
-          if (ASB_DEC_ABLATE != 4) mbar_wait(&full[s], (c / kStages) & 1);
-          fence_after_sync();
-          const uint64_t bdesc = smem_desc_k_sw128(smem_u32(Ws + s * kStageBytes));
+          TR(0, 10 + j);
+        };
+        for (int j = 0; j < k_chunks; ++j) {
+          await(j, c);
+          const uint32_t st = c % kStages;
+          const bool closes = (j % per_stage) == per_stage - 1;
+          const uint64_t bdesc = smem_desc_k_sw128(smem_u32(Ws + st * kStageBytes + (j % per_stage) * sub_bytes));
+          const uint32_t acol = a_tmem + j * kChunkK;
+          if (elect_one()) {
 #pragma unroll
-          for (int ks = 0; ks < (ASB_DEC_ABLATE == 3 ? 0 : 4); ++ks)
-            mma_tf32_ts(d_tmem, a_tmem + j * kChunkK + ks * 8, bdesc + uint64_t(2 * ks), idesc, (j | ks) != 0);
-          if (ASB_DEC_ABLATE != 4) commit(&empty[s]);  // frees the stage once these MMAs have read it
-          ++c;
+            for (int ks = 0; ks < (ASB_DEC_ABLATE == 3 ? 0 : 4); ++ks)
+              mma_tf32_ts(d_tmem, acol + ks * 8, bdesc + uint64_t(2 * ks), idesc, (j | ks) != 0);
+            if (closes && ASB_DEC_ABLATE != 4) commit(&empty[st]);   // frees the stage once its MMAs have read it
+            if (j == k_chunks - 1) commit(done);
+          }
+          __syncwarp();
+          if (closes) ++c;
         }
-        commit(&d_ready[gcount & 1]);
         TR(0, 99);
-        ++gcount;
       };
-      for (int u = blockIdx.x; u < a.n_units; u += gridDim.x) {
-        const int grp = u % a.n_groups;
-        const int g0 = grp * a.group, g1 = min(a.n_art, g0 + a.group);
+      // the accumulator about to be overwritten still holds the previous heads output until the
+      // output warps have loaded it
+      auto wait_heads_read = [&]() {
+        if (artc) {
+          mbar_wait(d3_free, (artc - 1) & 1);
+          fence_after_sync();
+        }
+      };
+      UnitIter units(a);
+      int tile, g0, g1;
+      while (units.next(tile, g0, g1)) {
         {
           const uint32_t P = tmem_base + (artc & 1) * 256, Q = tmem_base + ((artc & 1) ^ 1) * 256;
-          gemm(P, Q, 128, 8, chunk, ph_chunk, true);            // linear.0          K = 256
+          wait_heads_read();
+          gemm(P, Q, 128, 8, 2, kLinChunk * 4, chunk, ph_chunk, &dbar[0]);     // linear.0          K = 256
         }
         for (int k = 0; k < g1 - g0; ++k) {
           const uint32_t P = tmem_base + (artc & 1) * 256, Q = tmem_base + ((artc & 1) ^ 1) * 256;
-          gemm(Q, P + 128, 256, 4, a1bar, ph_a1, false);        // Linear(128, 256)
-          gemm(P, Q, 256, 8, chunk, ph_chunk, true);            // Linear(256, 256)
-          gemm(Q, P, kHeadN, 8, chunk, ph_chunk, false);        // x/y heads
+          gemm(Q, P + 128, 256, 4, 1, 0, a1bar, ph_a1, &dbar[1]);              // Linear(128, 256)
+          wait_heads_read();
+          gemm(P, Q, 256, 8, 1, 0, chunk, ph_chunk, &dbar[2]);                 // Linear(256, 256)
+          gemm(Q, P, kHeadN, 8, 2, kHeadChunk * 4, chunk, ph_chunk, &dbar[3]);  // x/y heads
           ++artc;
         }
       }
     }
     __syncwarp();
+  } else if (warp >= kHeadWarp0) {
+    // ===================== output warps: thread = frame; sigmoid(rstd * D3 + ...) -> contours ======
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
+    const uint32_t ps_addr = smem_u32(Ps);
+    uint32_t pa = 0, artc = 0;
+    uint32_t r[32], r2[32], r4[4];
+    TR_DECL;
+    UnitIter units(a);
+    int tile, g0, g1;
+    while (units.next(tile, g0, g1)) {
+      const long long grow = (long long)tile * kTileM + row;
+      const bool live = grow < a.M;
+      for (int k = 0; k < g1 - g0; ++k) {
+        const int art = g0 + k;
+        const uint32_t Q = tmem_base + lane_sel + ((artc & 1) ^ 1) * 256;
+        const uint32_t pb = pa & 1;
+        const uint32_t prm = ps_addr + pb * kArtParams * 4;
+        mbar_wait(&pfull[pb], (pa >> 1) & 1);
+        mbar_wait(&dbar[3], artc & 1);
+        fence_after_sync();
+        TR(4 + (warp - kHeadWarp0), 600);
+        const float2 m0 = Stat2[((artc & 1) * 2 + 0) * kTileM + row], m1 = Stat2[((artc & 1) * 2 + 1) * kTileM + row];
+        const float mean = (m0.x + m1.x) * (1.f / 256.f);
+        const float var = fmaxf((m0.y + m1.y) * (1.f / 256.f) - mean * mean, 0.f);
+        const float rstd = rsqrtf(var + 1e-5f);
+        const float nm = -mean * rstd;
+        // the head parameters carry the factor -log2(e): t = -log2(e) (rstd D + b - rstd mean ws)
+        const f32x2 rs2 = pack2(-1.4426950408889634f * rstd, -1.4426950408889634f * rstd), nm2 = pack2(nm, nm);
+        float* dst = a.out + (grow * a.n_art + art) * 100;
+        auto emit = [&](const uint32_t* v, int col) {   // 4 columns
+          const float4 b4 = lds4(prm + (P_BH + col) * 4);
+          const float4 w4 = lds4(prm + (P_WSH + col) * 4);
+          float t0, t1, t2, t3;
+          unpack2(fma2(rs2, pack2(__uint_as_float(v[0]), __uint_as_float(v[1])),
+                       fma2(nm2, pack2(w4.x, w4.y), pack2(b4.x, b4.y))), t0, t1);
+          unpack2(fma2(rs2, pack2(__uint_as_float(v[2]), __uint_as_float(v[3])),
+                       fma2(nm2, pack2(w4.z, w4.w), pack2(b4.z, b4.w))), t2, t3);
+          __stcs(reinterpret_cast<float4*>(dst + col),
+                 make_float4(sigmoid_exp2(t0), sigmoid_exp2(t1), sigmoid_exp2(t2), sigmoid_exp2(t3)));
+        };
+        tmem_ld32(Q, r);
+        tmem_ld_wait();
+        tmem_ld32(Q + 32, r2);
+        if (live) {
+#pragma unroll
+          for (int q = 0; q < 8; ++q) emit(&r[4 * q], 4 * q);
+        }
+        tmem_ld_wait();
+        tmem_ld32(Q + 64, r);
+        tmem_ld4(Q + 96, r4);
+        if (live) {
+#pragma unroll
+          for (int q = 0; q < 8; ++q) emit(&r2[4 * q], 32 + 4 * q);
+        }
+        tmem_ld_wait();
+        fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(d3_free);       // the accumulator columns may be overwritten now
+        TR(4 + (warp - kHeadWarp0), 603);
+        if (live) {
+#pragma unroll
+          for (int q = 0; q < 8; ++q) emit(&r[4 * q], 64 + 4 * q);
+          emit(r4, 96);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&pempty[pb]);
+        TR(4 + (warp - kHeadWarp0), 604);
+        ++pa;
+        ++artc;
+      }
+    }
   } else {
     // ===================== epilogue: thread = (frame = TMEM lane, alternate 32-column chunks) ======
     const int quarter = warp & 3, half = warp >> 2;
@@ -286,16 +421,15 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
     const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
     float* xrow = Xs + row * kXStride;
     const uint32_t ps_addr = smem_u32(Ps), linb_addr = smem_u32(LinB);
-    uint32_t gcount = 0, pa = 0, use = 0, artc = 0;
-    uint32_t r[32];
-    int tr_n = 0;
-    (void)tr_n;
+    uint32_t pa = 0, artc = 0, unitc = 0;
+    uint32_t r[32], r2[32];
+    TR_DECL;
+#ifdef ASB_DEC_TRACE
     const int tr_role = 1 + half;
-    (void)tr_role;
+#endif
 
-    auto wait_d = [&]() {
-      mbar_wait(&d_ready[gcount & 1], (gcount >> 1) & 1);
-      ++gcount;
+    auto wait_d = [&](int which, uint32_t parity) {
+      mbar_wait(&dbar[which], parity & 1);
       fence_after_sync();
       if (quarter == 0) TR(tr_role, 200);
     };
@@ -307,17 +441,16 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
       if (lane == 0) mbar_arrive(bar);
       if (quarter == 0) TR(tr_role, 201);
     };
-    // row moments are split over the two halves: each half publishes its partial sums after a layer
-    // and reads the partner's before the next one (ordered by the chunk -> MMA -> D-ready chain)
+    // row moments are split over the two halves: each half publishes its partial sums after a layer;
+    // the partner (or the output warp) reads them behind the chunk -> MMA -> D-complete chain
     float own_s = 0.f, own_ss = 0.f;
-    auto publish = [&](float s, float ss) {
+    auto publish = [&](float2* buf, float s, float ss) {
       own_s = s;
       own_ss = ss;
-      Stat[((use & 1) * 2 + half) * kTileM + row] = make_float2(s, ss);
+      buf[half * kTileM + row] = make_float2(s, ss);
     };
-    auto moments = [&](float inv_n, float& rstd, float& nm) {
-      const float2 o = Stat[((use & 1) * 2 + (half ^ 1)) * kTileM + row];
-      ++use;
+    auto moments = [&](const float2* buf, float inv_n, float& rstd, float& nm) {
+      const float2 o = buf[(half ^ 1) * kTileM + row];
       const float mean = (own_s + o.x) * inv_n;
       const float var = fmaxf((own_ss + o.y) * inv_n - mean * mean, 0.f);
       rstd = rsqrtf(var + 1e-5f);
@@ -325,13 +458,12 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
     };
     // accumulator -> relu(rs * D + (b + nm * ws)) -> moments, tf32 -> the same columns, chunk by chunk.
     // The TMEM load of the next chunk is in flight while this one is converted; the arithmetic is
-    // packed fp32x2 (FFMA2 / FADD2) except the relu and the integer rounding.
-    uint32_t r2[32];
+    // packed fp32x2 (FFMA2) except the relu and the integer rounding.
     auto convert_in_place = [&](uint32_t region, uint32_t b_addr, uint32_t ws_addr, float rs, float nm,
-                                bool deferred) {
+                                bool deferred, float2* stat) {
       const f32x2 rs2 = pack2(rs, rs), nm2 = pack2(nm, nm), one2 = pack2(1.f, 1.f);
       f32x2 sa = pack2(0.f, 0.f), sb = sa, qa = sa, qb = sa;
-      auto body = [&](uint32_t(&buf)[32], int ch) {
+      auto body = [&](uint32_t(&buf)[32], int ch, bool last) {
 #pragma unroll
         for (int q = 0; q < (ASB_DEC_ABLATE == 1 || ASB_DEC_ABLATE == 2 ? 0 : 8); ++q) {
           const float4 b4 = lds4(b_addr + (32 * ch + 4 * q) * 4);
@@ -359,6 +491,14 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
           buf[4 * q + 3] = to_tf32_finite(v3);
         }
         if (ASB_DEC_ABLATE != 2) tmem_st32(region + 32 * ch, buf);
+        if (last) {   // the moments are published BEFORE the last chunk is signalled (their readers sit behind it)
+          float s0, s1, s2, s3, q0, q1, q2, q3;
+          unpack2(sa, s0, s1);
+          unpack2(sb, s2, s3);
+          unpack2(qa, q0, q1);
+          unpack2(qb, q2, q3);
+          publish(stat, (s0 + s1) + (s2 + s3), (q0 + q1) + (q2 + q3));
+        }
         signal(&chunk[ch]);
       };
       if (ASB_DEC_ABLATE != 2) tmem_ld32(region + 32 * half, r);
@@ -368,18 +508,12 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
         tmem_ld_wait();
         if (c & 1) {
           if (c < 3 && ASB_DEC_ABLATE != 2) tmem_ld32(region + 32 * (ch + 2), r);
-          body(r2, ch);
+          body(r2, ch, c == 3);
         } else {
           if (c < 3 && ASB_DEC_ABLATE != 2) tmem_ld32(region + 32 * (ch + 2), r2);
-          body(r, ch);
+          body(r, ch, c == 3);
         }
       }
-      float s0, s1, s2, s3, q0, q1, q2, q3;
-      unpack2(sa, s0, s1);
-      unpack2(sb, s2, s3);
-      unpack2(qa, q0, q1);
-      unpack2(qb, q2, q3);
-      publish((s0 + s1) + (s2 + s3), (q0 + q1) + (q2 + q3));
     };
     // x-hat (shared memory) -> A operand of FC1 in region[128, 256)
     auto write_a1 = [&](uint32_t region) {
@@ -393,15 +527,16 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
       }
     };
 
-    for (int u = blockIdx.x; u < a.n_units; u += gridDim.x) {
-      const int tile = u / a.n_groups, grp = u % a.n_groups;
-      const int g0 = grp * a.group, g1 = min(a.n_art, g0 + a.group);
+    UnitIter units(a);
+    int tile, g0, g1;
+    while (units.next(tile, g0, g1)) {
       const long long grow = (long long)tile * kTileM + row;
       const bool live = grow < a.M;
 
       // ---- input tile -> A0 (tf32) in Q: this thread converts 128 of its frame's 256 features
       {
         const uint32_t P = tmem_base + lane_sel + (artc & 1) * 256, Q = tmem_base + lane_sel + ((artc & 1) ^ 1) * 256;
+        if (artc) wait_d(3, artc - 1);   // Q was the A operand of the previous heads GEMM
         const float4* src = reinterpret_cast<const float4*>(a.rnn_out + grow * 256);
 #pragma unroll 1
         for (int c = 0; c < 4; ++c) {
@@ -410,16 +545,16 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
           for (int q = 0; q < 8; ++q) {
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
             if (live) v = __ldg(src + 8 * ch + q);
-            r[4 * q + 0] = to_tf32(v.x);
-            r[4 * q + 1] = to_tf32(v.y);
-            r[4 * q + 2] = to_tf32(v.z);
-            r[4 * q + 3] = to_tf32(v.w);
+            r[4 * q + 0] = to_tf32_finite(v.x);
+            r[4 * q + 1] = to_tf32_finite(v.y);
+            r[4 * q + 2] = to_tf32_finite(v.z);
+            r[4 * q + 3] = to_tf32_finite(v.w);
           }
           tmem_st32(Q + 32 * ch, r);
           signal(&chunk[ch]);
         }
         // ---- linear.0 epilogue: relu(D0 + b) -> LayerNorm(128) -> x-hat (tf32) kept in shared memory
-        wait_d();
+        wait_d(0, unitc);
         float s = 0.f, ss = 0.f;
 #pragma unroll 1
         for (int c = 0; c < 2; ++c) {
@@ -441,10 +576,11 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
             ss = fmaf(v0, v0, fmaf(v1, v1, fmaf(v2, v2, fmaf(v3, v3, ss))));
           }
         }
-        publish(s, ss);
+        bar_sync_epilogue();   // the partner has read the previous unit's Stat0
+        publish(Stat0, s, ss);
         bar_sync_epilogue();   // once per unit: the partner's partial sums are needed right away
         float rstd, nm;
-        moments(1.f / 128.f, rstd, nm);
+        moments(Stat0, 1.f / 128.f, rstd, nm);
 #pragma unroll 1
         for (int c = 0; c < 2; ++c) {
           const int ch = 2 * c + half;
@@ -453,56 +589,23 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
             xrow[32 * ch + k] = __uint_as_float(to_tf32_finite(fmaf(xrow[32 * ch + k], rstd, nm)));
         }
         write_a1(P);
+        ++unitc;
       }
 
       for (int k = 0; k < g1 - g0; ++k) {
-        const int art = rotated(g0, g1, k);
         const uint32_t P = tmem_base + lane_sel + (artc & 1) * 256, Q = tmem_base + lane_sel + ((artc & 1) ^ 1) * 256;
         const uint32_t pb = pa & 1;
         const uint32_t prm = ps_addr + pb * kArtParams * 4;
         mbar_wait(&pfull[pb], (pa >> 1) & 1);
         float rstd, nm;
-        wait_d();                                             // FC1 done: D1 in Q
-        convert_in_place(Q, prm + P_B1 * 4, 0u, 1.f, 0.f, false);
-        wait_d();                                             // FC2 done: D2 in P
-        moments(1.f / 256.f, rstd, nm);
-        convert_in_place(P, prm + P_B2 * 4, prm + P_WS2 * 4, rstd, nm, true);
-        if (k + 1 < g1 - g0) write_a1(Q);                      // next articulator's FC1 operand, under the heads GEMM
-        wait_d();                                             // heads done: D3 in Q[0, 112)
-        moments(1.f / 256.f, rstd, nm);
-        if (quarter == 0) TR(tr_role, 300);
-        // ---- heads: sigmoid(rstd * D3 + ...) -> contours in their final layout
-        {
-          float* dst = a.out + (grow * a.n_art + art) * 100;
-#pragma unroll 1
-          for (int c = 0; c < 2; ++c) {
-            const int cbase = 32 * (2 * c + half);
-            if (cbase < 100) {  // warp-uniform
-              tmem_ld32(Q + cbase, r);
-              tmem_ld_wait();
-              if (live) {
-#pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                  const int col = cbase + 4 * q;
-                  if (col < 100) {
-                    const float4 b4 = lds4(prm + (P_BH + col) * 4);
-                    const float4 w4 = lds4(prm + (P_WSH + col) * 4);
-                    float4 o;
-                    o.x = sigmoid_fast(fmaf(rstd, __uint_as_float(r[4 * q + 0]), fmaf(nm, w4.x, b4.x)));
-                    o.y = sigmoid_fast(fmaf(rstd, __uint_as_float(r[4 * q + 1]), fmaf(nm, w4.y, b4.y)));
-                    o.z = sigmoid_fast(fmaf(rstd, __uint_as_float(r[4 * q + 2]), fmaf(nm, w4.z, b4.z)));
-                    o.w = sigmoid_fast(fmaf(rstd, __uint_as_float(r[4 * q + 3]), fmaf(nm, w4.w, b4.w)));
-                    *reinterpret_cast<float4*>(dst + col) = o;
-                  }
-                }
-              }
-            }
-          }
-        }
-        fence_before_sync();
+        wait_d(1, artc);                                      // FC1 done: D1 in Q
+        convert_in_place(Q, prm + P_B1 * 4, 0u, 1.f, 0.f, false, Stat1);
+        wait_d(2, artc);                                      // FC2 done: D2 in P
+        moments(Stat1, 1.f / 256.f, rstd, nm);
+        convert_in_place(P, prm + P_B2 * 4, prm + P_WS2 * 4, rstd, nm, true, Stat2 + (artc & 1) * 2 * kTileM);
+        if (k + 1 < g1 - g0) write_a1(Q);                     // next articulator's FC1 operand, under the heads GEMM
         __syncwarp();
         if (lane == 0) mbar_arrive(&pempty[pb]);
-        if (quarter == 0) TR(tr_role, 301);
         ++pa;
         ++artc;
       }
@@ -532,13 +635,15 @@ static int pack_mat(const float* src, const float* scale, float* dst, int n_src,
   ASB_CHECK_LAUNCH("pack_umma_kernel");
   return ASB_OK;
 }
-static int fold_wsum(const float* W, const float* scale, float* dst, int N, int K, cudaStream_t st) {
-  fold_wsum_kernel<<<(N + 127) / 128, 128, 0, st>>>(W, scale, dst, N, K);
+static int fold_wsum(const float* W, const float* scale, float* dst, int N, int K, cudaStream_t st,
+                     double out_scale = 1.0) {
+  fold_wsum_kernel<<<(N + 127) / 128, 128, 0, st>>>(W, scale, dst, N, K, out_scale);
   ASB_CHECK_LAUNCH("fold_wsum_kernel");
   return ASB_OK;
 }
-static int fold_bias(const float* W, const float* beta, const float* b, float* dst, int N, int K, cudaStream_t st) {
-  fold_bias_kernel<<<(N + 127) / 128, 128, 0, st>>>(W, beta, b, dst, N, K);
+static int fold_bias(const float* W, const float* beta, const float* b, float* dst, int N, int K, cudaStream_t st,
+                     double out_scale = 1.0) {
+  fold_bias_kernel<<<(N + 127) / 128, 128, 0, st>>>(W, beta, b, dst, N, K, out_scale);
   ASB_CHECK_LAUNCH("fold_bias_kernel");
   return ASB_OK;
 }
@@ -561,11 +666,13 @@ int pack_umma_image(asb_model* m, const asb_weights* s, cudaStream_t st) {
     // LayerNorm affines folded forward: W' = W diag(gamma), b' = b + W beta   (models.py:11-21)
     ASB_TRY(fold_bias(s->fc1_w[i], s->ln0_b[i], s->fc1_b[i], blk + P_B1, kFc, kH, st));
     ASB_TRY(fold_bias(s->fc2_w[i], s->ln1_b[i], s->fc2_b[i], blk + P_B2, kFc, kFc, st));
-    ASB_TRY(fold_bias(s->xh_w[i], s->ln2_b[i], s->xh_b[i], blk + P_BH, D, kFc, st));
-    ASB_TRY(fold_bias(s->yh_w[i], s->ln2_b[i], s->yh_b[i], blk + P_BH + D, D, kFc, st));
+    // the head parameters carry -log2(e): the output warps evaluate the sigmoid as 1 / (1 + 2^t)
+    const double kNegLog2e = -1.4426950408889634;
+    ASB_TRY(fold_bias(s->xh_w[i], s->ln2_b[i], s->xh_b[i], blk + P_BH, D, kFc, st, kNegLog2e));
+    ASB_TRY(fold_bias(s->yh_w[i], s->ln2_b[i], s->yh_b[i], blk + P_BH + D, D, kFc, st, kNegLog2e));
     ASB_TRY(fold_wsum(s->fc2_w[i], s->ln1_w[i], blk + P_WS2, kFc, kFc, st));
-    ASB_TRY(fold_wsum(s->xh_w[i], s->ln2_w[i], blk + P_WSH, D, kFc, st));
-    ASB_TRY(fold_wsum(s->yh_w[i], s->ln2_w[i], blk + P_WSH + D, D, kFc, st));
+    ASB_TRY(fold_wsum(s->xh_w[i], s->ln2_w[i], blk + P_WSH, D, kFc, st, kNegLog2e));
+    ASB_TRY(fold_wsum(s->yh_w[i], s->ln2_w[i], blk + P_WSH + D, D, kFc, st, kNegLog2e));
     float* w1 = blk + kArtParams;
     float* w2 = w1 + 4 * kFcChunk;
     float* wh = w2 + 8 * kFcChunk;
@@ -586,19 +693,6 @@ int launch_decoder_umma(const asb_model* m, const float* rnn_out, float* out, in
   }
   const int sms = sm_count();
   const int n_tiles = (M + kTileM - 1) / kTileM;
-  // articulators per work unit: minimise (waves) x (cycles per unit); linear.0 is redone per unit
-  int best_g = m->N;
-  double best_cost = 1e300;
-  for (int g = 1; g <= m->N; ++g) {
-    const int n_groups = (m->N + g - 1) / g;
-    const long long units = (long long)n_tiles * n_groups;
-    const double waves = double((units + sms - 1) / sms);
-    const double cost = waves * (4500.0 + g * 12500.0);
-    if (cost < best_cost - 1e-9) {
-      best_cost = cost;
-      best_g = g;
-    }
-  }
   UmmaArgs a;
   a.image = m->w.umma_image;
   a.rnn_out = rnn_out;
@@ -606,10 +700,8 @@ int launch_decoder_umma(const asb_model* m, const float* rnn_out, float* out, in
   a.M = M;
   a.n_art = m->N;
   a.D = m->D;
-  a.group = best_g;
-  a.n_groups = (m->N + best_g - 1) / best_g;
-  a.n_units = n_tiles * a.n_groups;
-  const int grid = a.n_units < sms ? a.n_units : sms;
+  a.n_items = (long long)n_tiles * m->N;
+  const int grid = int(a.n_items < sms ? a.n_items : sms);
   decoder_umma_kernel<<<grid, kThreads, kSmemBytes, st>>>(a);
   ASB_CHECK_LAUNCH("decoder_umma_kernel");
   return ASB_OK;

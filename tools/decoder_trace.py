@@ -5,7 +5,7 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from artspeech_b200 import _lib
-_lib.LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_var_dec_trace.so")
+_lib.LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), os.environ.get("ASB_TRACE_LIB", "_var_dec_trace.so"))
 from artspeech_b200 import models, synthetic
 
 net = models.ArtSpeech(45, 10, precision="fast").cuda().eval()
@@ -15,12 +15,12 @@ with torch.no_grad():
     for _ in range(3):
         net(x, L)
 torch.cuda.synchronize()
-buf = (ctypes.c_longlong * (3 * 4096))()
+buf = (ctypes.c_longlong * (8 * 4096))()
 fn = _lib.lib().asb_debug_decoder_trace
 fn.argtypes = [ctypes.POINTER(ctypes.c_longlong)]
 assert fn(buf) == 0
 ev = []
-for role in range(3):
+for role in range(8):
     for i in range(2047):
         tag, t = buf[role * 4096 + 2 * i], buf[role * 4096 + 2 * i + 1]
         if t == 0:
@@ -31,5 +31,12 @@ t0 = ev[0][0]
 names = {99: "commit D", 200: "D ready seen", 201: "chunk signalled", 300: "heads begin", 301: "heads end"}
 limit = int(sys.argv[1]) if len(sys.argv) > 1 else 260
 for t, role, tag in ev[:limit]:
-    what = names.get(tag, f"gemm N={tag - 100} begin" if tag >= 100 else f"A chunk {tag - 10} ready")
-    print(f"{t - t0:8d}  {'MMA ' if role == 0 else 'EPI' + str(role - 1)}  {what}")
+    if tag >= 600:
+        what = {600: "heads D seen", 603: "heads D read (freed)", 604: "contours stored"}[tag]
+    elif tag >= 500:
+        what = f"weights in slot {tag - 500} seen"
+    elif tag >= 400:
+        what = f"copy into slot {tag - 400} issued"
+    else:
+        what = names.get(tag, f"gemm N={tag - 100} begin" if tag >= 100 else f"A chunk {tag - 10} ready")
+    print(f"{t - t0:8d}  {['MMA ', 'EPI0', 'EPI1', 'PROD', 'OUT0', 'OUT1', 'OUT2', 'OUT3'][role]}  {what}")
