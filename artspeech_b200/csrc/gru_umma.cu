@@ -1,21 +1,25 @@
-// Recurrent layer on tcgen05 tensor cores with W_hh resident in shared memory for all T steps.
+// Recurrent layer on tcgen05 tensor cores with W_hh resident in TENSOR MEMORY for all T steps.
 //
 // Same computation as gru.cu's fast kernel (nn.GRU cell of models.py:111 with packed-sequence
-// semantics): per step gh^T[G*H x batch] = W_hh[G*H x H] . h^T[H x batch], gates fused behind it.
+// semantics; G = 4: nn.LSTM): per step gh^T[G*H x batch] = W_hh[G*H x H] . h^T[H x batch], gates
+// fused behind it.
 //
 // Blackwell mapping
 //   * one CTA = 2*CPT (4, 8 or 16) batch rows of one direction - as few as still fill one wave of
-//     SMs, because the gate math (6 MUFU per unit and row) is what bounds a step; W_hh (bf16, G tiles of 128 x 128, K-major with the
-//     128-byte swizzle) is copied ONCE into shared memory (96 KB for the GRU) by bulk async copies
-//     from an image pre-swizzled at model creation and stays there for the whole sequence;
-//   * per step one thread issues G x 8 tcgen05.mma (kind::f16, bf16 in, fp32 accumulate, M = 128
-//     gate rows, N = 16 batch rows, K = 16): A = W_hh tile (smem), B = h as bf16 (smem, 4 KB),
-//     D = G x 16 columns of tensor memory, lane = hidden unit;
-//   * the 8 epilogue warps (thread = hidden unit, 8 batch columns) read D with tcgen05.ld - the r,
-//     z, n pre-activations of one (unit, row) sit in the same lane, so the gate math is
-//     thread-local -, keep h in fp32 registers, write h as bf16 back into the B operand and
-//     the fp32 output row, and hand over to the MMA thread through one mbarrier; the input
-//     pre-activations of the next step are prefetched while the MMAs run.
+//     SMs, because the gate math (6 MUFU per unit and row) is what bounds a step;
+//   * W_hh (bf16) is the A operand and lives in tensor memory: lane = gate row, 64 columns per gate
+//     (two consecutive-k bf16 per 32-bit column), written ONCE with tcgen05.st at kernel start -
+//     G * 64 columns next to the G * 16 accumulator columns.  (The first version kept W_hh in shared
+//     memory: every step then re-read 96 KB through the SS form, 32+ clk per MMA; the TS form
+//     issues an N = 16 MMA every ~11 clk, tools/micro/umma_rate.cu.)
+//   * per step ONE ELECTED lane of a converged warp issues G x 8 tcgen05.mma (kind::f16, bf16 in,
+//     fp32 accumulate, M = 128 gate rows, N = 16 batch rows, K = 16): B = h as bf16 (shared
+//     memory, 4 KB, K-major, 128-byte swizzle), D = G x 16 columns, lane = hidden unit;
+//   * the 8 epilogue warps (thread = hidden unit, CPT batch columns) read D with tcgen05.ld - the
+//     gate pre-activations of one (unit, row) sit in the same lane, so the gate math is
+//     thread-local -, keep h (and the LSTM's c) in fp32 registers, write h as bf16 back into the B
+//     operand and the fp32 output row, and hand over to the MMA warp through one mbarrier; the
+//     input pre-activations of the next step are prefetched while the MMAs run.
 #include <cuda_bf16.h>
 
 #include "model.cuh"
@@ -28,7 +32,7 @@ using namespace asb::umma;
 
 constexpr int kRows = 16;                    // the MMA's N (columns past the CTA's rows stay zero)
 constexpr int kTileBytes = 128 * kH * 2;     // one gate tile of W_hh in bf16: 32 KB
-constexpr int kAtomBytes = 128 * 128;        // 128 rows x 64 bf16
+constexpr int kACol0 = 64;                   // TMEM: accumulators in columns [0, G*16), W_hh from column 64
 constexpr int kHsBytes = 2 * kRows * 128;    // h as the B operand: 2 k-atoms x 16 rows x 128 B
 constexpr int kEpiWarps = 8;
 constexpr int kCtlWarp = 8;
@@ -44,14 +48,11 @@ __host__ __device__ constexpr uint32_t sw128_bf16(uint32_t row, uint32_t k, uint
          ((((k & 63u) >> 3) ^ (row & 7u)) << 4) + (k & 7u) * 2u;
 }
 
-// whh (G*128, 128) fp32 -> bf16 image [gate][k-atom][128 rows][128 B swizzled]
+// whh (G*128, 128) fp32 -> bf16, same row-major layout (a row = the 64 TMEM columns of one lane)
 __global__ void pack_whh_umma_kernel(const float* __restrict__ whh, __nv_bfloat16* __restrict__ img, int G) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= G * kH * kH) return;
-  const int row = i / kH, k = i - row * kH;
-  const int gate = row / kH, m = row - gate * kH;
-  const uint32_t off = gate * kTileBytes + sw128_bf16(m, k, kAtomBytes);
-  img[off / 2] = __float2bfloat16_rn(whh[i]);
+  img[i] = __float2bfloat16_rn(whh[i]);
 }
 
 struct RnnArgs {
@@ -68,10 +69,8 @@ template <int G, int CPT>
 __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // keeps the shared address space
-  unsigned char* Wsm = smem;                         // G x 32 KB
-  unsigned char* Hs = smem + G * kTileBytes;         // 4 KB
+  unsigned char* Hs = smem;                          // 4 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(Hs + kHsBytes);
-  uint64_t* w_full = bars;       // weights landed
   uint64_t* h_ready = bars + 1;  // h (bf16) of this step is in shared memory, D has been read
   uint64_t* d_ready = bars + 2;  // this step's MMAs completed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
@@ -81,14 +80,14 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
   const int b0 = blockIdx.x * 2 * CPT;
   const int Lmax = a.lengths[b0];   // sorted descending: the tile's first row is its longest
   constexpr int GH = G * kH;
+  constexpr uint32_t kTmemCols = (kACol0 + G * 64 <= 256) ? 256 : 512;
 
   if (tid == 0) {
-    mbar_init(w_full, 1);
     mbar_init(h_ready, kEpiWarps);
     mbar_init(d_ready, 1);
     fence_mbar_init();
   }
-  if (warp == kCtlWarp) tmem_alloc(tmem_slot, 64);
+  if (warp == kCtlWarp) tmem_alloc(tmem_slot, kTmemCols);
   for (int i = tid; i < kHsBytes / 4; i += kThreads) reinterpret_cast<uint32_t*>(Hs)[i] = 0u;   // h0 = 0
   fence_proxy_async();
   fence_before_sync();
@@ -97,36 +96,52 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
   const uint32_t tmem_d = *tmem_slot;
 
   if (warp == kCtlWarp) {
-    if (lane == 0) {
-      mbar_arrive_expect_tx(w_full, G * kTileBytes);
-      const unsigned char* src = reinterpret_cast<const unsigned char*>(a.img[dir]);
-      for (int j = 0; j < G * 2; ++j) bulk_g2s(Wsm + j * kAtomBytes, src + (size_t)j * kAtomBytes, kAtomBytes, w_full);
-      mbar_wait(w_full, 0);
-      const uint32_t idesc = idesc_bf16_m128(kRows);
-      const uint64_t adesc0 = smem_desc_k_sw128(smem_u32(Wsm));
-      const uint64_t bdesc0 = smem_desc_k_sw128(smem_u32(Hs));
-      for (int s = 0; s < Lmax; ++s) {
-        mbar_wait(h_ready, s & 1);
-        fence_after_sync();
+    // the whole warp walks the loop, one ELECTED lane issues (behind `lane == 0` the compiler wraps
+    // every tcgen05.mma in an R2UR/ELECT loop that costs far more than the MMA itself)
+    const uint32_t idesc = idesc_bf16_m128(kRows);
+    const uint64_t bdesc0 = smem_desc_k_sw128(smem_u32(Hs));
+    const uint32_t tmem_a = tmem_d + kACol0;
+    for (int s = 0; s < Lmax; ++s) {
+      mbar_wait(h_ready, s & 1);
+      fence_after_sync();
+      if (elect_one()) {
 #pragma unroll
         for (int g = 0; g < G; ++g)
 #pragma unroll
           for (int kt = 0; kt < 8; ++kt) {
-            // k-step kt: atom kt / 4, 32 bytes (2 descriptor units) per step inside the atom
-            const uint64_t ad = adesc0 + uint64_t((g * kTileBytes + (kt >> 2) * kAtomBytes) >> 4) + uint64_t(2 * (kt & 3));
+            // k-step kt: 8 TMEM columns of A; B: atom kt / 4, 32 bytes (2 descriptor units) per step
             const uint64_t bd = bdesc0 + uint64_t(((kt >> 2) * kRows * 128) >> 4) + uint64_t(2 * (kt & 3));
-            mma_bf16_ss(tmem_d + g * kRows, ad, bd, idesc, kt != 0);
+            mma_bf16_ts(tmem_d + g * kRows, tmem_a + g * 64 + kt * 8, bd, idesc, kt != 0);
           }
         commit(d_ready);
       }
+      __syncwarp();
     }
-    __syncwarp();
   } else {
     // thread = (hidden unit u = TMEM lane, CPT of the CTA's 2 * CPT batch rows)
     const int quarter = warp & 3, colhalf = warp >> 2;
     const int u = quarter * 32 + lane;
     const uint32_t taddr = tmem_d + (uint32_t(quarter * 32) << 16) + colhalf * CPT;
     const float bn = (G == 3) ? a.bhhn[dir][u] : 0.f;
+    {   // W_hh -> tensor memory: this thread's gate rows, its half of the k range
+      const uint32_t ta = tmem_d + (uint32_t(quarter * 32) << 16) + kACol0 + colhalf * 32;
+      uint32_t w[32];
+#pragma unroll 1
+      for (int g = 0; g < G; ++g) {
+        const uint4* src = reinterpret_cast<const uint4*>(a.img[dir] + (size_t)(g * kH + u) * kH + colhalf * 64);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const uint4 v = __ldg(src + q);
+          w[4 * q + 0] = v.x;
+          w[4 * q + 1] = v.y;
+          w[4 * q + 2] = v.z;
+          w[4 * q + 3] = v.w;
+        }
+        tmem_st32(ta + g * 64, w);
+      }
+      tmem_st_wait();
+      fence_before_sync();
+    }
     int len[CPT];
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
@@ -205,7 +220,7 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  if (warp == kCtlWarp) tmem_dealloc(tmem_d, 64);
+  if (warp == kCtlWarp) tmem_dealloc(tmem_d, kTmemCols);
 }
 
 }  // namespace
@@ -231,7 +246,7 @@ int pack_whh_umma(asb_model* m, const asb_weights* src, cudaStream_t st) {
 
 template <int G>
 static int launch_rnn_umma_g(const asb_model* m, const RnnArgs& a, int B, cudaStream_t st) {
-  const int smem = G * kTileBytes + kHsBytes + 64 + 1024;
+  const int smem = kHsBytes + 64 + 1024;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(rnn_umma_kernel<G, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);

@@ -133,7 +133,7 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   for (int l = 0; l < 2; ++l)
     for (int d = 0; d < 2; ++d) w.whh_umma[l][d] = rnnu ? static_cast<void*>(b + o_whhu[l][d]) : nullptr;
   m->decoder_impl = umma ? 1 : 0;
-  m->rnn_impl = (cell == ASB_CELL_LSTM) ? 1 : 0;   // the LSTM cell exists only in the tcgen05 kernel
+  m->rnn_impl = rnnu ? 1 : 0;   // fast precision: the tcgen05 kernel (W_hh in tensor memory); the LSTM cell exists only there
 
   int rc = pack_recurrent_weights(m, src, st);
   if (!rc) rc = pack_dense_weights(m, src, st);

@@ -52,7 +52,7 @@ struct asb_model {
   asb::PackedWeights w;
   // optional per-stage timing (asb_model_profile_*): one event set per profiled forward
   int decoder_impl = 0;  // 0 = mma.sync (decoder.cu), 1 = tcgen05/TMEM (decoder_umma.cu, proj_umma.cu)
-  int rnn_impl = 0;      // 0 = register-resident mma.sync (gru.cu, the faster one), 1 = tcgen05 (gru_umma.cu)
+  int rnn_impl = 0;      // 0 = register-resident mma.sync / fp32 (gru.cu), 1 = tcgen05, W_hh in tensor memory (gru_umma.cu; fast-mode default)
   bool profile = false;
   std::vector<std::array<cudaEvent_t, ASB_N_STAGES + 1>> pending;
   std::vector<std::array<cudaEvent_t, ASB_N_STAGES + 1>> free_sets;

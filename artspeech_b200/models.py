@@ -153,9 +153,8 @@ class ArtSpeech(nn.Module):
         _lib.check(_lib.lib().asb_model_set_decoder(self._ensure_native(dev), code))
 
     def set_recurrent(self, impl):
-        """"mma" (default: W_hh in registers, mma.sync) or "tcgen05" (W_hh in shared memory,
-        tcgen05.mma with the gates behind tcgen05.ld) for the two recurrent layers; fast precision
-        only.  The LSTM cell exists in the tcgen05 kernel alone (selected automatically)."""
+        """"tcgen05" (default in fast precision: W_hh in tensor memory, tcgen05.mma with the gates behind
+        tcgen05.ld) or "mma" (W_hh in registers, mma.sync; GRU only) for the two recurrent layers."""
         dev = self.embedding.weight.device
         code = {"tcgen05": 1, "mma": 0}[impl]
         _lib.check(_lib.lib().asb_model_set_recurrent(self._ensure_native(dev), code))

@@ -31,7 +31,6 @@ def main():
         res[impl] = {"stage_ms": {k: round(v, 4) for k, v in ms.items()},
                      "us_per_step_layer0": ms["gru_l0"] * 1e3 / T, "us_per_step_layer1": ms["gru_l1"] * 1e3 / T,
                      "forward_ms": sum(ms.values()), "frames_per_s": B * T / (sum(ms.values()) * 1e-3)}
-    net.set_recurrent("mma")
     print(json.dumps(res))
 
 
