@@ -115,25 +115,40 @@ __device__ __forceinline__ Best search(const float* ax, const float* ay, ColFn c
   return warp_argmin(b);
 }
 
-__global__ void __launch_bounds__(kWarps * 32)
+#ifndef ASB_TV_MINB
+#define ASB_TV_MINB 2
+#endif
+__global__ void __launch_bounds__(kWarps * 32, ASB_TV_MINB)
 tract_variables_kernel(const float* __restrict__ sets_ptr, long long sets, int n_art, ArtIndex ai,
                        const float* __restrict__ uinc_ext, long long uinc_stride,
                        float* __restrict__ val, int* __restrict__ idx, float* __restrict__ poc) {
-  __shared__ __align__(16) float sm[kWarps][S_COUNT * kItemF];
+  // persistent warps: the next set's six contours are copied global -> shared (cp.async, no
+  // registers) while the current one is searched; without this 23 % of the issue slots waited on
+  // the staging loads (profiles/r1c_geometry_ncu.txt)
+  __shared__ __align__(16) float sm[kWarps][2][S_COUNT * kItemF];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long set = (long long)blockIdx.x * kWarps + warp;
-  if (set >= sets) return;
-  float* s = sm[warp];
-  const float* base = sets_ptr + set * (long long)n_art * kItemF;
-  // 6 contours x 25 float4
-  for (int q = lane; q < S_COUNT * (kItemF / 4); q += 32) {
-    const int slot = q / (kItemF / 4), part = q - slot * (kItemF / 4);
-    // the upper incisor may live outside the set (evaluation.py:93-109 injects a reference contour)
-    const float* src = (slot == S_UINC && uinc_ext) ? uinc_ext + set * uinc_stride
-                                                    : base + (long long)ai.v[slot] * kItemF;
-    const float4 t = __ldg(reinterpret_cast<const float4*>(src) + part);
-    *reinterpret_cast<float4*>(s + slot * kItemF + 4 * part) = t;
-  }
+  const long long stride = (long long)gridDim.x * kWarps;
+  auto stage = [&](long long set, float* dst) {
+    const float* base = sets_ptr + set * (long long)n_art * kItemF;
+    // 6 contours x 25 x 16 bytes
+    for (int q = lane; q < S_COUNT * (kItemF / 4); q += 32) {
+      const int slot = q / (kItemF / 4), part = q - slot * (kItemF / 4);
+      // the upper incisor may live outside the set (evaluation.py:93-109 injects a reference contour)
+      const float* src = (slot == S_UINC && uinc_ext) ? uinc_ext + set * uinc_stride
+                                                      : base + (long long)ai.v[slot] * kItemF;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst + slot * kItemF + 4 * part)),
+                   "l"(src + 4 * part)
+                   : "memory");
+    }
+  };
+  long long set = (long long)blockIdx.x * kWarps + warp;
+  if (set < sets) stage(set, sm[warp][0]);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  for (int it = 0; set < sets; set += stride, ++it) {
+  float* s = sm[warp][it & 1];
+  if (set + stride < sets) stage(set + stride, sm[warp][(it + 1) & 1]);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 1;" ::: "memory");   // everything but the copy just issued has landed
   __syncwarp();
 
   const float* llip = s + S_LLIP * kItemF;
@@ -179,6 +194,8 @@ tract_variables_kernel(const float* __restrict__ sets_ptr, long long sets, int n
     p.w = a2[kD + b.j];
     *reinterpret_cast<float4*>(poc + 4 * o) = p;
   }
+  __syncwarp();   // every lane is done with this buffer before the copy after next overwrites it
+  }
 }
 
 }  // namespace
@@ -200,8 +217,9 @@ static int tv_launch(const float* sets_ptr, int64_t sets, int n_art, const int32
   if ((reinterpret_cast<uintptr_t>(sets_ptr) & 15) || (reinterpret_cast<uintptr_t>(poc) & 15) ||
       (reinterpret_cast<uintptr_t>(uinc) & 15) || (uinc_stride & 3))
     return asb::set_error(ASB_ERR_INVALID, "asb_tract_variables: sets/poc/upper_incisor must be 16-byte aligned");
-  const long long blocks = (sets + kWarps - 1) / kWarps;
-  if (blocks > 0x7fffffffLL) return asb::set_error(ASB_ERR_INVALID, "asb_tract_variables: too many sets");
+  long long blocks = (sets + kWarps - 1) / kWarps;
+  const long long resident = (long long)asb::sm_count() * ASB_TV_MINB;   // persistent: one wave of CTAs
+  if (blocks > resident) blocks = resident;
   tract_variables_kernel<<<unsigned(blocks), kWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
       sets_ptr, sets, n_art, ai, uinc, uinc_stride, val, idx, poc);
   ASB_CHECK_LAUNCH("tract_variables_kernel");
