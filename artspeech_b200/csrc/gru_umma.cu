@@ -25,6 +25,29 @@
 #include "model.cuh"
 #include "umma.cuh"
 
+#ifndef ASB_RNN_FENCE_AT_MMA
+#define ASB_RNN_FENCE_AT_MMA 0
+#endif
+#ifdef ASB_RNN_TRACE
+// timeline of CTA (0, 0) (tools/rnn_trace.py): [role][event] = (tag, clock64); role 0 = MMA warp, 1 = epilogue warp 0
+__device__ long long g_rnn_trace[2 * 4096];
+#define TR(role, tag)                                                                   \
+  do {                                                                                  \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && lane == 0 && tr_n < 2047) {               \
+      g_rnn_trace[(role) * 4096 + 2 * tr_n] = (tag);                                    \
+      g_rnn_trace[(role) * 4096 + 2 * tr_n + 1] = clock64();                            \
+      ++tr_n;                                                                           \
+    }                                                                                   \
+  } while (0)
+#define TR_DECL int tr_n = 0
+extern "C" __attribute__((visibility("default"))) int asb_debug_rnn_trace(long long* host_out) {
+  return int(cudaMemcpyFromSymbol(host_out, g_rnn_trace, sizeof(g_rnn_trace)));
+}
+#else
+#define TR(role, tag) do { } while (0)
+#define TR_DECL do { } while (0)
+#endif
+
 namespace {
 
 using namespace asb;
@@ -32,6 +55,7 @@ using namespace asb::umma;
 
 constexpr int kRows = 16;                    // the MMA's N (columns past the CTA's rows stay zero)
 constexpr int kTileBytes = 128 * kH * 2;     // one gate tile of W_hh in bf16: 32 KB
+constexpr int kAhead = 3, kGiSlots = 4;        // look-ahead of the input pre-activations (steps), ring slots
 constexpr int kACol0 = 64;                   // TMEM: accumulators in columns [0, G*16), W_hh from column 64
 constexpr int kHsBytes = 2 * kRows * 128;    // h as the B operand: 2 k-atoms x 16 rows x 128 B
 constexpr int kEpiWarps = 8;
@@ -71,6 +95,7 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // keeps the shared address space
   unsigned char* Hs = smem;                          // 4 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(Hs + kHsBytes);
+  float* Gs = reinterpret_cast<float*>(Hs + kHsBytes + 64);   // [kGiSlots][CPT][G][256 threads] input pre-activations
   uint64_t* h_ready = bars + 1;  // h (bf16) of this step is in shared memory, D has been read
   uint64_t* d_ready = bars + 2;  // this step's MMAs completed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
@@ -101,9 +126,14 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
     const uint32_t idesc = idesc_bf16_m128(kRows);
     const uint64_t bdesc0 = smem_desc_k_sw128(smem_u32(Hs));
     const uint32_t tmem_a = tmem_d + kACol0;
+    TR_DECL;
     for (int s = 0; s < Lmax; ++s) {
       mbar_wait(h_ready, s & 1);
+#if ASB_RNN_FENCE_AT_MMA
+      fence_proxy_async();     // the generic-proxy writes of h (ordered before the barrier) -> async proxy
+#endif
       fence_after_sync();
+      TR(0, 1);
       if (elect_one()) {
 #pragma unroll
         for (int g = 0; g < G; ++g)
@@ -116,6 +146,7 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
         commit(d_ready);
       }
       __syncwarp();
+      TR(0, 2);
     }
   } else {
     // thread = (hidden unit u = TMEM lane, CPT of the CTA's 2 * CPT batch rows)
@@ -152,40 +183,59 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
 #pragma unroll
     for (int j = 0; j < CPT; ++j) h[j] = cs[j] = 0.f;
 
-    float gin[CPT][G];
-    auto load_gi = [&](int t) {
+    // Input pre-activations are fetched kAhead steps before they are used, straight into shared
+    // memory with cp.async: gi (78 MB per layer at batch 256 x 100) streams from L2 / HBM and one
+    // step (~0.65 us) does not cover that latency - with one step of look-ahead in registers 31 % of
+    // the epilogue's issue slots waited on these loads, and deeper look-ahead in registers does not
+    // help because a scoreboard wait covers the youngest loads too; cp.async.wait_group counts groups.
+    // Each thread reads back only what it copied itself.  Rows past their length are not fetched:
+    // their gate values are computed from stale data and discarded by the `valid` selects.
+    auto fetch_gi = [&](int step) {
+      const int t = dir ? Lmax - 1 - step : step;
+      float* dst = Gs + (size_t)(step & (kGiSlots - 1)) * (CPT * G * 256) + (tid & 255);
 #pragma unroll
       for (int j = 0; j < CPT; ++j) {
-        if (t < len[j]) {
+        if (step < Lmax && t < len[j]) {
           const float* p = a.gi + (((long long)(b0 + colhalf * CPT + j) * a.T + t) * 2 + dir) * GH + u;
 #pragma unroll
-          for (int g = 0; g < G; ++g) gin[j][g] = __ldg(p + g * kH);
-        } else {
-#pragma unroll
-          for (int g = 0; g < G; ++g) gin[j][g] = 0.f;
+          for (int g = 0; g < G; ++g)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst + (j * G + g) * 256)),
+                         "l"(p + g * kH)
+                         : "memory");
         }
       }
+      asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    if (Lmax > 0) load_gi(dir ? Lmax - 1 : 0);
+#pragma unroll 1
+    for (int k = 0; k < kAhead; ++k) fetch_gi(k);
     // h0 (zeros) is in place: first hand-over to the MMA thread
     __syncwarp();
     if (lane == 0) mbar_arrive(h_ready);
 
+    TR_DECL;
     for (int s = 0; s < Lmax; ++s) {
       const int t = dir ? Lmax - 1 - s : s;
+      if (warp == 0) TR(1, 15);
+      fetch_gi(s + kAhead);   // into the slot that was read a step ago
+      asm volatile("cp.async.wait_group %0;" ::"n"(kAhead) : "memory");   // this step's group has landed
       float gc[CPT][G];
+      {
+        const float* src = Gs + (size_t)(s & (kGiSlots - 1)) * (CPT * G * 256) + (tid & 255);
 #pragma unroll
-      for (int j = 0; j < CPT; ++j)
+        for (int j = 0; j < CPT; ++j)
 #pragma unroll
-        for (int g = 0; g < G; ++g) gc[j][g] = gin[j][g];
-      if (s + 1 < Lmax) load_gi(dir ? t - 1 : t + 1);   // in flight while the MMAs run
+          for (int g = 0; g < G; ++g) gc[j][g] = src[(j * G + g) * 256];
+      }
+      if (warp == 0) TR(1, 10);
 
       mbar_wait(d_ready, s & 1);
       fence_after_sync();
+      if (warp == 0) TR(1, 11);
       uint32_t d[G][CPT];
 #pragma unroll
       for (int g = 0; g < G; ++g) tmem_ldn(taddr + g * kRows, d[g]);
       tmem_ld_wait();
+      if (warp == 0) TR(1, 12);
 
 #pragma unroll
       for (int j = 0; j < CPT; ++j) {
@@ -208,12 +258,22 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
         h[j] = valid ? hn : h[j];
         const int n = colhalf * CPT + j;
         *reinterpret_cast<__nv_bfloat16*>(Hs + sw128_bf16(n, u, kRows * 128)) = __float2bfloat16_rn(h[j]);
-        if (valid) a.out[((long long)(b0 + n) * a.T + t) * (2 * kH) + dir * kH + u] = h[j];
       }
+      if (warp == 0) TR(1, 13);
+#if !ASB_RNN_FENCE_AT_MMA
       fence_proxy_async();     // the generic-proxy writes of h must be visible to the tensor core
+#endif
       fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(h_ready);
+      if (warp == 0) TR(1, 14);
+      // the fp32 output rows go out AFTER the hand-over: stores in flight ahead of the proxy fence
+      // would be waited for on the step's critical path
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) {
+        const int n = colhalf * CPT + j;
+        if (t < len[j]) a.out[((long long)(b0 + n) * a.T + t) * (2 * kH) + dir * kH + u] = h[j];
+      }
     }
   }
 
@@ -246,7 +306,7 @@ int pack_whh_umma(asb_model* m, const asb_weights* src, cudaStream_t st) {
 
 template <int G>
 static int launch_rnn_umma_g(const asb_model* m, const RnnArgs& a, int B, cudaStream_t st) {
-  const int smem = kHsBytes + 64 + 1024;
+  const int smem = kHsBytes + 64 + 1024 + kGiSlots * 8 * G * 1024;   // sized for CPT = 8
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(rnn_umma_kernel<G, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
