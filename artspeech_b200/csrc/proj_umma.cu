@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(kThreads, 1) proj_umma_kernel(const ProjArgs a
     }
     __syncwarp();
   } else if (warp == kMmaWarp) {
-    if (lane == 0) {
+    {   // the whole warp walks the loop, one elected lane issues (see decoder_umma.cu)
       const uint32_t idesc = idesc_tf32_m128(kBlockN);
       uint32_t c = 0, dcount = 0, ucount = 0;
       for (int u = blockIdx.x; u < a.n_units; u += gridDim.x) {
@@ -134,13 +134,16 @@ __global__ void __launch_bounds__(kThreads, 1) proj_umma_kernel(const ProjArgs a
             mbar_wait(&full[s], (c / kStages) & 1);
             fence_after_sync();
             const uint64_t bdesc = smem_desc_k_sw128(smem_u32(Ws + s * kStageFloats));
+            if (elect_one()) {
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks)
-              mma_tf32_ts(tmem_d, tmem_a + j * kChunkK + ks * 8, bdesc + uint64_t(2 * ks), idesc, (j | ks) != 0);
-            commit(&empty[s]);
+              for (int ks = 0; ks < 4; ++ks)
+                mma_tf32_ts(tmem_d, tmem_a + j * kChunkK + ks * 8, bdesc + uint64_t(2 * ks), idesc, (j | ks) != 0);
+              commit(&empty[s]);
+              if (j == kChunks - 1) commit(&d_full[b]);
+            }
+            __syncwarp();
             ++c;
           }
-          commit(&d_full[b]);
           ++dcount;
         }
       }
