@@ -82,7 +82,10 @@ __global__ void pack_whh_umma_kernel(const float* __restrict__ whh, __nv_bfloat1
 struct RnnArgs {
   const __nv_bfloat16* img[2];   // per direction
   const float* bhhn[2];          // GRU: b_hh of the n gate
-  const float* gi;               // (B*T, 2, G*H)
+  const float* gi;               // (B*T, 2, G*H) input pre-activations, or (layer 0) null:
+  const long long* tokens;       //   (B, T_in) token ids and
+  const float* tab;              //   tab0[dir][token][G*H] = embedding . W_ih_l0^T + folded biases (model.cuh)
+  int T_in, V;
   const int* lengths;            // (B) sorted descending
   float* out;                    // (B, T, 2H), pre-zeroed
   int B, T;
@@ -96,6 +99,7 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
   unsigned char* Hs = smem;                          // 4 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(Hs + kHsBytes);
   float* Gs = reinterpret_cast<float*>(Hs + kHsBytes + 64);   // [kGiSlots][CPT][G][256 threads] input pre-activations
+  int* Toks = reinterpret_cast<int*>(Gs + kGiSlots * CPT * G * 256);   // [2 * CPT rows][T] token ids (layer 0)
   uint64_t* h_ready = bars + 1;  // h (bf16) of this step is in shared memory, D has been read
   uint64_t* d_ready = bars + 2;  // this step's MMAs completed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
@@ -114,6 +118,13 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
   }
   if (warp == kCtlWarp) tmem_alloc(tmem_slot, kTmemCols);
   for (int i = tid; i < kHsBytes / 4; i += kThreads) reinterpret_cast<uint32_t*>(Hs)[i] = 0u;   // h0 = 0
+  if (a.tokens) {   // layer 0: the embedding + input projection is a table look-up done by this kernel
+    for (int i = tid; i < 2 * CPT * a.T; i += kThreads) {
+      const int row = i / a.T, t = i - row * a.T;
+      long long tok = (b0 + row < a.B) ? a.tokens[(long long)(b0 + row) * a.T_in + t] : 0;
+      Toks[i] = int(tok < 0 ? 0 : (tok >= a.V ? a.V - 1 : tok));
+    }
+  }
   fence_proxy_async();
   fence_before_sync();
   __syncthreads();
@@ -196,7 +207,9 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
 #pragma unroll
       for (int j = 0; j < CPT; ++j) {
         if (step < Lmax && t < len[j]) {
-          const float* p = a.gi + (((long long)(b0 + colhalf * CPT + j) * a.T + t) * 2 + dir) * GH + u;
+          const float* p = a.tokens
+                               ? a.tab + ((long long)dir * a.V + Toks[(colhalf * CPT + j) * a.T + t]) * GH + u
+                               : a.gi + (((long long)(b0 + colhalf * CPT + j) * a.T + t) * 2 + dir) * GH + u;
 #pragma unroll
           for (int g = 0; g < G; ++g)
             asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst + (j * G + g) * 256)),
@@ -304,24 +317,30 @@ int pack_whh_umma(asb_model* m, const asb_weights* src, cudaStream_t st) {
   return ASB_OK;
 }
 
+constexpr int kMaxTokenBytes = 64 * 1024;   // token ids staged per CTA (16 rows x 1024 steps)
+
 template <int G>
-static int launch_rnn_umma_g(const asb_model* m, const RnnArgs& a, int B, cudaStream_t st) {
-  const int smem = kHsBytes + 64 + 1024 + kGiSlots * 8 * G * 1024;   // sized for CPT = 8
+static int launch_rnn_umma_g(const asb_model* m, RnnArgs& a, int B, bool use_tokens, cudaStream_t st) {
+  const int sms = sm_count();
+  // fewest rows per CTA that still fit one wave of the machine (the gate math bounds a step)
+  const int cpt = (2 * ((B + 3) / 4) <= sms) ? 2 : (2 * ((B + 7) / 8) <= sms) ? 4 : 8;
+  const int tok_bytes = 2 * cpt * a.T * 4;
+  if (!use_tokens || tok_bytes > kMaxTokenBytes) a.tokens = nullptr;   // the caller materialised gi instead
+  const int smem = kHsBytes + 64 + 1024 + kGiSlots * cpt * G * 1024 + (a.tokens ? tok_bytes : 0);
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(rnn_umma_kernel<G, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    const int max_smem = kHsBytes + 64 + 1024 + kGiSlots * 8 * G * 1024 + kMaxTokenBytes;
+    cudaError_t e = cudaFuncSetAttribute(rnn_umma_kernel<G, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(rnn_umma_kernel<G, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      e = cudaFuncSetAttribute(rnn_umma_kernel<G, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(rnn_umma_kernel<G, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      e = cudaFuncSetAttribute(rnn_umma_kernel<G, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e != cudaSuccess) return check_cuda(e, "rnn_umma_kernel smem attribute");
     configured = true;
   }
-  // fewest rows per CTA that still fit one wave of the machine (the gate math bounds a step)
-  const int sms = sm_count();
-  if (2 * ((B + 3) / 4) <= sms) {
+  if (cpt == 2) {
     rnn_umma_kernel<G, 2><<<dim3((B + 3) / 4, 2), kThreads, smem, st>>>(a);
-  } else if (2 * ((B + 7) / 8) <= sms) {
+  } else if (cpt == 4) {
     rnn_umma_kernel<G, 4><<<dim3((B + 7) / 8, 2), kThreads, smem, st>>>(a);
   } else {
     rnn_umma_kernel<G, 8><<<dim3((B + 15) / 16, 2), kThreads, smem, st>>>(a);
@@ -330,15 +349,24 @@ static int launch_rnn_umma_g(const asb_model* m, const RnnArgs& a, int B, cudaSt
   return ASB_OK;
 }
 
-int launch_rnn_umma(const asb_model* m, int layer, const float* gi, const int* lengths, float* out, int B, int T,
-                    cudaStream_t st) {
+// layer 0 may read its input pre-activations through the token table instead of a materialised gi
+bool rnn_umma_reads_tokens(const asb_model* m, int B, int T) {
+  const int sms = sm_count();
+  const int cpt = (2 * ((B + 3) / 4) <= sms) ? 2 : (2 * ((B + 7) / 8) <= sms) ? 4 : 8;
+  return rnn_umma_supported(m) && 2 * cpt * T * 4 <= kMaxTokenBytes;
+}
+
+int launch_rnn_umma(const asb_model* m, int layer, const float* gi, const long long* tokens, int T_in,
+                    const int* lengths, float* out, int B, int T, cudaStream_t st) {
   RnnArgs a;
   for (int d = 0; d < 2; ++d) {
     a.img[d] = reinterpret_cast<const __nv_bfloat16*>(m->w.whh_umma[layer][d]);
     a.bhhn[d] = m->w.bhh_n[layer][d];
   }
   a.gi = gi; a.lengths = lengths; a.out = out; a.B = B; a.T = T;
-  return m->G == 3 ? launch_rnn_umma_g<3>(m, a, B, st) : launch_rnn_umma_g<4>(m, a, B, st);
+  a.tokens = tokens; a.tab = m->w.tab0; a.T_in = T_in; a.V = m->V;
+  const bool use_tokens = tokens != nullptr && layer == 0;
+  return m->G == 3 ? launch_rnn_umma_g<3>(m, a, B, use_tokens, st) : launch_rnn_umma_g<4>(m, a, B, use_tokens, st);
 }
 
 }  // namespace asb

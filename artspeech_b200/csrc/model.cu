@@ -222,10 +222,14 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
     if (prof) cudaEventRecord(ev[k], st);
   };
   mark(0);
-  if ((rc = launch_gather_gi0(m, tok, T_in, ws.gi, B, T, st))) return rc;
+  const bool umma_rnn = m->rnn_impl == 1 && m->w.whh_umma[0][0];
+  // the tcgen05 recurrent kernel looks the embedding / layer-0 projection table up itself
+  const bool fused_gather = umma_rnn && rnn_umma_reads_tokens(m, B, T);
+  if (!fused_gather && (rc = launch_gather_gi0(m, tok, T_in, ws.gi, B, T, st))) return rc;
   mark(1);
-  if (m->rnn_impl == 1 && m->w.whh_umma[0][0]) {
-    if ((rc = launch_rnn_umma(m, 0, ws.gi, ws.lengths, ws.out0, B, T, st))) return rc;
+  if (umma_rnn) {
+    if ((rc = launch_rnn_umma(m, 0, ws.gi, fused_gather ? tok : nullptr, T_in, ws.lengths, ws.out0, B, T, st)))
+      return rc;
   } else {
     if ((rc = launch_recurrent_layer(m, 0, ws.gi, ws.lengths, ws.out0, B, T, st))) return rc;
   }
@@ -237,7 +241,7 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
   }
   mark(3);
   if (m->rnn_impl == 1 && m->w.whh_umma[0][0]) {
-    if ((rc = launch_rnn_umma(m, 1, ws.gi, ws.lengths, ws.out1, B, T, st))) return rc;
+    if ((rc = launch_rnn_umma(m, 1, ws.gi, nullptr, 0, ws.lengths, ws.out1, B, T, st))) return rc;
   } else {
     if ((rc = launch_recurrent_layer(m, 1, ws.gi, ws.lengths, ws.out1, B, T, st))) return rc;
   }

@@ -94,7 +94,9 @@ int launch_proj_umma(const asb_model* m, const float* A, float* C, int M, cudaSt
 size_t whh_umma_bytes(const asb_model* m);
 bool rnn_umma_supported(const asb_model* m);
 int pack_whh_umma(asb_model* m, const asb_weights* w, cudaStream_t st);
-int launch_rnn_umma(const asb_model* m, int layer, const float* gi, const int* lengths, float* out, int B, int T,
-                    cudaStream_t st);
+// tokens != null (layer 0 only): gi is not read, the kernel looks tab0 up itself
+int launch_rnn_umma(const asb_model* m, int layer, const float* gi, const long long* tokens, int T_in,
+                    const int* lengths, float* out, int B, int T, cudaStream_t st);
+bool rnn_umma_reads_tokens(const asb_model* m, int B, int T);
 
 }  // namespace asb
