@@ -47,19 +47,29 @@ utterance_partials_kernel(const float* __restrict__ p2cp, const float* __restric
   }
 }
 
-__global__ void __launch_bounds__(64)
+// one warp per accumulator column: lane l adds utterances l, l + 32, ... in order, then the fixed
+// shuffle tree - a fixed summation order (a serial loop over the utterances took 24 us of
+// dependent loads)
+__global__ void __launch_bounds__(1024)
 reduce_partials_kernel(const double* __restrict__ partial, const int* __restrict__ lengths, int B, int T, int n_art,
                        double* __restrict__ acc) {
-  const int j = threadIdx.x, cols = n_art + 12;
-  if (j < cols) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, cols = n_art + 12;
+  for (int j = warp; j <= cols; j += 32) {
     double s = 0.0;
-    for (int b = 0; b < B; ++b) s += partial[(size_t)b * cols + j];
-    acc[j < n_art ? j : j + 1] = s;
-  } else if (j == cols) {
-    long long frames = 0;
-    for (int b = 0; b < B; ++b) frames += min(lengths[b], T);
-    acc[n_art] = double(B);
-    acc[n_art + 13] = double(frames);
+    if (j < cols) {
+      for (int b = lane; b < B; b += 32) s += partial[(size_t)b * cols + j];
+    } else {
+      for (int b = lane; b < B; b += 32) s += double(min(lengths[b], T));   // exact: integers far below 2^53
+    }
+    s = warp_sum_f64(s);
+    if (lane == 0) {
+      if (j < cols) {
+        acc[j < n_art ? j : j + 1] = s;
+      } else {
+        acc[n_art] = double(B);
+        acc[n_art + 13] = s;
+      }
+    }
   }
 }
 
@@ -75,7 +85,7 @@ extern "C" int asb_eval_accumulate(const float* p2cp, const float* tv_pred, cons
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   utterance_partials_kernel<<<B, 256, 0, st>>>(p2cp, tv_pred, tv_target, lengths_dev, T, n_art, scratch);
   ASB_CHECK_LAUNCH("utterance_partials_kernel");
-  reduce_partials_kernel<<<1, 64, 0, st>>>(scratch, lengths_dev, B, T, n_art, acc);
+  reduce_partials_kernel<<<1, 1024, 0, st>>>(scratch, lengths_dev, B, T, n_art, acc);
   ASB_CHECK_LAUNCH("reduce_partials_kernel");
   return ASB_OK;
 }
