@@ -245,20 +245,21 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
       UnitIter units(a);
       int tile, g0, g1;
       while (units.next(tile, g0, g1)) {
-        {   // pull the NEXT unit's input tile towards L2 while this unit is being computed
-          UnitIter peek = units;
-          int t2, h0, h1;
-          if (peek.next(t2, h0, h1) && t2 != tile) {
-            const long long row0 = (long long)t2 * kTileM;
-            const long long rows = min((long long)kTileM, a.M - row0);
-            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.rnn_out + row0 * 256),
-                         "r"(uint32_t(rows * 256 * 4))
-                         : "memory");
-          }
-        }
         for (int j = 0; j < 4; ++j) push(a.image + kLinParams + 2 * j * kLinChunk, 2 * kLinChunk * 4);
         for (int k = 0; k < g1 - g0; ++k) {
           const int art = g0 + k;
+          if (k == g1 - g0 - 1) {   // last articulator of this unit: pull the NEXT unit's input tile towards L2
+            // (issued a whole unit ahead, the tile was evicted again by the output stream before its use)
+            UnitIter peek = units;
+            int t2, h0, h1;
+            if (peek.next(t2, h0, h1) && t2 != tile) {
+              const long long row0 = (long long)t2 * kTileM;
+              const long long rows = min((long long)kTileM, a.M - row0);
+              asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.rnn_out + row0 * 256),
+                           "r"(uint32_t(rows * 256 * 4))
+                           : "memory");
+            }
+          }
           const float* blk = a.image + kLinBlock + (size_t)art * kArtBlock;
           const uint32_t pb = pa & 1;
           mbar_wait(&pempty[pb], ((pa >> 1) & 1) ^ 1);
