@@ -185,10 +185,14 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
       fence_before_sync();
     }
     int len[CPT];
+    const float* gi_row[CPT];   // per-row bases: one multiply-add per step instead of a 64-bit chain
+    float* out_row[CPT];
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
       const int b = b0 + colhalf * CPT + j;
       len[j] = b < a.B ? a.lengths[b] : 0;
+      gi_row[j] = a.gi + ((long long)b * a.T * 2 + dir) * GH + u;
+      out_row[j] = a.out + (long long)b * a.T * (2 * kH) + dir * kH + u;
     }
     float h[CPT], cs[CPT];   // cs: LSTM cell state (unused by the GRU)
 #pragma unroll
@@ -209,7 +213,7 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
         if (step < Lmax && t < len[j]) {
           const float* p = a.tokens
                                ? a.tab + ((long long)dir * a.V + Toks[(colhalf * CPT + j) * a.T + t]) * GH + u
-                               : a.gi + (((long long)(b0 + colhalf * CPT + j) * a.T + t) * 2 + dir) * GH + u;
+                               : gi_row[j] + (long long)t * (2 * GH);
 #pragma unroll
           for (int g = 0; g < G; ++g)
             asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst + (j * G + g) * 256)),
@@ -284,8 +288,7 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
       // would be waited for on the step's critical path
 #pragma unroll
       for (int j = 0; j < CPT; ++j) {
-        const int n = colhalf * CPT + j;
-        if (t < len[j]) a.out[((long long)(b0 + n) * a.T + t) * (2 * kH) + dir * kH + u] = h[j];
+        if (t < len[j]) out_row[j][(long long)t * (2 * kH)] = h[j];
       }
     }
   }
