@@ -73,6 +73,71 @@ reduce_partials_kernel(const double* __restrict__ partial, const int* __restrict
   }
 }
 
+// ---- per-sentence MED and Pearson correlations (run_test, evaluation.py:68-84) ------------------
+// One block per (utterance, articulator); thread d < D owns point d: over the valid frames it sums
+// the point distance (MED, metrics.py:54-68 over phoneme_to_articulation/metrics.py:10-24) and the
+// five moments per coordinate from which pearsons_correlation (metrics.py:9-35) follows - including
+// its quirk: the x TARGETS are centred with the mean of the x OUTPUTS (:22).  fp64 throughout.
+// partial[(b * n_art + art) * 3 + {0, 1, 2}] = mean MED, mean_d x_corr, mean_d y_corr of the sentence.
+__global__ void __launch_bounds__(64)
+sentence_metrics_kernel(const float* __restrict__ outputs, const float* __restrict__ targets,
+                        const int* __restrict__ lengths, int T, int n_art, int D, double* __restrict__ partial) {
+  const int b = blockIdx.x, art = blockIdx.y, d = threadIdx.x;
+  const int L = min(lengths[b], T);
+  const size_t frame_stride = (size_t)n_art * 2 * D;
+  const float* o = outputs + ((size_t)b * T * n_art + art) * 2 * D;
+  const float* g = targets + ((size_t)b * T * n_art + art) * 2 * D;
+  double med = 0.0, xc = 0.0, yc = 0.0;
+  if (d < D) {
+    double so[2] = {0, 0}, st[2] = {0, 0}, soo[2] = {0, 0}, stt[2] = {0, 0}, sot[2] = {0, 0};
+    for (int t = 0; t < L; ++t) {
+      const double xo = o[t * frame_stride + d], yo = o[t * frame_stride + D + d];
+      const double xt = g[t * frame_stride + d], yt = g[t * frame_stride + D + d];
+      med += sqrt((xo - xt) * (xo - xt) + (yo - yt) * (yo - yt));
+      so[0] += xo; st[0] += xt; soo[0] += xo * xo; stt[0] += xt * xt; sot[0] += xo * xt;
+      so[1] += yo; st[1] += yt; soo[1] += yo * yo; stt[1] += yt * yt; sot[1] += yo * yt;
+    }
+    const double n = double(L), eps = 1e-5;
+    {   // x: both series centred with the OUTPUT mean
+      const double m = so[0] / n;
+      const double voo = fmax(soo[0] - n * m * m, 0.0), vtt = fmax(stt[0] - 2.0 * m * st[0] + n * m * m, 0.0);
+      xc = (sot[0] - m * st[0]) / (sqrt(voo) * sqrt(vtt) + eps);
+    }
+    {   // y: the usual form
+      const double mo = so[1] / n, mt = st[1] / n;
+      const double voo = fmax(soo[1] - n * mo * mo, 0.0), vtt = fmax(stt[1] - n * mt * mt, 0.0);
+      yc = (sot[1] - n * mo * mt) / (sqrt(voo) * sqrt(vtt) + eps);
+    }
+  }
+  __shared__ double red[2][3];
+  med = warp_sum_f64(med);
+  xc = warp_sum_f64(xc);
+  yc = warp_sum_f64(yc);
+  if ((d & 31) == 0) {
+    red[d >> 5][0] = med;
+    red[d >> 5][1] = xc;
+    red[d >> 5][2] = yc;
+  }
+  __syncthreads();
+  if (d < 3) {
+    const double v = red[0][d] + red[1][d];
+    partial[((size_t)b * n_art + art) * 3 + d] = d == 0 ? v / (double(D) * double(L)) : v / double(D);
+  }
+}
+
+// acc[k * n_art + art] = sum over utterances of partial[.][art][k]  (fixed order: lane-strided, then the tree)
+__global__ void __launch_bounds__(1024)
+reduce_sentence_metrics_kernel(const double* __restrict__ partial, int B, int n_art, double* __restrict__ acc) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int j = warp; j < 3 * n_art; j += 32) {
+    const int k = j / n_art, art = j - k * n_art;
+    double s = 0.0;
+    for (int b = lane; b < B; b += 32) s += partial[((size_t)b * n_art + art) * 3 + k];
+    s = warp_sum_f64(s);
+    if (lane == 0) acc[j] = s;
+  }
+}
+
 }  // namespace
 
 extern "C" int asb_eval_accumulate(const float* p2cp, const float* tv_pred, const float* tv_target,
@@ -87,5 +152,20 @@ extern "C" int asb_eval_accumulate(const float* p2cp, const float* tv_pred, cons
   ASB_CHECK_LAUNCH("utterance_partials_kernel");
   reduce_partials_kernel<<<1, 1024, 0, st>>>(scratch, lengths_dev, B, T, n_art, acc);
   ASB_CHECK_LAUNCH("reduce_partials_kernel");
+  return ASB_OK;
+}
+
+extern "C" int asb_eval_sentence_metrics(const float* outputs, const float* targets, const int32_t* lengths_dev, int B,
+                                         int T, int n_art, int n_points, double* scratch, double* acc, void* stream) {
+  if (B <= 0 || T <= 0 || n_art <= 0 || n_points <= 0 || n_points > 64)
+    return asb::set_error(ASB_ERR_INVALID, "asb_eval_sentence_metrics: bad shape (B %d, T %d, n_art %d, points %d)", B,
+                          T, n_art, n_points);
+  if (!outputs || !targets || !lengths_dev || !scratch || !acc)
+    return asb::set_error(ASB_ERR_INVALID, "asb_eval_sentence_metrics: null pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  sentence_metrics_kernel<<<dim3(B, n_art), 64, 0, st>>>(outputs, targets, lengths_dev, T, n_art, n_points, scratch);
+  ASB_CHECK_LAUNCH("sentence_metrics_kernel");
+  reduce_sentence_metrics_kernel<<<1, 1024, 0, st>>>(scratch, B, n_art, acc);
+  ASB_CHECK_LAUNCH("reduce_sentence_metrics_kernel");
   return ASB_OK;
 }

@@ -65,6 +65,39 @@ def accumulate_device(p2cp, tv_pred, tv_tgt, lengths_dev):
     return acc
 
 
+def sentence_metrics_device(outputs, targets, lengths_dev):
+    """Sums over the batch's sentences of the per-sentence MED and Pearson correlations per
+    articulator (asb_eval_sentence_metrics; run_test, evaluation.py:68-84): (3, N) fp64 on the GPU,
+    rows = MED, x_corr, y_corr.  outputs/targets (B,T,N,2,D) fp32 on the GPU, lengths_dev (B) int32."""
+    from . import _lib
+    B, T, n, _, D = outputs.shape
+    dev = outputs.device
+    tgt = targets[:, :T]
+    scratch = torch.empty(B * n * 3, dtype=torch.float64, device=dev)
+    acc = torch.empty(3 * n, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().asb_eval_sentence_metrics(
+            _lib.ptr(outputs.contiguous()), _lib.ptr(tgt.contiguous()), _lib.ptr(lengths_dev), B, T, n, D,
+            _lib.ptr(scratch), _lib.ptr(acc), _lib.stream_ptr(dev)))
+    return acc.view(3, n)
+
+
+def run_test_info(acc, sentence_acc, n_articulators, to_mm=1.0, articulators=None):
+    """The per-articulator block of run_test's ``info`` dict (evaluation.py:146-159) from the reduced
+    accumulators: {art: {x_corr, y_corr, p2cp, p2cp_mm, med, med_mm}}."""
+    articulators = articulators or synthetic.ARTICULATORS
+    a = acc.detach().cpu().tolist()
+    s = sentence_acc.detach().cpu().view(3, -1).tolist()
+    n = n_articulators
+    utt = a[n]
+    info = {}
+    for i, art in enumerate(articulators[:n]):
+        p2cp, med = a[i] / utt, s[0][i] / utt
+        info[art] = {"x_corr": s[1][i] / utt, "y_corr": s[2][i] / utt, "p2cp": p2cp, "p2cp_mm": p2cp * to_mm,
+                     "med": med, "med_mm": med * to_mm}
+    return info
+
+
 def shard_utterances(n_utterances, rank, world):
     """Indices of the utterances rank ``rank`` of ``world`` owns (round-robin)."""
     return list(range(rank, n_utterances, world))

@@ -126,6 +126,17 @@ ASB_API int asb_eval_accumulate(const float* p2cp, const float* tv_pred, const f
                         const int32_t* lengths_dev, int B, int T, int n_art, double* scratch,
                         double* acc, void* stream);
 
+/* The other per-sentence numbers of run_test (evaluation.py:68-84): outputs/targets
+ * (B,T,n_art,2,n_points) fp32 planar, lengths_dev (B) DEVICE int32.  Per sentence and articulator:
+ * the mean over valid frames of euclidean_distance (metrics.py:54-68) and, over the valid frames as
+ * the time axis, pearsons_correlation (metrics.py:9-35, with its quirk: x targets centred by the x
+ * OUTPUT mean, :22) averaged over the points.  scratch: B*n_art*3 doubles.  acc (3*n_art doubles) is
+ * OVERWRITTEN with the sums over the B sentences of [0:n) MED, [n:2n) x_corr, [2n:3n) y_corr (divide
+ * by the sentence count for run_test's means, evaluation.py:150-156).  fp64, fixed summation order. */
+ASB_API int asb_eval_sentence_metrics(const float* outputs, const float* targets, const int32_t* lengths_dev,
+                              int B, int T, int n_art, int n_points, double* scratch, double* acc,
+                              void* stream);
+
 /* ------------------------------------------------------------------ model */
 
 typedef struct asb_model asb_model;

@@ -90,6 +90,32 @@ def golden_p2cp():
     print("p2cp:", tuple(ref64.shape), "reference fp32-vs-fp64 max rel", rel)
 
 
+def golden_sentence_metrics():
+    """run_test's per-sentence numbers (evaluation.py:68-84) from the reference's own metrics.py:
+    p2cp / euclidean means over the sentence and pearsons_correlation with the sentence as batch."""
+    rm = ref.root_metrics()
+    B, T, N = 3, 17, 10
+    lengths = [17, 11, 1]
+    tgt = synthetic.contours(B * T, N, 50, seed=15).view(B, T, N, 2, 50)
+    pred = synthetic.perturbed(tgt.view(B * T, N, 2, 50), seed=16).view(B, T, N, 2, 50)
+    # a smooth drift over time so that the correlations are not all ~1
+    drift = 0.02 * torch.sin(torch.arange(T, dtype=torch.float32) * 0.7).view(1, T, 1, 1, 1)
+    pred = pred + drift * torch.linspace(-1, 1, 50).view(1, 1, 1, 1, 50)
+    out = np.zeros((4, B, N))
+    with torch.no_grad():
+        for b, L in enumerate(lengths):
+            so = pred[b, :L].unsqueeze(0).double()
+            st = tgt[b, :L].unsqueeze(0).double()
+            out[0, b] = rm.p2cp_distance(so, st).mean(dim=1)[0].numpy()
+            out[1, b] = rm.euclidean_distance(so, st).mean(dim=1)[0].numpy()
+            xc, yc = rm.pearsons_correlation(so, st)
+            out[2, b] = xc.mean(dim=-1)[0].numpy()
+            out[3, b] = yc.mean(dim=-1)[0].numpy()
+    np.savez_compressed(os.path.join(GOLDEN, "sentence_metrics.npz"), pred=pred.numpy(), target=tgt.numpy(),
+                        lengths=np.array(lengths), per_sentence=out)
+    print("sentence_metrics:", out.shape, "x_corr range", out[2].min(), out[2].max())
+
+
 def golden_tv():
     tv = ref.tract_variables()
     frames = synthetic.tv_frames(24, seed=7)
@@ -162,4 +188,5 @@ if __name__ == "__main__":
     golden_model()
     golden_p2cp()
     golden_tv()
+    golden_sentence_metrics()
     golden_area()

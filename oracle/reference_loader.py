@@ -55,6 +55,25 @@ def p2a_metrics():
     return _load("_ref_p2a_metrics", "phoneme_to_articulation/metrics.py")
 
 
+def root_metrics():
+    """reference metrics.py (pearsons_correlation, p2cp_distance, euclidean_distance).  Its imports of
+    the un-vendored ``vt_tools.metrics.p2cp_mean`` (unused by these functions) and of the
+    ``phoneme_to_articulation`` package (whose __init__ needs vt_tools / vt_shape_gen) are stubbed:
+    the package stub only carries the real phoneme_to_articulation/metrics.py module."""
+    _stub_vt_tools()
+    if "vt_tools.metrics" not in sys.modules:
+        m = types.ModuleType("vt_tools.metrics")
+        m.p2cp_mean = None
+        m.euclidean = None
+        sys.modules["vt_tools.metrics"] = m
+    if "phoneme_to_articulation" not in sys.modules:
+        pkg = types.ModuleType("phoneme_to_articulation")
+        pkg.__path__ = []
+        sys.modules["phoneme_to_articulation"] = pkg
+        sys.modules["phoneme_to_articulation.metrics"] = p2a_metrics()
+    return _load("_ref_root_metrics", "metrics.py")
+
+
 def tract_variables():
     """reference tract_variables.py with the vt_tools constant stub"""
     _stub_vt_tools()

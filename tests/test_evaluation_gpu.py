@@ -81,3 +81,51 @@ def test_streamed_evaluator_matches_step_by_step():
     for a, b in zip(got, want):
         assert torch.equal(a, b)
     assert len(st.run(batches[:1])) == 1 and torch.equal(st.run(batches[:1])[0], want[0])
+
+
+def test_sentence_metrics_match_reference_run_test_numbers():
+    """asb_eval_sentence_metrics (per-sentence MED and Pearson correlations, run_test
+    evaluation.py:68-84) against numbers produced by the reference's own metrics.py, and the
+    run_test info block assembled from the two accumulator vectors."""
+    import os
+    import numpy as np
+    import torch
+    from artspeech_b200 import evaluation, metrics, synthetic
+    from artspeech_b200.tract_variables import tract_variables_batch
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "sentence_metrics.npz"))
+    pred = torch.from_numpy(g["pred"]).cuda()
+    tgt = torch.from_numpy(g["target"]).cuda()
+    lengths = g["lengths"].tolist()
+    ld = torch.tensor(lengths, dtype=torch.int32, device="cuda")
+    sacc = evaluation.sentence_metrics_device(pred, tgt, ld)
+    want = g["per_sentence"][1:4].sum(axis=1)                      # (3, N): sums over the sentences
+    np.testing.assert_allclose(sacc.cpu().numpy(), want, rtol=1e-9, atol=1e-12)
+    # the complete per-articulator block of run_test's info dict
+    p2cp = metrics.p2cp_distance(pred, tgt)
+    tvp = tract_variables_batch(pred, synthetic.ARTICULATORS, synthetic.UPPER_INCISOR_REF.cuda())[0]
+    tvt = tract_variables_batch(tgt, synthetic.ARTICULATORS, synthetic.UPPER_INCISOR_REF.cuda())[0]
+    acc = evaluation.accumulate_device(p2cp, tvp, tvt, ld)
+    info = evaluation.run_test_info(acc, sacc, 10, to_mm=2.0)
+    B = len(lengths)
+    for i, art in enumerate(synthetic.ARTICULATORS[:10]):
+        ref = g["per_sentence"][:, :, i].mean(axis=1)              # means over sentences: p2cp, med, x, y
+        assert abs(info[art]["p2cp"] - ref[0]) <= 1e-5 * ref[0]
+        assert abs(info[art]["med"] - ref[1]) <= 1e-9 * ref[1]
+        assert abs(info[art]["x_corr"] - ref[2]) <= 1e-9
+        assert abs(info[art]["y_corr"] - ref[3]) <= 1e-9
+        assert info[art]["p2cp_mm"] == info[art]["p2cp"] * 2.0 and info[art]["med_mm"] == info[art]["med"] * 2.0
+    # a larger ragged batch against the fp64 oracle
+    from oracle import geometry as ogeo
+    Bn, T = 37, 23
+    t2 = synthetic.contours(Bn * T, 10, 50, seed=31).view(Bn, T, 10, 2, 50)
+    p2 = synthetic.perturbed(t2.view(Bn * T, 10, 2, 50), seed=32).view(Bn, T, 10, 2, 50)
+    L2 = synthetic.sorted_lengths(Bn, 1, T, seed=33)
+    got = evaluation.sentence_metrics_device(p2.cuda(), t2.cuda(), torch.as_tensor(L2, dtype=torch.int32).cuda())
+    ref = np.zeros((3, 10))
+    for b, L in enumerate([int(v) for v in L2]):
+        so, st = p2[b, :L].unsqueeze(0), t2[b, :L].unsqueeze(0)
+        ref[0] += ogeo.euclidean_distance(so, st).mean(dim=1)[0].numpy()
+        xc, yc = ogeo.pearsons_correlation(so, st)
+        ref[1] += xc.mean(dim=-1)[0].numpy()
+        ref[2] += yc.mean(dim=-1)[0].numpy()
+    np.testing.assert_allclose(got.cpu().numpy(), ref, rtol=1e-8, atol=1e-9)

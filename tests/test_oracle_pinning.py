@@ -128,3 +128,22 @@ def test_live_reference_agrees_with_oracle():
         want = net.double()(x, L)
     got = omodel.artspeech_forward(sd, x, L, torch.float64)
     assert (got - want).abs().max() <= 1e-12
+
+
+def test_sentence_metrics_oracle_matches_reference_metrics_py(golden_dir):
+    """oracle.geometry (euclidean_distance, pearsons_correlation incl. the x-target-mean quirk, p2cp)
+    against per-sentence numbers produced by the reference's own metrics.py (oracle/make_golden.py)."""
+    import numpy as np
+    import torch
+    from oracle import geometry as ogeo
+    g = np.load(os.path.join(golden_dir, "sentence_metrics.npz"))
+    pred, tgt = torch.from_numpy(g["pred"]), torch.from_numpy(g["target"])
+    for b, L in enumerate(g["lengths"].tolist()):
+        so, st = pred[b, :L].unsqueeze(0), tgt[b, :L].unsqueeze(0)
+        p2cp = ogeo.p2cp_distance(so, st).mean(dim=1)[0].numpy()
+        med = ogeo.euclidean_distance(so, st).mean(dim=1)[0].numpy()
+        xc, yc = ogeo.pearsons_correlation(so, st)
+        np.testing.assert_allclose(p2cp, g["per_sentence"][0, b], rtol=1e-12)
+        np.testing.assert_allclose(med, g["per_sentence"][1, b], rtol=1e-12)
+        np.testing.assert_allclose(xc.mean(dim=-1)[0].numpy(), g["per_sentence"][2, b], rtol=1e-10, atol=1e-12)
+        np.testing.assert_allclose(yc.mean(dim=-1)[0].numpy(), g["per_sentence"][3, b], rtol=1e-10, atol=1e-12)
