@@ -73,6 +73,7 @@ constexpr int kChunkK = 32;                 // tf32 per 128-byte swizzle row
 constexpr int kStages = 4;                  // weight ring: 32 KB stages = one 256-row K chunk or two 128- / 112-row ones
 constexpr int kStageBytes = 256 * 128;
 constexpr int kXStride = 129;               // x-hat row stride (floats), conflict-free per-thread rows
+constexpr int kTilePitch = 36;              // per-warp 32 x 32 transposition tile of the input load (floats per row)
 constexpr int kEpiWarps = 8;                // two warps per TMEM lane quarter, each owning half the columns
 constexpr int kProducerWarp = 8, kMmaWarp = 9;
 constexpr int kHeadWarp0 = 10, kHeadWarps = 4;   // warps 10..13: output warps, TMEM lane quarter = warp % 4
@@ -531,26 +532,48 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma_kernel(const UmmaArg
     UnitIter units(a);
     int tile, g0, g1;
     while (units.next(tile, g0, g1)) {
-      const long long grow = (long long)tile * kTileM + row;
-      const bool live = grow < a.M;
-
-      // ---- input tile -> A0 (tf32) in Q: this thread converts 128 of its frame's 256 features
+      // ---- input tile -> A0 (tf32) in Q: this warp converts 32 rows x 128 of the 256 features
       {
         const uint32_t P = tmem_base + lane_sel + (artc & 1) * 256, Q = tmem_base + lane_sel + ((artc & 1) ^ 1) * 256;
         if (artc) wait_d(3, artc - 1);   // Q was the A operand of the previous heads GEMM
-        const float4* src = reinterpret_cast<const float4*>(a.rnn_out + grow * 256);
+        // Coalesced: a warp instruction reads 4 rows x 128 B (one 16-byte piece per lane), the 32 x 32
+        // block is turned to lane = row through a per-warp tile in the x-hat buffer, which is dead
+        // between units.  (One row per lane costs an L1 tag look-up per lane and instruction: the
+        // four chunks then took ~13 k clk per unit.)
+        float* tile32 = Xs + warp * (32 * kTilePitch);
+        const long long row0 = (long long)tile * kTileM + quarter * 32;
+        auto load_block = [&](int ch, uint32_t(&buf)[32]) {   // 8 x float4 per lane, in flight
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const long long gr = row0 + 4 * i + (lane >> 3);
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (gr < a.M) v = __ldg(reinterpret_cast<const float4*>(a.rnn_out + gr * 256 + 32 * ch) + (lane & 7));
+            buf[4 * i + 0] = __float_as_uint(v.x);
+            buf[4 * i + 1] = __float_as_uint(v.y);
+            buf[4 * i + 2] = __float_as_uint(v.z);
+            buf[4 * i + 3] = __float_as_uint(v.w);
+          }
+        };
+        load_block(half, r2);
 #pragma unroll 1
         for (int c = 0; c < 4; ++c) {
           const int ch = 2 * c + half;
 #pragma unroll
+          for (int i = 0; i < 8; ++i)
+            *reinterpret_cast<float4*>(tile32 + (4 * i + (lane >> 3)) * kTilePitch + 4 * (lane & 7)) =
+                make_float4(__uint_as_float(r2[4 * i + 0]), __uint_as_float(r2[4 * i + 1]),
+                            __uint_as_float(r2[4 * i + 2]), __uint_as_float(r2[4 * i + 3]));
+          __syncwarp();
+          if (c < 3) load_block(ch + 2, r2);   // the next block's loads fly under this block's conversion
+#pragma unroll
           for (int q = 0; q < 8; ++q) {
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (live) v = __ldg(src + 8 * ch + q);
+            const float4 v = *reinterpret_cast<const float4*>(tile32 + lane * kTilePitch + 4 * q);
             r[4 * q + 0] = to_tf32_finite(v.x);
             r[4 * q + 1] = to_tf32_finite(v.y);
             r[4 * q + 2] = to_tf32_finite(v.z);
             r[4 * q + 3] = to_tf32_finite(v.w);
           }
+          __syncwarp();   // the tile is rewritten by the next block
           tmem_st32(Q + 32 * ch, r);
           signal(&chunk[ch]);
         }
