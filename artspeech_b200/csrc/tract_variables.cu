@@ -33,86 +33,96 @@ struct Best {
   int i, j;
 };
 
-// Column scan: rows [0, P) of (ax, ay) against the single point (cx, cy).
-// Returns min squared distance and the smallest row index attaining it.
-template <int P>
-__device__ __forceinline__ void scan_rows(const float* __restrict__ ax, const float* __restrict__ ay, float cx,
-                                          float cy, float& best, int& best_i) {
+// Squared distance of row i of (ax, ay) to the point (cx, cy), with exactly the operations the
+// scan uses (packed subtract, multiply, fused multiply-add), so that re-evaluating a pair gives
+// the bit pattern the scan saw.
+__device__ __forceinline__ float pair_d2(const float* __restrict__ ax, const float* __restrict__ ay, int i, float cx,
+                                         float cy) {
+  const f32x2 dx = sub2(pack2(ax[i], ax[i]), pack2(cx, cx));
+  const f32x2 dy = sub2(pack2(ay[i], ay[i]), pack2(cy, cy));
+  float d0, d1;
+  unpack2(fma2(dy, dy, mul2(dx, dx)), d0, d1);
+  return d0;
+}
+
+// Column scan: minimum over the rows [0, P) of (ax, ay) of the squared distance to each of NC
+// column points.  The rows are read once (broadcast LDS.64) for all NC columns of the lane; only
+// the minimum is tracked here, the winning row is resolved afterwards for the one winning column.
+template <int P, int NC>
+__device__ __forceinline__ void scan_min(const float* __restrict__ ax, const float* __restrict__ ay,
+                                         const float (&cx)[NC], const float (&cy)[NC], float (&m)[NC]) {
   const float kInf = __int_as_float(0x7f800000);
-  const f32x2 vx = pack2(cx, cx), vy = pack2(cy, cy);
-  float m = kInf;
-  int step = 0;
+  f32x2 vx[NC], vy[NC];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    vx[c] = pack2(cx[c], cx[c]);
+    vy[c] = pack2(cy[c], cy[c]);
+    m[c] = kInf;
+  }
 #pragma unroll
   for (int s = 0; s < P / 2; ++s) {
     const f32x2 ux = *reinterpret_cast<const f32x2*>(ax + 2 * s);
     const f32x2 uy = *reinterpret_cast<const f32x2*>(ay + 2 * s);
-    const f32x2 dx = sub2(ux, vx), dy = sub2(uy, vy);
-    float d0, d1;
-    unpack2(fma2(dy, dy, mul2(dx, dx)), d0, d1);
-    const float mn = min3(m, d0, d1);
-    step = (mn < m) ? s : step;
-    m = mn;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const f32x2 dx = sub2(ux, vx[c]), dy = sub2(uy, vy[c]);
+      float d0, d1;
+      unpack2(fma2(dy, dy, mul2(dx, dx)), d0, d1);
+      m[c] = min3(m[c], d0, d1);
+    }
   }
   if (P & 1) {
-    const f32x2 ux = pack2(ax[P - 1], ax[P - 1]);
-    const f32x2 uy = pack2(ay[P - 1], ay[P - 1]);
-    const f32x2 dx = sub2(ux, vx), dy = sub2(uy, vy);
-    float d0, d1;
-    unpack2(fma2(dy, dy, mul2(dx, dx)), d0, d1);
-    const float mn = fminf(m, d0);
-    step = (mn < m) ? (P / 2) : step;
-    m = mn;
-  }
-  // resolve the row inside the winning pair with the same arithmetic
-  int row = 2 * step;
-  if (2 * step + 1 < P) {
-    const f32x2 ux = *reinterpret_cast<const f32x2*>(ax + 2 * step);
-    const f32x2 uy = *reinterpret_cast<const f32x2*>(ay + 2 * step);
-    const f32x2 dx = sub2(ux, vx), dy = sub2(uy, vy);
-    float d0, d1;
-    unpack2(fma2(dy, dy, mul2(dx, dx)), d0, d1);
-    row = (d0 == m) ? 2 * step : 2 * step + 1;
-  }
-  best = m;
-  best_i = row;
-}
-
-__device__ __forceinline__ Best warp_argmin(Best b) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const float od = __shfl_xor_sync(0xffffffffu, b.d, o);
-    const int oi = __shfl_xor_sync(0xffffffffu, b.i, o);
-    const int oj = __shfl_xor_sync(0xffffffffu, b.j, o);
-    const bool take = (od < b.d) || (od == b.d && oj < b.j);
-    b.d = take ? od : b.d;
-    b.i = take ? oi : b.i;
-    b.j = take ? oj : b.j;
+    for (int c = 0; c < NC; ++c) m[c] = fminf(m[c], pair_d2(ax, ay, P - 1, cx[c], cy[c]));
   }
-  return b;
 }
 
 // One search: rows = P points starting at (ax, ay); columns = R points, column j read through
-// the functor col(j, cx, cy).
+// the functor col(j, cx, cy).  A lane owns the columns lane and lane + 32.  The reduction orders
+// candidates by (distance, j) - the reference's argmin over the flattened (j, i) matrix picks the
+// smallest j among the global minima, then the smallest i for that j - and the row is found by
+// re-evaluating the winning column against every row, one row per lane.
 template <int P, int R, typename ColFn>
 __device__ __forceinline__ Best search(const float* ax, const float* ay, ColFn col, int lane) {
   const float kInf = __int_as_float(0x7f800000);
-  Best b{kInf, 0, 0x7fffffff};
+  constexpr int NC = (R + 31) / 32;
+  float cx[NC], cy[NC], m[NC];
 #pragma unroll
-  for (int pass = 0; pass < (R + 31) / 32; ++pass) {
-    const int j = lane + 32 * pass;
-    const int jc = j < R ? j : R - 1;  // clamp: idle lanes redo the last column, then are ignored
-    float cx, cy;
-    col(jc, cx, cy);
-    float d;
-    int i;
-    scan_rows<P>(ax, ay, cx, cy, d, i);
-    if (j < R && d < b.d) {  // strict: an equal later column never displaces an earlier one
-      b.d = d;
-      b.i = i;
-      b.j = j;
+  for (int c = 0; c < NC; ++c) {
+    const int j = lane + 32 * c;
+    col(j < R ? j : R - 1, cx[c], cy[c]);  // clamp: idle lanes redo the last column, then are ignored
+  }
+  scan_min<P, NC>(ax, ay, cx, cy, m);
+  float d = (lane < R) ? m[0] : kInf;
+  int j = lane;
+  if (NC > 1 && lane + 32 < R && m[NC - 1] < d) {  // strict: an equal later column never displaces an earlier one
+    d = m[NC - 1];
+    j = lane + 32;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float od = __shfl_xor_sync(0xffffffffu, d, o);
+    const int oj = __shfl_xor_sync(0xffffffffu, j, o);
+    const bool take = (od < d) || (od == d && oj < j);
+    d = take ? od : d;
+    j = take ? oj : j;
+  }
+  j = j < R ? j : R - 1;  // only reachable with non-finite input
+  float wx, wy;
+  col(j, wx, wy);
+  int row = P - 1;
+  bool found = false;
+#pragma unroll
+  for (int pass = 0; pass < (P + 31) / 32; ++pass) {
+    const int i = lane + 32 * pass;
+    const float di = pair_d2(ax, ay, i < P ? i : P - 1, wx, wy);
+    const unsigned hit = __ballot_sync(0xffffffffu, i < P && di == d);
+    if (!found && hit) {
+      row = 32 * pass + __ffs(hit) - 1;
+      found = true;
     }
   }
-  return warp_argmin(b);
+  return Best{d, row, j};
 }
 
 #ifndef ASB_TV_MINB
