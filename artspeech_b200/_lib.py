@@ -45,12 +45,17 @@ SIGNATURES = {
                                 ctypes.c_int, ctypes.c_void_p]),
     "asb_mean_euclidean": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_int,
                                           ctypes.c_void_p]),
+    "asb_min_distance": (ctypes.c_int, [_c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_int, ctypes.c_int, _c_f32p,
+                                        ctypes.c_void_p, ctypes.c_void_p]),
     "asb_tract_variables": (ctypes.c_int, [_c_f32p, ctypes.c_int64, ctypes.c_int,
                                            ctypes.POINTER(ctypes.c_int32), _c_f32p, ctypes.c_void_p, _c_f32p,
                                            ctypes.c_void_p]),
     "asb_tract_variables_ref": (ctypes.c_int, [_c_f32p, ctypes.c_int64, ctypes.c_int,
                                                ctypes.POINTER(ctypes.c_int32), _c_f32p, ctypes.c_int64, _c_f32p,
                                                ctypes.c_void_p, _c_f32p, ctypes.c_void_p]),
+    "asb_tract_variables_ex": (ctypes.c_int, [_c_f32p, ctypes.c_int64, ctypes.c_int,
+                                              ctypes.POINTER(ctypes.c_int32), _c_f32p, ctypes.c_int64, ctypes.c_int,
+                                              _c_f32p, ctypes.c_void_p, _c_f32p, ctypes.c_void_p]),
     "asb_area_function": (ctypes.c_int, [_c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_int, ctypes.c_void_p,
                                          ctypes.c_int, ctypes.c_double, ctypes.c_double, ctypes.c_int, _c_f32p,
                                          ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
@@ -67,6 +72,9 @@ SIGNATURES = {
     "asb_eval_sentence_metrics": (ctypes.c_int, [_c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                                  ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                                  ctypes.c_void_p]),
+    "asb_model_decode": (ctypes.c_int, [ctypes.c_void_p, _c_f32p, ctypes.c_int64, _c_f32p, ctypes.c_void_p]),
+    "asb_gather_rows": (ctypes.c_int, [_c_f32p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_int,
+                                       _c_f32p, ctypes.c_void_p]),
     "asb_model_set_decoder": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "asb_model_set_recurrent": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "asb_model_profile_enable": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),

@@ -87,7 +87,7 @@ struct RnnArgs {
   const float* tab;              //   tab0[dir][token][G*H] = embedding . W_ih_l0^T + folded biases (model.cuh)
   int T_in, V;
   const int* lengths;            // (B) sorted descending
-  float* out;                    // (B, T, 2H), pre-zeroed
+  float* out;                    // (B, T, 2H); every element is written (zeros at t >= length)
   int B, T;
 };
 
@@ -290,6 +290,13 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
       for (int j = 0; j < CPT; ++j) {
         if (t < len[j]) out_row[j][(long long)t * (2 * kH)] = h[j];
       }
+    }
+    // padded steps of the output are zero (pad_packed_sequence, models.py:138): written here, after
+    // the last step, so that the caller does not have to clear the whole (B, T, 2H) buffer first
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      if (b0 + colhalf * CPT + j < a.B)
+        for (int t = len[j]; t < a.T; ++t) out_row[j][(long long)t * (2 * kH)] = 0.f;
     }
   }
 

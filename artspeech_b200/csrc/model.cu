@@ -201,11 +201,15 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
                     "asb_model_forward: lengths H2D");
     if (rc) return rc;
   }
-  // padded steps of the recurrent outputs are zero (pad_packed_sequence, models.py:138)
-  rc = check_cuda(cudaMemsetAsync(ws.out0, 0, sizeof(float) * (size_t)M * 2 * kH, st), "asb_model_forward: memset");
-  if (rc) return rc;
-  rc = check_cuda(cudaMemsetAsync(ws.out1, 0, sizeof(float) * (size_t)M * 2 * kH, st), "asb_model_forward: memset");
-  if (rc) return rc;
+  // padded steps of the recurrent outputs are zero (pad_packed_sequence, models.py:138): the tcgen05
+  // recurrent kernel writes those zeros itself, the other kernels expect a cleared buffer
+  const bool umma_rnn = m->rnn_impl == 1 && m->w.whh_umma[0][0];
+  if (!umma_rnn) {
+    rc = check_cuda(cudaMemsetAsync(ws.out0, 0, sizeof(float) * (size_t)M * 2 * kH, st), "asb_model_forward: memset");
+    if (rc) return rc;
+    rc = check_cuda(cudaMemsetAsync(ws.out1, 0, sizeof(float) * (size_t)M * 2 * kH, st), "asb_model_forward: memset");
+    if (rc) return rc;
+  }
   const long long* tok = reinterpret_cast<const long long*>(x);
   std::array<cudaEvent_t, ASB_N_STAGES + 1> ev{};
   const bool prof = m->profile;
@@ -222,7 +226,6 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
     if (prof) cudaEventRecord(ev[k], st);
   };
   mark(0);
-  const bool umma_rnn = m->rnn_impl == 1 && m->w.whh_umma[0][0];
   // the tcgen05 recurrent kernel looks the embedding / layer-0 projection table up itself
   const bool fused_gather = umma_rnn && rnn_umma_reads_tokens(m, B, T);
   if (!fused_gather && (rc = launch_gather_gi0(m, tok, T_in, ws.gi, B, T, st))) return rc;
@@ -240,7 +243,7 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
     if ((rc = launch_linear(m, ws.out0, m->w.wih1, m->w.bih1, ws.gi, int(M), 2 * m->G * kH, 2 * kH, st))) return rc;
   }
   mark(3);
-  if (m->rnn_impl == 1 && m->w.whh_umma[0][0]) {
+  if (umma_rnn) {
     if ((rc = launch_rnn_umma(m, 1, ws.gi, nullptr, 0, ws.lengths, ws.out1, B, T, st))) return rc;
   } else {
     if ((rc = launch_recurrent_layer(m, 1, ws.gi, ws.lengths, ws.out1, B, T, st))) return rc;
@@ -254,6 +257,20 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
   mark(5);
   if (prof) m->pending.push_back(ev);
   return ASB_OK;
+}
+
+// Decoder only: linear.0 + ReLU -> every predictor -> sigmoid on caller-supplied feature rows
+// (models.py:140-145).  Used by SimpleArtSpeech (models.py:53-96), whose features are embedding rows.
+extern "C" int asb_model_decode(asb_model* m, const float* features, int64_t rows, float* out, void* stream) {
+  if (!m) return set_error(ASB_ERR_INVALID, "asb_model_decode: null model");
+  if (rows < 0 || rows > 0x7fffffffLL / 64) return set_error(ASB_ERR_INVALID, "asb_model_decode: bad row count");
+  if (rows == 0) return ASB_OK;
+  if (!features || !out) return set_error(ASB_ERR_INVALID, "asb_model_decode: null pointer");
+  if (reinterpret_cast<uintptr_t>(features) & 15)
+    return set_error(ASB_ERR_INVALID, "asb_model_decode: features must be 16-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return m->decoder_impl == 1 ? launch_decoder_umma(m, features, out, int(rows), st)
+                              : launch_decoder(m, features, out, int(rows), st);
 }
 
 extern "C" int asb_model_set_recurrent(asb_model* m, int impl) {

@@ -192,6 +192,53 @@ mean_euclidean_kernel(const float* __restrict__ u, const float* __restrict__ v, 
   if (lane == 0) out[item] = acc / float(n);
 }
 
+// Closest pair between two planar contours u (2, n) and v (2, m): min over all (i, j) of the
+// Euclidean distance, plus the pair that attains it (smallest flattened index i*m + j among
+// ties).  This is the reduction of CriticalLoss (phoneme_to_articulation/principal_components/
+// losses.py:86-96: cdist -> reshape(D*D) -> min) and _calculate_TV without slices; one warp per
+// item, lane owns columns j = lane, lane + 32, ...; direct dx*dx + dy*dy form, sqrt of the minimum only.
+__global__ void __launch_bounds__(256)
+min_distance_kernel(const float* __restrict__ u, const float* __restrict__ v, float* __restrict__ out_d,
+                    int* __restrict__ out_ij, long long items, int n, int m) {
+  const long long item = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (item >= items) return;
+  const int lane = threadIdx.x & 31;
+  const float* pu = u + item * 2 * n;
+  const float* pv = v + item * 2 * m;
+  const float kInf = __int_as_float(0x7f800000);
+  float best = kInf;
+  int flat = 0x7fffffff;
+  for (int j = lane; j < m; j += 32) {
+    const float x = pv[j], y = pv[m + j];
+    for (int i = 0; i < n; ++i) {
+      const float dx = pu[i] - x, dy = pu[n + i] - y;
+      const float d = fmaf(dy, dy, dx * dx);
+      const int f = i * m + j;
+      if (d < best || (d == best && f < flat)) {
+        best = d;
+        flat = f;
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float od = __shfl_xor_sync(0xffffffffu, best, o);
+    const int of = __shfl_xor_sync(0xffffffffu, flat, o);
+    if (od < best || (od == best && of < flat)) {
+      best = od;
+      flat = of;
+    }
+  }
+  if (lane == 0) {
+    out_d[item] = sqrtf(best);
+    if (out_ij) {
+      if (flat == 0x7fffffff) flat = 0;   // only reachable with non-finite input
+      out_ij[2 * item] = flat / m;
+      out_ij[2 * item + 1] = flat - (flat / m) * m;
+    }
+  }
+}
+
 }  // namespace
 
 extern "C" int asb_p2cp(const float* u, const float* v, float* out, int64_t items, int n, int m, int layout,
@@ -237,5 +284,20 @@ extern "C" int asb_mean_euclidean(const float* u, const float* v, float* out, in
   if (blocks > 0x7fffffffLL) return asb::set_error(ASB_ERR_INVALID, "asb_mean_euclidean: too many items");
   mean_euclidean_kernel<<<unsigned(blocks), warps * 32, 0, static_cast<cudaStream_t>(stream)>>>(u, v, out, items, n);
   ASB_CHECK_LAUNCH("mean_euclidean_kernel");
+  return ASB_OK;
+}
+
+extern "C" int asb_min_distance(const float* u, const float* v, int64_t items, int n, int m, float* out_d,
+                                int32_t* out_ij, void* stream) {
+  if (items < 0 || n <= 0 || m <= 0 || (long long)n * m > 0x7ffffffeLL)
+    return asb::set_error(ASB_ERR_INVALID, "asb_min_distance: bad shape");
+  if (items == 0) return ASB_OK;
+  if (!u || !v || !out_d) return asb::set_error(ASB_ERR_INVALID, "asb_min_distance: null pointer");
+  const int warps = 8;
+  const long long blocks = (items + warps - 1) / warps;
+  if (blocks > 0x7fffffffLL) return asb::set_error(ASB_ERR_INVALID, "asb_min_distance: too many items");
+  min_distance_kernel<<<unsigned(blocks), warps * 32, 0, static_cast<cudaStream_t>(stream)>>>(u, v, out_d, out_ij,
+                                                                                             items, n, m);
+  ASB_CHECK_LAUNCH("min_distance_kernel");
   return ASB_OK;
 }

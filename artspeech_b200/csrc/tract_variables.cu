@@ -211,7 +211,8 @@ tract_variables_kernel(const float* __restrict__ sets_ptr, long long sets, int n
 }  // namespace
 
 static int tv_launch(const float* sets_ptr, int64_t sets, int n_art, const int32_t* art_index_host,
-                     const float* uinc, int64_t uinc_stride, float* val, int32_t* idx, float* poc, void* stream) {
+                     const float* uinc, int64_t uinc_stride, float* val, int32_t* idx, float* poc, void* stream,
+                     int max_ctas = 0) {
   if (sets < 0 || n_art <= 0 || !art_index_host)
     return asb::set_error(ASB_ERR_INVALID, "asb_tract_variables: bad arguments");
   ArtIndex ai;
@@ -230,6 +231,7 @@ static int tv_launch(const float* sets_ptr, int64_t sets, int n_art, const int32
   long long blocks = (sets + kWarps - 1) / kWarps;
   const long long resident = (long long)asb::sm_count() * ASB_TV_MINB;   // persistent: one wave of CTAs
   if (blocks > resident) blocks = resident;
+  if (max_ctas > 0 && blocks > max_ctas) blocks = max_ctas;   // the sets are strided over whatever grid there is
   tract_variables_kernel<<<unsigned(blocks), kWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
       sets_ptr, sets, n_art, ai, uinc, uinc_stride, val, idx, poc);
   ASB_CHECK_LAUNCH("tract_variables_kernel");
@@ -247,4 +249,12 @@ extern "C" int asb_tract_variables_ref(const float* sets_ptr, int64_t sets, int 
                                        void* stream) {
   if (!upper_incisor) return asb::set_error(ASB_ERR_INVALID, "asb_tract_variables_ref: null upper_incisor");
   return tv_launch(sets_ptr, sets, n_art, art_index_host, upper_incisor, upper_incisor_stride, val, idx, poc, stream);
+}
+
+extern "C" int asb_tract_variables_ex(const float* sets_ptr, int64_t sets, int n_art, const int32_t* art_index_host,
+                                      const float* upper_incisor, int64_t upper_incisor_stride, int max_ctas,
+                                      float* val, int32_t* idx, float* poc, void* stream) {
+  if (max_ctas < 0) return asb::set_error(ASB_ERR_INVALID, "asb_tract_variables_ex: max_ctas < 0");
+  return tv_launch(sets_ptr, sets, n_art, art_index_host, upper_incisor, upper_incisor_stride, val, idx, poc, stream,
+                   max_ctas);
 }

@@ -103,9 +103,19 @@ def shard_utterances(n_utterances, rank, world):
     return list(range(rank, n_utterances, world))
 
 
+_SIDE_STREAMS = {}
+
+
+def _side_stream(dev):
+    key = (dev.type, dev.index if dev.index is not None else torch.cuda.current_device())
+    if key not in _SIDE_STREAMS:
+        _SIDE_STREAMS[key] = torch.cuda.Stream(device=dev)
+    return _SIDE_STREAMS[key]
+
+
 @torch.no_grad()
 def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_incisor=None, mark=None,
-                   lengths_dev=None):
+                   lengths_dev=None, overlap_target=True):
     """One evaluation step on the model's device.
 
     tokens (B, T) int64, lengths sorted descending, targets (B, T, N, 2, 50) fp32, on the GPU (host
@@ -123,16 +133,34 @@ def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_inc
     if lengths_dev is None:
         lengths_dev = torch.as_tensor([int(v) for v in lengths], dtype=torch.int32).to(dev)
     mark("start")
-    outputs = model(tokens, lengths, lengths_dev=lengths_dev)         # evaluation.py:57
-    mark("forward")
-    T = outputs.shape[1]
-    tgt = targets[:, :T]
+    # The target's tract variables do not depend on the forward pass: they run on a side stream
+    # (forked here, joined before the accumulation) and fill the SMs the recurrent kernels leave
+    # idle (2 directions x B/16 CTAs).  Inside a CUDA-graph capture this becomes a parallel branch.
+    cur = torch.cuda.current_stream(dev)
+    side = _side_stream(dev) if overlap_target else cur
+    T_in = min(int(max(lengths)), tokens.shape[1]) if len(lengths) else 0
+    tgt = targets[:, :max(1, T_in)]
     if not tgt.is_contiguous():
         tgt = tgt.contiguous()
+    fork = torch.cuda.Event()
+    fork.record(cur)
+    outputs = model(tokens, lengths, lengths_dev=lengths_dev)         # evaluation.py:57
+    # The branch is enqueued AFTER the forward's kernels (it depends only on `fork`): a full wave of
+    # tract-variable CTAs takes every register of every SM, so the recurrent kernel (B/16 CTAs per
+    # direction, the critical path) has to be placed first.  Measured on B200 at batch 256 x 100
+    # (tools/overlap_check.py): 0.500 -> 0.479 ms per step; capping the branch's grid
+    # (tract_variables_batch(max_ctas=...)) to leave SMs free did not improve on that.
+    side.wait_event(fork)
+    with torch.cuda.stream(side):
+        tv_tgt, _, _ = tract_variables_batch(tgt, articulators, upper_incisor)    # __init__.py:261
+    mark("forward")
+    assert outputs.shape[1] == tgt.shape[1], (outputs.shape, tgt.shape)
     p2cp = p2cp_distance(outputs, tgt)                                # evaluation.py:72 (all sentences at once)
     mark("p2cp")
     tv_pred, _, _ = tract_variables_batch(outputs, articulators, upper_incisor)   # __init__.py:256
-    tv_tgt, _, _ = tract_variables_batch(tgt, articulators, upper_incisor)        # __init__.py:261
+    cur.wait_stream(side)
+    if side is not cur and not torch.cuda.is_current_stream_capturing():
+        tv_tgt.record_stream(cur)
     mark("tv")
     acc = accumulate_device(p2cp, tv_pred, tv_tgt, lengths_dev)       # evaluation.py:68-84,142-156
     mark("reduce")
@@ -168,7 +196,8 @@ class GraphedEvaluator:
     copied into static device buffers (``tokens``, ``targets``); results are the static tensors of
     the captured step (valid until the next replay)."""
 
-    def __init__(self, model, tokens, lengths, targets, articulators=None, upper_incisor=None, warmup=3):
+    def __init__(self, model, tokens, lengths, targets, articulators=None, upper_incisor=None, warmup=3,
+                 overlap_target=True):
         dev = model.embedding.weight.device
         self.model = model
         self.lengths = [int(v) for v in lengths]
@@ -180,7 +209,7 @@ class GraphedEvaluator:
 
         def run():
             return evaluate_batch(model, self.tokens, self.lengths, self.targets, self.articulators,
-                                  self.upper_incisor, lengths_dev=self.lengths_dev)
+                                  self.upper_incisor, lengths_dev=self.lengths_dev, overlap_target=overlap_target)
 
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))

@@ -227,3 +227,127 @@ class ArtSpeech(nn.Module):
                                                       _lib.ptr(self._workspace), self._workspace.numel(),
                                                       _lib.stream_ptr(dev)))
         return out
+
+
+class SimpleArtSpeech(nn.Module):
+    """models.py:53-96 of the reference: Embedding -> Dropout -> Linear(embed_dim, hidden)+ReLU -> the same
+    ``ArticulatorPredictor`` heads -> sigmoid; same constructor (note ``num_samples``), ``forward(x, lengths)``
+    and state_dict keys.  There is no recurrence, so a frame's contours depend on its token only: the
+    decoder kernel (``asb_model_decode``) is run once over the V embedding rows whenever the weights
+    change, and ``forward`` is a row gather from that (V, N, 2, n_samples) table (``asb_gather_rows``),
+    bound by the 4000 B per frame it writes.  ``lengths`` is accepted and ignored, as in the reference.
+    Inference only (dropout is the identity in eval mode, models.py:64,92)."""
+
+    def __init__(self, vocab_size, n_articulators, embed_dim=64, hidden_size=128, num_samples=50, dropout=0.,
+                 precision="fast"):
+        super().__init__()
+        self.embedding = nn.Embedding(vocab_size, embed_dim)
+        self.dropout = nn.Dropout(dropout)
+        self.linear = nn.Sequential(nn.Linear(embed_dim, hidden_size), nn.ReLU())
+        self.predictors = nn.ModuleList([
+            ArticulatorPredictor(hidden_size, num_samples) for _ in range(n_articulators)
+        ])
+        if precision not in PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(PRECISIONS)}")
+        if embed_dim > 2 * hidden_size:
+            raise ValueError("embed_dim must not exceed 2 * hidden_size (the decoder kernel's feature width)")
+        self.precision = precision
+        self._dims = (vocab_size, n_articulators, embed_dim, hidden_size, num_samples)
+        self._native = None
+        self._table = None
+        self._keep = None
+
+    @property
+    def total_parameters(self):
+        return sum(p.numel() for p in self.parameters())
+
+    def _apply(self, fn, *args, **kwargs):
+        self._native = None
+        self._table = None
+        return super()._apply(fn, *args, **kwargs)
+
+    def _ensure_table(self, dev):
+        key = (self.precision,) + tuple((p.data_ptr(), p._version) for p in self.parameters())
+        if self._native is not None and self._native.key == key:
+            return self._table
+        self._native = None
+        vocab, n_art, embed, hidden, n_samples = self._dims
+        sd = {k: v.detach() for k, v in self.named_parameters()}
+        for k, v in sd.items():
+            if not v.is_cuda or v.device != dev:
+                raise RuntimeError(f"parameter {k} is on {v.device}; artspeech_b200.SimpleArtSpeech runs on CUDA only "
+                                   "(call .to('cuda')) - there is no CPU fallback")
+            if v.dtype != torch.float32 or not v.is_contiguous():
+                raise RuntimeError(f"parameter {k} must be contiguous float32")
+        # The decoder kernel consumes (rows, 2*hidden) features through linear.0 (hidden, 2*hidden):
+        # zero-pad the embedding rows and the Linear(embed_dim, hidden) weight to that width (layout
+        # plumbing at pack time; the product with the padding is exactly zero).
+        feat = torch.zeros(vocab, 2 * hidden, dtype=torch.float32, device=dev)
+        feat[:, :embed] = sd["embedding.weight"]
+        lin_w = torch.zeros(hidden, 2 * hidden, dtype=torch.float32, device=dev)
+        lin_w[:, :embed] = sd["linear.0.weight"]
+        # asb_model_create packs a recurrent stack as well; this model has none, so it gets zeros
+        zeros = {(layer, what): torch.zeros(3 * hidden * (1 if what.startswith("b") else
+                                                           (hidden if what == "w_hh" else (embed, 2 * hidden)[layer])),
+                                            dtype=torch.float32, device=dev)
+                 for layer in range(2) for what in ("w_ih", "w_hh", "b_ih", "b_hh")}
+        w = _lib.AsbWeights()
+        w.embedding = sd["embedding.weight"].data_ptr()
+        for layer in range(2):
+            for d in range(2):
+                w.rnn_w_ih[layer][d] = zeros[(layer, "w_ih")].data_ptr()
+                w.rnn_w_hh[layer][d] = zeros[(layer, "w_hh")].data_ptr()
+                w.rnn_b_ih[layer][d] = zeros[(layer, "b_ih")].data_ptr()
+                w.rnn_b_hh[layer][d] = zeros[(layer, "b_hh")].data_ptr()
+        w.linear_w = lin_w.data_ptr()
+        w.linear_b = sd["linear.0.bias"].data_ptr()
+        keep = [feat, lin_w, zeros]
+
+        def arr(fmt):
+            a = (ctypes.c_void_p * n_art)(*[sd[fmt.format(i)].data_ptr() for i in range(n_art)])
+            keep.append(a)
+            return ctypes.cast(a, ctypes.POINTER(ctypes.c_void_p))
+
+        w.ln0_w, w.ln0_b = arr("predictors.{}.linear.0.weight"), arr("predictors.{}.linear.0.bias")
+        w.fc1_w, w.fc1_b = arr("predictors.{}.linear.1.weight"), arr("predictors.{}.linear.1.bias")
+        w.ln1_w, w.ln1_b = arr("predictors.{}.linear.3.weight"), arr("predictors.{}.linear.3.bias")
+        w.fc2_w, w.fc2_b = arr("predictors.{}.linear.4.weight"), arr("predictors.{}.linear.4.bias")
+        w.ln2_w, w.ln2_b = arr("predictors.{}.linear.6.weight"), arr("predictors.{}.linear.6.bias")
+        w.xh_w, w.xh_b = arr("predictors.{}.x_coords.weight"), arr("predictors.{}.x_coords.bias")
+        w.yh_w, w.yh_b = arr("predictors.{}.y_coords.weight"), arr("predictors.{}.y_coords.bias")
+        handle = ctypes.c_void_p()
+        table = torch.empty(vocab, n_art, 2, n_samples, dtype=torch.float32, device=dev)
+        lib = _lib.lib()
+        with torch.cuda.device(dev):
+            _lib.check(lib.asb_model_create(ctypes.byref(w), vocab, n_art, embed, hidden, n_samples, _lib.CELL_GRU,
+                                            PRECISIONS[self.precision], _lib.stream_ptr(dev), ctypes.byref(handle)))
+            self._native = _NativeHandle(handle, key)
+            _lib.check(lib.asb_model_decode(handle, _lib.ptr(feat), vocab, _lib.ptr(table), _lib.stream_ptr(dev)))
+        self._table = table
+        self._keep = keep
+        return table
+
+    def forward(self, x, lengths=None):
+        """x (bs, seq_len) int64 -> (bs, seq_len, n_articulators, 2, n_samples) float32 (models.py:84-96)."""
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            raise NotImplementedError("artspeech_b200.SimpleArtSpeech implements inference only; call it under "
+                                      "torch.no_grad()")
+        if self.training and self.dropout.p > 0:
+            raise NotImplementedError("dropout (train mode) is not implemented; call .eval()")
+        dev = self.embedding.weight.device
+        if dev.type != "cuda":
+            raise RuntimeError("artspeech_b200.SimpleArtSpeech runs on CUDA only (call .to('cuda')); no CPU fallback")
+        if x.dim() != 2:
+            raise ValueError(f"x must be (bs, seq_len), got {tuple(x.shape)}")
+        table = self._ensure_table(dev)
+        vocab, n_art, _, _, n_samples = self._dims
+        row = n_art * 2 * n_samples
+        if row % 4:
+            raise ValueError("n_articulators * 2 * num_samples must be a multiple of 4")
+        xd = x.detach().to(device=dev, dtype=torch.int64).contiguous()
+        B, T = xd.shape
+        out = torch.empty(B, T, n_art, 2, n_samples, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().asb_gather_rows(_lib.ptr(table), _lib.ptr(xd), B * T, vocab, row, _lib.ptr(out),
+                                                  _lib.stream_ptr(dev)))
+        return out

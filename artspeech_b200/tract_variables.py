@@ -41,7 +41,7 @@ _ABI_ORDER = (LOWER_LIP, PHARYNX, SOFT_PALATE_MIDLINE, TONGUE, UPPER_INCISOR, UP
 _ARR1 = ((LOWER_LIP, 0), (TONGUE, 30), (TONGUE, 10), (SOFT_PALATE_MIDLINE, 0))
 
 
-def tract_variables_batch(frames, articulators, upper_incisor=None):
+def tract_variables_batch(frames, articulators, upper_incisor=None, max_ctas=0):
     """All four TVs for every contour set in one launch.
 
     frames: (..., N_art, 2, 50) float tensor (CPU or CUDA); ``articulators``: the N_art names in
@@ -49,7 +49,8 @@ def tract_variables_batch(frames, articulators, upper_incisor=None):
     sets, or (..., 2, 50) one per set, used instead of a row of ``frames`` (the reference injects
     a fixed reference contour, evaluation.py:93-109).  Returns (val (...,4) fp32, idx (...,4,2) int32,
     poc (...,4,2,2) fp32) on the CUDA device; idx = (i into arr1, j into arr2) of each search,
-    poc = (arr1[i], arr2[j])."""
+    poc = (arr1[i], arr2[j]).  ``max_ctas`` > 0 caps the grid (for a launch that runs beside other
+    kernels and must leave SMs to them)."""
     if isinstance(articulators, dict):
         index = articulators
     else:
@@ -69,17 +70,16 @@ def tract_variables_batch(frames, articulators, upper_incisor=None):
     idx = torch.empty(sets, 4, 2, dtype=torch.int32, device=dev)
     poc = torch.empty(sets, 4, 2, 2, dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
-        if upper_incisor is None:
-            _lib.check(_lib.lib().asb_tract_variables(_lib.ptr(f), sets, n_art, rows, _lib.ptr(val),
-                                                      _lib.ptr(idx), _lib.ptr(poc), _lib.stream_ptr(dev)))
-        else:
+        ui, stride = None, 0
+        if upper_incisor is not None:
             ui = upper_incisor.detach().to(device=dev, dtype=torch.float32).contiguous()
             if ui.shape[-2:] != (2, 50) or ui.numel() not in (100, sets * 100):
                 raise ValueError(f"upper_incisor must be (2, 50) or (..., 2, 50) per set, got {tuple(ui.shape)}")
             stride = 0 if ui.numel() == 100 else 100
-            _lib.check(_lib.lib().asb_tract_variables_ref(_lib.ptr(f), sets, n_art, rows, _lib.ptr(ui), stride,
-                                                          _lib.ptr(val), _lib.ptr(idx), _lib.ptr(poc),
-                                                          _lib.stream_ptr(dev)))
+        _lib.check(_lib.lib().asb_tract_variables_ex(_lib.ptr(f), sets, n_art, rows,
+                                                     _lib.ptr(ui) if ui is not None else None, stride,
+                                                     int(max_ctas), _lib.ptr(val), _lib.ptr(idx), _lib.ptr(poc),
+                                                     _lib.stream_ptr(dev)))
     return val.view(*lead, 4), idx.view(*lead, 4, 2), poc.view(*lead, 4, 2, 2)
 
 

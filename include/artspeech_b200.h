@@ -68,6 +68,13 @@ ASB_API int asb_p2cp(const float* u, const float* v, float* out, int64_t items, 
 ASB_API int asb_mean_euclidean(const float* u, const float* v, float* out, int64_t items, int n,
                        void* stream);
 
+/* Closest pair of two planar contours per item: u (items, 2, n), v (items, 2, m) fp32 ->
+ * out_d (items) = min_{i,j} |u_i - v_j|, out_ij (items, 2) int32 = the pair attaining it (smallest
+ * i*m + j among ties; may be NULL).  The reduction inside CriticalLoss.forward,
+ * phoneme_to_articulation/principal_components/losses.py:86-96 (cdist -> reshape -> min). */
+ASB_API int asb_min_distance(const float* u, const float* v, int64_t items, int n, int m, float* out_d,
+                     int32_t* out_ij, void* stream);
+
 /* calculate_vocal_tract_variables, tract_variables.py:73-125 (LA, TTCD, TBCD, VEL via
  * _calculate_TV :23-35) for `sets` contour sets of shape (n_art, 2, 50), planar.
  * art_index_host[6]: rows of lower-lip, pharynx, soft-palate-midline, tongue, upper-incisor,
@@ -88,6 +95,14 @@ ASB_API int asb_tract_variables_ref(const float* sets_ptr, int64_t sets, int n_a
                             const int32_t* art_index_host, const float* upper_incisor,
                             int64_t upper_incisor_stride, float* val, int32_t* idx, float* poc,
                             void* stream);
+
+/* Same with a cap on the grid (`max_ctas` CTAs of 8 warps; 0 = one full wave) and an optional
+ * upper incisor (NULL = row art_index_host[4] of each set).  A call that runs BESIDE other kernels
+ * (the target's tract variables next to the forward pass, evaluation.py:57 vs __init__.py:261) leaves
+ * SMs free this way: a full wave of these CTAs takes every register of every SM. */
+ASB_API int asb_tract_variables_ex(const float* sets_ptr, int64_t sets, int n_art, const int32_t* art_index_host,
+                           const float* upper_incisor, int64_t upper_incisor_stride, int max_ctas,
+                           float* val, int32_t* idx, float* poc, void* stream);
 
 /* intersect_semipolar_grid -> area_function -> evenly_spaced_fx, area_function.py:175-223,
  * :124-142 (mid_point :113-121), :145-159, for `frames` independent frames.
@@ -189,15 +204,28 @@ ASB_API int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_in,
                                const int32_t* lengths_dev, int B, float* out, void* workspace,
                                size_t workspace_bytes, void* stream);
 
+/* Decoder alone on caller-supplied feature rows: features (rows, 2*hidden) fp32 ->
+ * out (rows, n_art, 2, n_samples) = sigmoid(stack(predictor_i(ReLU(linear.0(features))))),
+ * models.py:140-145.  SimpleArtSpeech (models.py:53-96) runs through this entry: its features are
+ * embedding rows zero-padded to 2*hidden and its Linear(embed_dim, hidden) zero-padded likewise. */
+ASB_API int asb_model_decode(asb_model* m, const float* features, int64_t rows, float* out, void* stream);
+
+/* out[r, :] = table[tokens[r], :] for r < rows; table (vocab, row_floats) fp32, row_floats % 4 == 0,
+ * table/out 16-byte aligned.  nn.Embedding (models.py:63,135) and, for SimpleArtSpeech, the whole
+ * forward pass as a lookup in the per-token contour table (models.py:84-96).  A token outside
+ * [0, vocab) yields a row of NaNs. */
+ASB_API int asb_gather_rows(const float* table, const int64_t* tokens, int64_t rows, int vocab, int row_floats,
+                    float* out, void* stream);
+
 /* Decoder implementation: 1 = tcgen05/TMEM kernel (default in fast precision with n_samples = 50),
  * 0 = mma.sync kernel (always used in fp32 precision).  Both compute models.py:140-145.  The
  * layer-1 input projection follows the same switch (tcgen05 proj_umma.cu / mma.sync linear256). */
 ASB_API int asb_model_set_decoder(asb_model* m, int impl);
 
-/* Recurrent-layer implementation (fast precision): 0 = W_hh resident in registers, mma.sync bf16
- * (default: 0.91 us per time step at batch 256 on B200), 1 = W_hh resident in shared memory,
- * tcgen05.mma kind::f16 with the gates fused behind tcgen05.ld (1.27 us per step: the 96 KB A
- * operand is re-read from shared memory every step).  Both compute models.py:111,136-138. */
+/* Recurrent-layer implementation (fast precision): 1 = W_hh resident in TENSOR MEMORY, tcgen05.mma
+ * kind::f16 (TS form) with the gates fused behind tcgen05.ld (default; GRU and LSTM; 0.55 us per
+ * time step at batch 256 on B200), 0 = W_hh resident in registers, mma.sync bf16 (GRU only,
+ * 0.84-0.91 us per step).  Both compute models.py:111,136-138. */
 ASB_API int asb_model_set_recurrent(asb_model* m, int impl);
 
 /* Per-stage device timing of asb_model_forward (CUDA events on `stream`): enable, run forwards,

@@ -193,3 +193,13 @@ def artspeech_forward(sd, x, lengths, dtype=torch.float32, rnn="stock", return_h
     if return_hidden:
         return out, rnn_out, lin
     return out
+
+
+@torch.no_grad()
+def simple_artspeech_forward(sd, x, dtype=torch.float32):
+    """SimpleArtSpeech.forward(x, lengths), models.py:84-96 (eval mode: dropout is the identity)."""
+    embed = F.embedding(x.cpu(), sd["embedding.weight"].to(dtype))                      # :91
+    lin = F.relu(F.linear(embed, sd["linear.0.weight"].to(dtype), sd["linear.0.bias"].to(dtype)))  # :92
+    n_art = n_articulators_of(sd)
+    out = torch.stack([predictor_forward(sd, i, lin, dtype) for i in range(n_art)], dim=2)   # :93-95
+    return torch.sigmoid(out)                                                           # :97

@@ -230,3 +230,53 @@ def test_lstm_config4_long_sequence(mods):
         want = omodel.artspeech_forward(sd, x[b:b + 1], [lb], torch.float32)
         err = float((out[b:b + 1, :lb].cpu() - want).abs().max())
         assert err <= 2e-3, (b, err)
+
+
+@pytest.mark.parametrize("precision", ["fast", "fp32"])
+def test_simple_artspeech_golden(mods, golden_dir, precision):
+    """SimpleArtSpeech (models.py:53-96) as a lookup in the per-token contour table, against the
+    reference's own output (tests/golden/model_small.npz: out_simple) and the fp64 oracle."""
+    models, omodel = mods
+    g = np.load(os.path.join(golden_dir, "model_small.npz"))
+    torch.manual_seed(0)
+    net = models.SimpleArtSpeech(45, 10, precision=precision)
+    sd = {k: v.detach().clone() for k, v in net.state_dict().items()}
+    net = net.cuda().eval()
+    x = torch.from_numpy(g["x"]).cuda()
+    with torch.no_grad():
+        out = net(x, torch.from_numpy(g["lengths"]))
+    assert out.shape == g["out_simple"].shape and out.dtype == torch.float32 and out.is_contiguous()
+    err = np.abs(out.cpu().numpy() - g["out_simple"]).max()
+    print(f"simple_artspeech[{precision}] max-abs vs reference {err:.3e}")
+    assert err <= TOL[precision]
+    # perturbed LayerNorm affines + a full-vocabulary batch; every row equals the row of its token
+    sd2 = omodel.randomize_affine(sd, seed=4)
+    net.load_state_dict(sd2)
+    x2 = synthetic.tokens(7, 33, 45, seed=9)
+    with torch.no_grad():
+        out2 = net(x2.cuda(), [33] * 7).cpu()
+    want = omodel.simple_artspeech_forward(sd2, x2, torch.float64)
+    assert (out2.double() - want).abs().max().item() <= TOL[precision]
+    flat, tok = out2.view(-1, 1000), x2.view(-1)
+    first = {}
+    for r, t in enumerate(tok.tolist()):
+        first.setdefault(t, r)
+        assert torch.equal(flat[r], flat[first[t]])
+    # out-of-range token -> NaN row (nn.Embedding raises; the device kernel flags instead)
+    bad = x2.clone(); bad[0, 0] = 45
+    with torch.no_grad():
+        ob = net(bad.cuda(), None).cpu()
+    assert torch.isnan(ob[0, 0]).all() and not torch.isnan(ob[0, 1:]).any()
+
+
+def test_gather_rows_abi(mods):
+    from artspeech_b200 import _lib
+    table = torch.randn(45, 256, device="cuda")
+    tok = torch.randint(0, 45, (1000,), device="cuda")
+    out = torch.empty(1000, 256, device="cuda")
+    _lib.check(_lib.lib().asb_gather_rows(_lib.ptr(table), _lib.ptr(tok), 1000, 45, 256, _lib.ptr(out),
+                                          _lib.stream_ptr(out.device)))
+    assert torch.equal(out, table[tok])
+    with pytest.raises(ValueError):
+        _lib.check(_lib.lib().asb_gather_rows(_lib.ptr(table), _lib.ptr(tok), 1000, 45, 255, _lib.ptr(out),
+                                              _lib.stream_ptr(out.device)))

@@ -147,3 +147,17 @@ def test_sentence_metrics_oracle_matches_reference_metrics_py(golden_dir):
         np.testing.assert_allclose(med, g["per_sentence"][1, b], rtol=1e-12)
         np.testing.assert_allclose(xc.mean(dim=-1)[0].numpy(), g["per_sentence"][2, b], rtol=1e-10, atol=1e-12)
         np.testing.assert_allclose(yc.mean(dim=-1)[0].numpy(), g["per_sentence"][3, b], rtol=1e-10, atol=1e-12)
+
+
+def test_simple_artspeech_constructor_and_oracle_match_reference(gm):
+    """SimpleArtSpeech (models.py:53-96): the drop-in's constructor draws the reference's initial
+    weights under the same seed, and the oracle restatement reproduces the reference's output."""
+    from artspeech_b200 import models
+    torch.manual_seed(0)
+    net = models.SimpleArtSpeech(45, 10)
+    sd = {k: v.detach() for k, v in net.state_dict().items()}
+    sums = np.array([v.double().sum().item() for k, v in sorted(sd.items())])
+    assert np.array_equal(sums, gm["simple_sums"])
+    out = omodel.simple_artspeech_forward(sd, torch.from_numpy(gm["x"]))
+    assert out.shape == gm["out_simple"].shape
+    assert np.abs(out.numpy() - gm["out_simple"]).max() <= 2e-6
