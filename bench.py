@@ -51,7 +51,7 @@ def load_peaks():
 
 
 class ClockSampler:
-    """SM clock + throttle reasons sampled every 20 ms through NVML while the timed region runs."""
+    """SM clock + throttle reasons sampled every 2 ms through NVML while the timed region runs."""
 
     def __init__(self, index):
         self.index = index
@@ -87,7 +87,7 @@ class ClockSampler:
                     for name, bit in flags.items():
                         if bit and (r & int(bit)):
                             self.reasons.add(name)
-                self._stop.wait(0.02)
+                self._stop.wait(0.002)
         except Exception as exc:  # NVML missing: report it instead of inventing numbers
             self.error = repr(exc)
 
@@ -318,10 +318,17 @@ def run_ours(args):
     else:
         achieved = work / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
         peak, unit = peaks["hbm_gbs"], "GB/s"
+    # DRAM bytes per launch of each kernel from the committed `ncu --set full` capture of this
+    # workload (profiles/ncu_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum)
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tpath) and (B, T) == (256, 100):
+        with open(tpath) as f:
+            traffic = json.load(f).get("bytes_per_launch", {}).get(top)
     roofline = {"kernel": top, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit,
                 "frac": achieved / peak if peak else None,
                 "frac_of_tf32_rate": (achieved / (0.5 * peak) if peak and bound == "tensor" else None),
-                "traffic": None,
+                "traffic": traffic,
                 "peak_source": f"{peaks['source']} (dense bf16 cuBLAS sustained; this kernel computes in tf32, whose tensor rate is half: frac_of_tf32_rate)"
                 if bound == "tensor" else peaks["source"],
                 "ms_per_launch": ms,
@@ -406,7 +413,8 @@ def run_ours(args):
                        "precision": args.precision, "frames_per_step_per_gpu": frames,
                        "parallelism": f"utterance-sharded x{world}, one NCCL all-reduce of {N_ART + 14} fp64 per step",
                        "l2": "256 MiB flush between timed steps; per-step working set > L2",
-                       "launch": "CUDA graph replay of the captured step" if graphed is not None else "eager"},
+                       "launch": "CUDA graph replay of the captured step (target TVs on a forked branch beside the "
+                                 "forward pass)" if graphed is not None else "eager"},
             "stage_ms": {k: round(v, 4) for k, v in stage_ms.items()},
             "roofline": roofline, "cpu_baseline": cpu_baseline,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -168,3 +168,31 @@ def calculate_vocal_tract_variables(inputs_dict, dtype=torch.float64):
     for k, name in enumerate(TV_NAMES):
         out[name] = {"value": float(val[0, k]), "poc_1": poc[0, k, 0], "poc_2": poc[0, k, 1]}
     return out
+
+
+CRITICAL_TV_TO_ARTICULATORS = {
+    "LA": ("lower-lip", "upper-lip"), "TTCD": ("tongue", "upper-incisor"),
+    "TBCD": ("tongue", "upper-incisor"), "VEL": ("soft-palate", "pharynx"),
+}
+
+
+def critical_loss(output_shapes, reference_arrays, critical_mask, TVs, articulators, dtype=torch.float64):
+    """CriticalLoss.forward, phoneme_to_articulation/principal_components/losses.py:52-99 (no
+    denormalisation): mean over the entries with critical_mask == 1 of the minimum distance
+    between the two (whole) articulators of each tract variable.  Differentiable torch ops, so the
+    tests can take its gradient as the truth for the CUDA path's backward."""
+    TVs = sorted(TVs)                                                       # :38
+    articulators = list(articulators)
+    x = output_shapes.to(dtype)
+    if "upper-incisor" not in articulators:                                 # :39-42, :64-70
+        articulators = sorted(articulators + ["upper-incisor"])
+        k = articulators.index("upper-incisor")
+        x = torch.cat([x[:, :, :k], reference_arrays.to(dtype), x[:, :, k:]], dim=2)
+    index = {a: i for i, a in enumerate(articulators)}
+    per_tv = []
+    for tv in TVs:                                                          # :74-93
+        a1, a2 = CRITICAL_TV_TO_ARTICULATORS[tv]
+        d = _pairwise(x[..., index[a1], :, :].transpose(-1, -2), x[..., index[a2], :, :].transpose(-1, -2))
+        per_tv.append(d.flatten(-2).min(dim=-1).values)                     # (B, T)  :95-98
+    loss = torch.stack(per_tv, dim=1)                                       # (B, Ntvs, T)
+    return loss[critical_mask == 1].mean()                                  # :99

@@ -148,6 +148,33 @@ def golden_tv():
           np.max(np.abs(val32 - val) / np.maximum(val, 1e-30)))
 
 
+def golden_critical_loss():
+    """CriticalLoss of the unmodified reference (class statement only, see reference_loader) on
+    seeded contours: loss value and its gradient, in fp64 and fp32."""
+    CL = ref.critical_loss()
+    arts = ["lower-lip", "pharynx", "soft-palate", "tongue", "upper-lip"]   # upper incisor injected
+    B, T = 3, 7
+    x = synthetic.contours(B * T, 5, 50, seed=21).view(B, T, 5, 2, 50)
+    refarr = synthetic.UPPER_INCISOR_REF.view(1, 1, 1, 2, 50).expand(B, T, 1, 2, 50).contiguous()
+    g = torch.Generator().manual_seed(5)
+    mask = (torch.rand(B, 4, T, generator=g) < 0.4).to(torch.int64)
+    mask[0, 0, 0] = 1
+    out = {}
+    for name, dt in (("64", torch.float64), ("32", torch.float32)):
+        xi = x.to(dt).clone().requires_grad_(True)
+        loss = CL(["LA", "TTCD", "TBCD", "VEL"], list(arts))(xi, xi.detach(), refarr.to(dt), mask)
+        loss.backward()
+        out["loss" + name] = np.array(loss.item())
+        out["grad" + name] = xi.grad.numpy()
+    # a two-TV instance whose articulator list already holds the upper incisor (no injection)
+    arts6 = sorted(arts + ["upper-incisor"])
+    x6 = synthetic.contours(B * T, 6, 50, seed=22).view(B, T, 6, 2, 50).double()
+    loss6 = CL(["TTCD", "LA"], list(arts6))(x6, x6, None, mask[:, :2])
+    np.savez_compressed(os.path.join(GOLDEN, "critical_loss.npz"), x=x.numpy(), ref=refarr.numpy(), mask=mask.numpy(),
+                        x6=x6.float().numpy(), loss6=np.array(loss6.item()), **out)
+    print("critical_loss:", out["loss64"], out["loss32"], float(loss6))
+
+
 def golden_area():
     """The parts of area_function.py that run without GEOS: grid, mid_point, argmatrix, rotate and
     area_function (a9, a11).  a10 / a12 need shapely and stay unpinned (oracle/area.py header)."""
@@ -190,3 +217,4 @@ if __name__ == "__main__":
     golden_tv()
     golden_sentence_metrics()
     golden_area()
+    golden_critical_loss()

@@ -110,3 +110,24 @@ def area_function():
     if not hasattr(np, "float"):
         np.float = float
     return _load("_ref_area_function", "area_function.py")
+
+
+def critical_loss():
+    """reference ``CriticalLoss`` (phoneme_to_articulation/principal_components/losses.py:23-99).
+    The module's other imports (helpers, the principal_components models, vt_tools) cannot be
+    satisfied here, so ONLY the class statement is compiled - its source text unmodified, cut out
+    of the file with ``ast`` - in a namespace holding torch, nn and the six vt_tools name
+    constants it uses as dict keys (``SOFT_PALATE`` = "soft-palate")."""
+    import ast
+    import torch
+    import torch.nn as nn
+    path = os.path.join(REFERENCE_ROOT, "phoneme_to_articulation/principal_components/losses.py")
+    with open(path) as f:
+        src = f.read()
+    tree = ast.parse(src)
+    node = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "CriticalLoss")
+    code = compile(ast.Module(body=[node], type_ignores=[]), path, "exec")
+    ns = {"torch": torch, "nn": nn, "LOWER_LIP": "lower-lip", "PHARYNX": "pharynx", "SOFT_PALATE": "soft-palate",
+          "TONGUE": "tongue", "UPPER_INCISOR": "upper-incisor", "UPPER_LIP": "upper-lip"}
+    exec(code, ns)
+    return ns["CriticalLoss"]

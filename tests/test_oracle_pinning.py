@@ -161,3 +161,26 @@ def test_simple_artspeech_constructor_and_oracle_match_reference(gm):
     out = omodel.simple_artspeech_forward(sd, torch.from_numpy(gm["x"]))
     assert out.shape == gm["out_simple"].shape
     assert np.abs(out.numpy() - gm["out_simple"]).max() <= 2e-6
+
+
+def test_critical_loss_oracle_matches_reference(golden_dir):
+    """oracle.geometry.critical_loss against the reference's CriticalLoss (losses.py:23-99): value
+    and gradient, with and without the injected upper incisor."""
+    g = np.load(os.path.join(golden_dir, "critical_loss.npz"))
+    arts = ["lower-lip", "pharynx", "soft-palate", "tongue", "upper-lip"]
+    x = torch.from_numpy(g["x"]).double().requires_grad_(True)
+    loss = ogeo.critical_loss(x, torch.from_numpy(g["ref"]), torch.from_numpy(g["mask"]),
+                              ["LA", "TTCD", "TBCD", "VEL"], arts)
+    loss.backward()
+    assert abs(loss.item() - float(g["loss64"])) <= 1e-14
+    assert np.abs(x.grad.numpy() - g["grad64"]).max() <= 1e-14
+    assert abs(float(g["loss32"]) - float(g["loss64"])) / float(g["loss64"]) < 1e-4   # F2: fp32 cdist
+    loss6 = ogeo.critical_loss(torch.from_numpy(g["x6"]), None, torch.from_numpy(g["mask"])[:, :2],
+                               ["TTCD", "LA"], sorted(arts + ["upper-incisor"]))
+    assert abs(loss6.item() - float(g["loss6"])) <= 1e-14
+    if ref.available():
+        CL = ref.critical_loss()
+        live = CL(["TTCD", "LA"], sorted(arts + ["upper-incisor"]))(
+            torch.from_numpy(g["x6"]).double(), torch.from_numpy(g["x6"]).double(), None,
+            torch.from_numpy(g["mask"])[:, :2])
+        assert abs(live.item() - float(g["loss6"])) <= 1e-14
