@@ -280,3 +280,25 @@ def test_gather_rows_abi(mods):
     with pytest.raises(ValueError):
         _lib.check(_lib.lib().asb_gather_rows(_lib.ptr(table), _lib.ptr(tok), 1000, 45, 255, _lib.ptr(out),
                                               _lib.stream_ptr(out.device)))
+
+
+@pytest.mark.parametrize("B,T,n_art,vocab", [(1, 1, 10, 45), (17, 5, 3, 45), (5, 40, 2, 3000), (130, 3, 1, 7)])
+def test_edge_shapes_vs_oracle(mods, B, T, n_art, vocab):
+    """Single frame, batch sizes that leave partly filled CTAs / tiles, articulator counts other than
+    10, and a vocabulary whose layer-0 table does not fit beside the recurrent kernel's shared memory
+    (the gather path).  Buffers are reused across calls of different shape: padded steps must not leak."""
+    models, omodel = mods
+    sd = omodel.randomize_affine(omodel.make_state_dict(vocab, n_art, seed=2), seed=5)
+    net = _build(models, sd, "fast", n_art=n_art, vocab=vocab)
+    with torch.no_grad():
+        net(synthetic.tokens(B + 3, T + 9, vocab, seed=1).cuda(), [T + 9] * (B + 3))   # dirties the workspace
+    x = synthetic.tokens(B, T, vocab, seed=8)
+    L = synthetic.sorted_lengths(B, 1, T, seed=8) if T > 1 else [1] * B
+    L[0] = T
+    with torch.no_grad():
+        out = net(x.cuda(), L)
+    want = omodel.artspeech_forward(sd, x, L, torch.float32)
+    assert out.shape == want.shape == (B, T, n_art, 2, 50)
+    err = (out.cpu() - want).abs().max().item()
+    print(f"edge[{B}x{T}, {n_art} articulators, vocab {vocab}] max-abs {err:.3e}")
+    assert err <= TOL["fast"]
