@@ -22,6 +22,8 @@
 //     input pre-activations of the next step are prefetched while the MMAs run.
 #include <cuda_bf16.h>
 
+#include <cstdlib>
+
 #include "model.cuh"
 #include "umma.cuh"
 
@@ -333,7 +335,8 @@ template <int G>
 static int launch_rnn_umma_g(const asb_model* m, RnnArgs& a, int B, bool use_tokens, cudaStream_t st) {
   const int sms = sm_count();
   // fewest rows per CTA that still fit one wave of the machine (the gate math bounds a step)
-  const int cpt = (2 * ((B + 3) / 4) <= sms) ? 2 : (2 * ((B + 7) / 8) <= sms) ? 4 : 8;
+  int cpt = (2 * ((B + 3) / 4) <= sms) ? 2 : (2 * ((B + 7) / 8) <= sms) ? 4 : 8;
+  if (const char* e = getenv("ASB_RNN_CPT")) cpt = atoi(e) == 8 ? 8 : (atoi(e) == 4 ? 4 : (atoi(e) == 2 ? 2 : cpt));   // experiment knob
   const int tok_bytes = 2 * cpt * a.T * 4;
   if (!use_tokens || tok_bytes > kMaxTokenBytes) a.tokens = nullptr;   // the caller materialised gi instead
   const int smem = kHsBytes + 64 + 1024 + kGiSlots * cpt * G * 1024 + (a.tokens ? tok_bytes : 0);
@@ -362,7 +365,8 @@ static int launch_rnn_umma_g(const asb_model* m, RnnArgs& a, int B, bool use_tok
 // layer 0 may read its input pre-activations through the token table instead of a materialised gi
 bool rnn_umma_reads_tokens(const asb_model* m, int B, int T) {
   const int sms = sm_count();
-  const int cpt = (2 * ((B + 3) / 4) <= sms) ? 2 : (2 * ((B + 7) / 8) <= sms) ? 4 : 8;
+  int cpt = (2 * ((B + 3) / 4) <= sms) ? 2 : (2 * ((B + 7) / 8) <= sms) ? 4 : 8;
+  if (const char* e = getenv("ASB_RNN_CPT")) cpt = atoi(e) == 8 ? 8 : (atoi(e) == 4 ? 4 : (atoi(e) == 2 ? 2 : cpt));
   return rnn_umma_supported(m) && 2 * cpt * T * 4 <= kMaxTokenBytes;
 }
 
