@@ -6,9 +6,11 @@ pass runs entirely in the hand-written sm_100a kernels behind the C ABI (asb_mod
 
 The torch submodules below are only PARAMETER CONTAINERS: they give identical initialisation
 (same RNG consumption order as the reference constructor, models.py:109-120), identical
-``state_dict`` keys, ``.to(device)`` and ``.parameters()``; their own ``forward`` is never
-called and there is no CPU or eager fallback.  Inference only: calling the module with autograd
-enabled on parameters that require grad raises (training support is SURVEY.md row N2).
+``state_dict`` keys, ``.to(device)`` and ``.parameters()``; the forward pass never calls their own
+``forward`` and there is no CPU or eager fallback for it.  With autograd enabled (training,
+train_phoneme_to_articulation.py:84-96) the forward values still come from the kernels and the
+backward pass differentiates a recomputed torch graph of the same parameters (library code, see
+``_TrainingForward``); hand-written backward kernels are SURVEY.md row N2.
 """
 from __future__ import annotations
 
@@ -40,8 +42,11 @@ class ArticulatorPredictor(nn.Module):
         self.y_coords = nn.Linear(in_features=256, out_features=n_samples)
 
     def forward(self, inputs):
-        raise RuntimeError("ArticulatorPredictor is evaluated inside ArtSpeech's fused CUDA decoder; "
-                           "it has no standalone forward in artspeech_b200")
+        """models.py:23-33 as a differentiable torch graph.  The PRODUCT forward never comes here (the
+        predictors are evaluated inside the fused CUDA decoder); this graph exists for the backward
+        pass of training, which re-derives the activations with autograd (see ``_TrainingForward``)."""
+        linear_out = self.linear(inputs)
+        return torch.stack([self.x_coords(linear_out), self.y_coords(linear_out)], dim=2)
 
 
 class _NativeHandle:
@@ -58,6 +63,35 @@ class _NativeHandle:
         except Exception:
             pass
         self.ptr = None
+
+
+class _TrainingForward(torch.autograd.Function):
+    """Forward = the native kernels (same values as in evaluation); backward = autograd through a
+    recomputed torch graph of the same module (``ArtSpeech._library_graph``: cuDNN GRU + cuBLAS
+    linears), i.e. the gradient of the fp32 model at the current parameters.  This is what lets
+    train_phoneme_to_articulation.py:84-96 run on the drop-in module; hand-written backward kernels
+    (BPTT through the resident-W_hh recurrent kernel, fused decoder backward) are SURVEY.md row N2 and
+    are not built - the backward pass is library code and is not counted in any benchmark."""
+
+    @staticmethod
+    def forward(ctx, module, x, lengths, *params):
+        ctx.module, ctx.x, ctx.lengths = module, x, lengths
+        ctx.n_params = len(params)
+        with torch.no_grad():
+            return module._native_forward(x, lengths)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        module = ctx.module
+        params = [p for p in module.parameters()]
+        # fp32 precision: keep cuDNN's recurrent GEMMs out of TF32 so the gradient is the fp32 one
+        tf32 = module.precision != "fp32"
+        with torch.enable_grad(), torch.backends.cudnn.flags(enabled=True, allow_tf32=tf32):
+            out = module._library_graph(ctx.x, ctx.lengths)
+            need = [p for p in params if p.requires_grad]
+            grads = torch.autograd.grad(out, need, grad_out.to(out.dtype), allow_unused=True)
+        it = iter(grads)
+        return (None, None, None) + tuple(next(it) if p.requires_grad else None for p in params)
 
 
 class ArtSpeech(nn.Module):
@@ -188,12 +222,24 @@ class ArtSpeech(nn.Module):
         Return:
             output (torch.tensor): (bs, max(lengths), n_articulators, 2, n_samples) float32
         """
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
-            raise NotImplementedError(
-                "artspeech_b200.ArtSpeech implements inference only; call it under torch.no_grad() "
-                "(evaluation.py:56-57 does). Training/backward kernels are not built yet.")
         if self.training and self.rnn.dropout > 0:
-            raise NotImplementedError("inter-layer dropout (train mode) is not implemented; call .eval()")
+            raise NotImplementedError("inter-layer dropout (train mode with dropout > 0) is not implemented")
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            if lengths_dev is not None:
+                raise ValueError("lengths_dev is an inference-only extension")
+            L = lengths.detach().cpu().tolist() if torch.is_tensor(lengths) else list(lengths)
+            return _TrainingForward.apply(self, x, [int(v) for v in L], *self.parameters())
+        return self._native_forward(x, lengths, lengths_dev)
+
+    def _library_graph(self, x, lengths):
+        """models.py:126-145 on the parameter containers as a differentiable torch graph (backward only)."""
+        from torch.nn.utils.rnn import pack_padded_sequence, pad_packed_sequence
+        packed = pack_padded_sequence(self.embedding(x), torch.as_tensor(lengths, dtype=torch.int64), batch_first=True)
+        rnn_out, _ = pad_packed_sequence(self.rnn(packed)[0], batch_first=True)
+        hidden = self.linear(rnn_out)
+        return torch.sigmoid(torch.stack([predictor(hidden) for predictor in self.predictors], dim=2))
+
+    def _native_forward(self, x, lengths, lengths_dev=None):
         dev = self.embedding.weight.device
         if not dev.type == "cuda":
             raise RuntimeError("artspeech_b200.ArtSpeech runs on CUDA only (call .to('cuda')); no CPU fallback")

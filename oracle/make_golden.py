@@ -66,6 +66,31 @@ def golden_model():
     print("model_small:", tuple(out32.shape), "params", sum(v.numel() for v in sd.values()))
 
 
+def golden_model_grad():
+    """Gradients of the unmodified reference ArtSpeech (fp32 and fp64) for a seeded linear functional
+    of its output: per-parameter sums / abs-sums plus the full gradient of the small tensors."""
+    m = ref.models()
+    torch.manual_seed(0)
+    net = m.ArtSpeech(45, 10).train()          # dropout = 0: train mode == eval mode numerically
+    x = synthetic.tokens(3, 12, 45, seed=3)
+    lengths = torch.tensor([12, 9, 5], dtype=torch.int32)
+    w = torch.randn(3, 12, 10, 2, 50, generator=torch.Generator().manual_seed(11))
+    out = {}
+    for name, dt in (("32", torch.float32), ("64", torch.float64)):
+        net = net.to(dt)
+        net.zero_grad()
+        (net(x, lengths) * w.to(dt)).sum().backward()
+        keys = sorted(k for k, _ in net.named_parameters())
+        g = {k: p.grad.detach().double() for k, p in net.named_parameters()}
+        out["sums" + name] = np.array([g[k].sum().item() for k in keys])
+        out["abssums" + name] = np.array([g[k].abs().sum().item() for k in keys])
+        for k in ("linear.0.bias", "rnn.bias_hh_l0", "rnn.bias_ih_l1_reverse", "predictors.3.x_coords.bias"):
+            out[f"grad{name}:{k}"] = g[k].numpy()
+    np.savez_compressed(os.path.join(GOLDEN, "model_grad.npz"), keys=np.array(keys), x=x.numpy(),
+                        lengths=lengths.numpy(), w=w.numpy(), **out)
+    print("model_grad:", len(keys), "parameters, |grad| total", out["abssums64"].sum())
+
+
 def golden_p2cp():
     pm = ref.p2a_metrics()
     tgt = synthetic.contours(24, 10, 50, seed=5)
@@ -213,6 +238,7 @@ if __name__ == "__main__":
     assert ref.available(), "reference checkout not found"
     os.makedirs(GOLDEN, exist_ok=True)
     golden_model()
+    golden_model_grad()
     golden_p2cp()
     golden_tv()
     golden_sentence_metrics()

@@ -109,8 +109,8 @@ def test_errors_and_state_dict(mods):
         net.linear[0].bias.add_(1.0)
         b = net(x, [9, 5, 3])
     assert (a - b).abs().max().item() > 1e-4
-    with pytest.raises(NotImplementedError):
-        net(x, [9, 5, 3])                  # autograd enabled: training is not implemented
+    out = net(x, [9, 5, 3])                # autograd enabled: the training path (see test_training_step_*)
+    assert out.requires_grad and torch.equal(out.detach(), b)
 
 
 def test_tcgen05_recurrent_kernel_matches_register_resident_kernel(mods):
@@ -302,3 +302,44 @@ def test_edge_shapes_vs_oracle(mods, B, T, n_art, vocab):
     err = (out.cpu() - want).abs().max().item()
     print(f"edge[{B}x{T}, {n_art} articulators, vocab {vocab}] max-abs {err:.3e}")
     assert err <= TOL["fast"]
+
+
+def test_training_step_gradients_match_reference(mods, golden_dir):
+    """train_phoneme_to_articulation.py:84-96 on the drop-in module: forward values from the kernels,
+    gradients equal to the reference model's own autograd gradients (tests/golden/model_grad.npz), and
+    an optimizer step changes what the kernels compute next."""
+    models, omodel = mods
+    g = np.load(os.path.join(golden_dir, "model_grad.npz"))
+    torch.manual_seed(0)
+    net = models.ArtSpeech(45, 10, precision="fp32").cuda().train()
+    x = torch.from_numpy(g["x"]).cuda()
+    lengths = torch.from_numpy(g["lengths"])
+    w = torch.from_numpy(g["w"]).cuda()
+    opt = torch.optim.SGD(net.parameters(), lr=0.05)
+    opt.zero_grad()
+    out = net(x, lengths)
+    assert out.requires_grad
+    with torch.no_grad():
+        ref_out = net._native_forward(x, lengths)
+    assert torch.equal(out.detach(), ref_out)               # the forward IS the native forward
+    (out * w).sum().backward()
+    named = dict(net.named_parameters())
+    keys = list(g["keys"])
+    sums = np.array([named[k].grad.double().sum().item() for k in keys])
+    abssums = np.array([named[k].grad.double().abs().sum().item() for k in keys])
+    assert np.allclose(abssums, g["abssums64"], rtol=2e-4, atol=1e-6)
+    assert np.abs(sums - g["sums64"]).max() <= 1e-4 * np.abs(g["abssums64"]).max()
+    for k in ("linear.0.bias", "rnn.bias_hh_l0", "rnn.bias_ih_l1_reverse", "predictors.3.x_coords.bias"):
+        want = g["grad64:" + k]
+        err = np.abs(named[k].grad.cpu().numpy() - want).max()
+        assert err <= 1e-4 * max(1.0, np.abs(want).max()), (k, err)
+    before = out.detach().clone()
+    opt.step()
+    with torch.no_grad():
+        after = net(x, lengths)                              # weights changed in place -> re-packed
+    assert (after - before).abs().max().item() > 1e-5
+    # fast precision trains too (forward within 2e-3 of the fp32 graph the gradient is taken through)
+    net2 = models.ArtSpeech(45, 10, precision="fast").cuda().train()
+    o2 = net2(x, lengths)
+    o2.mean().backward()
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in net2.parameters())

@@ -184,3 +184,20 @@ def test_critical_loss_oracle_matches_reference(golden_dir):
             torch.from_numpy(g["x6"]).double(), torch.from_numpy(g["x6"]).double(), None,
             torch.from_numpy(g["mask"])[:, :2])
         assert abs(live.item() - float(g["loss6"])) <= 1e-14
+
+
+def test_oracle_gradient_matches_reference(golden_dir):
+    """Gradients through the oracle's from-the-equations forward (fp64) against the reference
+    model's own autograd gradients (tests/golden/model_grad.npz)."""
+    g = np.load(os.path.join(golden_dir, "model_grad.npz"))
+    sd = {k: v.double().requires_grad_(True) for k, v in omodel.make_state_dict(45, 10, seed=0).items()}
+    fwd = omodel.artspeech_forward.__wrapped__            # the undecorated (grad-enabled) function
+    out = fwd(sd, torch.from_numpy(g["x"]), torch.from_numpy(g["lengths"]), torch.float64, rnn="equations")
+    (out * torch.from_numpy(g["w"]).double()).sum().backward()
+    keys = list(g["keys"])
+    sums = np.array([sd[k].grad.sum().item() for k in keys])
+    abssums = np.array([sd[k].grad.abs().sum().item() for k in keys])
+    assert np.allclose(sums, g["sums64"], rtol=1e-9, atol=1e-10)
+    assert np.allclose(abssums, g["abssums64"], rtol=1e-9, atol=1e-10)
+    for k in ("linear.0.bias", "rnn.bias_hh_l0", "rnn.bias_ih_l1_reverse", "predictors.3.x_coords.bias"):
+        assert np.allclose(sd[k].grad.numpy(), g["grad64:" + k], rtol=1e-9, atol=1e-11)
