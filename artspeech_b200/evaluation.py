@@ -281,3 +281,97 @@ class StreamedEvaluator:
             self.done[s].synchronize()
             out.append(self.acc_host[s].clone())
         return out
+
+
+def save_outputs(sentences_ids, frame_ids, outputs, targets, lengths, phonemes, articulators, save_to,
+                 regularize_out=False):
+    """phoneme_to_articulation/__init__.py:143-199 with the same arguments: per sentence,
+    ``contours/{frame}_{art}[_true].npy`` for the valid frames and ``phonemes.csv``.  B-spline
+    regularisation (``vt_tools.bs_regularization``, un-vendored) is not restated."""
+    import os
+
+    import pandas as pd
+
+    from .contour_files import save_contours
+    if regularize_out:
+        raise NotImplementedError("regularize_out needs vt_tools.bs_regularization.regularize_Bsplines, "
+                                  "which is not part of the reference repository")
+    out_h, tgt_h = outputs.detach().cpu(), targets.detach().cpu()
+    for b, (sentence_id, length, sentence_phonemes, sentence_frames) in enumerate(
+            zip(sentences_ids, lengths, phonemes, frame_ids)):
+        n = min(int(length), len(sentence_phonemes), len(sentence_frames))
+        saves_sentence_dir = os.path.join(save_to, sentence_id)
+        save_contours(saves_sentence_dir, list(sentence_frames)[:n], out_h[b, :n], tgt_h[b, :n], articulators)
+        rows = [{"sentence": sentence_id, "frame": f, "phoneme": p}
+                for f, p in zip(list(sentence_frames)[:n], list(sentence_phonemes)[:n])]
+        pd.DataFrame(rows).to_csv(os.path.join(saves_sentence_dir, "phonemes.csv"), index=False)
+
+
+@torch.no_grad()
+def run_test(epoch, model, dataloader, criterion, outputs_dir, articulators, device=None, regularize_out=False,
+             save=True):
+    """``run_test`` of the reference (phoneme_to_articulation/encoder_decoder/evaluation.py:17-160)
+    with the same arguments and the same ``info`` dict, for the drop-in model.
+
+    The reference moves every batch's outputs to the CPU and loops per sentence (P2CP, MED, Pearson)
+    and per frame (tract variables) in Python.  Here the per-sentence metrics are the device kernels
+    ``asb_p2cp`` + ``asb_eval_accumulate`` and ``asb_eval_sentence_metrics`` over the whole batch,
+    the tract variables of all frames are two launches (``tract_variables`` driver), and only the
+    accumulators and the files to be written leave the GPU.  ``save=False`` (extension) skips the
+    per-frame ``.npy`` / CSV files.  Batches are the dataset's 8-tuples (dataset.py collate):
+    (sentences_ids, sentences, targets, lengths, phonemes, reference_arrays, sentence_frames, voicing)."""
+    import os
+
+    from . import _lib
+    from .tract_variables import REQUIRED_ARTICULATORS_FOR_TVS, UPPER_INCISOR
+    from .tract_variables import tract_variables as tv_driver
+    if device is None:
+        device = torch.device("cuda")
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise RuntimeError("artspeech_b200.evaluation.run_test runs on CUDA only; there is no CPU fallback")
+    _lib.lib()
+    epoch_outputs_dir = os.path.join(outputs_dir, str(epoch))
+    os.makedirs(epoch_outputs_dir, exist_ok=True)
+    model.eval()
+    dataset_config = dataloader.dataset.dataset_config
+    articulators = list(articulators)
+    n = len(articulators)
+    acc = torch.zeros(accumulator_size(n), dtype=torch.float64, device=device)
+    sacc = torch.zeros(3, n, dtype=torch.float64, device=device)
+    losses = []
+    for (sentences_ids, sentences, targets, lengths, phonemes, reference_arrays, sentence_frames, _) in dataloader:
+        sentences = sentences.to(device)
+        targets = targets.to(device)
+        L = [int(v) for v in (lengths.tolist() if torch.is_tensor(lengths) else lengths)]
+        lengths_dev = torch.as_tensor(L, dtype=torch.int32).to(device)
+        outputs = model(sentences, L)                                          # :57
+        T = outputs.shape[1]
+        tgt = targets[:, :T].contiguous()
+        loss = criterion(outputs, tgt)                                         # :58-63
+        mask = length_mask(L, T, device)
+        losses.append(loss[mask].mean().item() if loss.dim() >= 2 else float(loss))
+        p2cp = p2cp_distance(outputs, tgt)                                     # :65-84, all sentences at once
+        zeros4 = torch.zeros(outputs.shape[0], T, 4, dtype=torch.float32, device=device)
+        acc += accumulate_device(p2cp, zeros4, zeros4, lengths_dev)
+        sacc += sentence_metrics_device(outputs, tgt, lengths_dev)
+        if UPPER_INCISOR not in articulators:                                  # :93-109
+            tv_articulators = sorted(articulators + [UPPER_INCISOR])
+            ref_idx = tv_articulators.index(UPPER_INCISOR)
+            ref = reference_arrays.to(device=device, dtype=outputs.dtype)[:, :T]
+            outputs = torch.concat([outputs[:, :, :ref_idx], ref, outputs[:, :, ref_idx:]], dim=2)
+            tgt = torch.concat([tgt[:, :, :ref_idx], ref, tgt[:, :, ref_idx:]], dim=2)
+        else:
+            tv_articulators = articulators
+        if save:
+            if all(a in tv_articulators for a in REQUIRED_ARTICULATORS_FOR_TVS):   # :113-129
+                tv_driver(sentences_ids, sentence_frames, outputs, tgt, L, phonemes, tv_articulators,
+                          epoch_outputs_dir)
+            save_outputs(sentences_ids, sentence_frames, outputs, tgt, L, phonemes, tv_articulators,
+                         epoch_outputs_dir, regularize_out)                    # :131-141
+    reduce_accumulators(acc)
+    reduce_accumulators(sacc)
+    info = {"loss": float(sum(losses) / len(losses)) if losses else float("nan")}
+    to_mm = dataset_config.RES * dataset_config.PIXEL_SPACING                  # :150
+    info.update(run_test_info(acc, sacc, n, to_mm=to_mm, articulators=articulators))
+    return info

@@ -42,8 +42,12 @@ class ArticulatorPredictor(nn.Module):
         self.y_coords = nn.Linear(in_features=256, out_features=n_samples)
 
     def forward(self, inputs):
-        """models.py:23-33 as a differentiable torch graph.  The PRODUCT forward never comes here (the
-        predictors are evaluated inside the fused CUDA decoder); this graph exists for the backward
+        raise RuntimeError("ArticulatorPredictor is evaluated inside ArtSpeech's fused CUDA decoder; "
+                           "it has no standalone forward in artspeech_b200")
+
+    def _graph(self, inputs):
+        """models.py:23-33 as a differentiable torch graph.  The forward pass never comes here (the
+        predictors are evaluated inside the fused CUDA decoder); this graph exists only for the backward
         pass of training, which re-derives the activations with autograd (see ``_TrainingForward``)."""
         linear_out = self.linear(inputs)
         return torch.stack([self.x_coords(linear_out), self.y_coords(linear_out)], dim=2)
@@ -237,7 +241,7 @@ class ArtSpeech(nn.Module):
         packed = pack_padded_sequence(self.embedding(x), torch.as_tensor(lengths, dtype=torch.int64), batch_first=True)
         rnn_out, _ = pad_packed_sequence(self.rnn(packed)[0], batch_first=True)
         hidden = self.linear(rnn_out)
-        return torch.sigmoid(torch.stack([predictor(hidden) for predictor in self.predictors], dim=2))
+        return torch.sigmoid(torch.stack([predictor._graph(hidden) for predictor in self.predictors], dim=2))
 
     def _native_forward(self, x, lengths, lengths_dev=None):
         dev = self.embedding.weight.device

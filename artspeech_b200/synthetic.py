@@ -136,3 +136,33 @@ def walls(n_frames, n_points=50, seed=0, noise=0.0005):
         pts = pts + noise * torch.randn(pts.shape, generator=g, dtype=torch.float64)
         out.append(pts.to(torch.float32).contiguous())
     return out[0], out[1]
+
+
+# ---- a stand-in for the reference's DataLoader (dataset.py collate_fn tuples) ----------------------
+class _Config:
+    RES, PIXEL_SPACING = 136, 1.412          # what dataset_config carries for run_test's to_mm factor
+
+
+class _Dataset:
+    dataset_config = _Config()
+
+
+class SyntheticLoader(list):
+    """A list of the 8-tuples the reference's collate_fn yields - (sentences_ids, sentences, targets,
+    lengths, phonemes, reference_arrays, sentence_frames, voicing) - with a ``.dataset.dataset_config``,
+    which is all ``run_test`` (evaluation.py:17-160) asks of its dataloader."""
+    dataset = _Dataset()
+
+
+def loader(n_batches=2, batch=3, seq_len=7, vocab=45, seed=0):
+    out = SyntheticLoader()
+    for k in range(n_batches):
+        L = sorted_lengths(batch, 2, seq_len, seed=seed + k)
+        tok = tokens(batch, seq_len, vocab, seed=seed + 10 * k)
+        tgt = contours(batch * seq_len, 10, 50, seed=seed + 100 + k).view(batch, seq_len, 10, 2, 50)
+        ids = [f"S{k}_{b}" for b in range(batch)]
+        frames = [["%04d" % (50 * b + t) for t in range(int(L[b]))] for b in range(batch)]
+        phon = [[chr(97 + (t % 26)) for t in range(int(L[b]))] for b in range(batch)]
+        ref = UPPER_INCISOR_REF.view(1, 1, 1, 2, 50).expand(batch, seq_len, 1, 2, 50).contiguous()
+        out.append((ids, tok, tgt, L, phon, ref, frames, None))
+    return out

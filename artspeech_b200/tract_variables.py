@@ -114,3 +114,39 @@ def calculate_vocal_tract_variables(inputs_dict):
         i, j = idx[k]
         out[name] = {"value": val[k], "poc_1": inputs_dict[a1_name][a1_off + i], "poc_2": arr2_point(k, j)}
     return out
+
+
+def tract_variables(sentences_ids, frame_ids, outputs, targets, lengths, phonemes, articulators, save_to):
+    """The frame driver of the reference, phoneme_to_articulation/__init__.py:201-297, with the same
+    arguments and the same ``{save_to}/{sentence_id}/tract_variables.csv`` files (columns: sentence,
+    frame, phoneme, then value + two PoCs per TV for the target, then for the prediction).
+
+    The reference calls ``calculate_vocal_tract_variables`` twice per frame from Python (about
+    0.35 ms each, three ``.item()`` syncs per search); here the tract variables of every frame of
+    the batch, prediction and target, are two kernel launches and one device->host copy.
+    outputs/targets: (bs, seq_len, n_articulators, 2, 50), CPU or CUDA."""
+    import os
+
+    import pandas as pd
+    articulators = list(articulators)
+    val_p, _, poc_p = tract_variables_batch(outputs, articulators)
+    val_t, _, poc_t = tract_variables_batch(targets, articulators)
+    val_p, poc_p, val_t, poc_t = (t.cpu().tolist() for t in (val_p, poc_p, val_t, poc_t))
+    for b, (sentence_id, length, sentence_frames, sentence_phonemes) in enumerate(
+            zip(sentences_ids, lengths, frame_ids, phonemes)):
+        saves_sentence_dir = os.path.join(save_to, sentence_id)
+        os.makedirs(saves_sentence_dir, exist_ok=True)
+        rows = []
+        for t, (frame, phoneme) in enumerate(zip(sentence_frames, sentence_phonemes)):
+            if t >= int(length):
+                break
+            item = {"sentence": sentence_id, "frame": frame, "phoneme": phoneme}
+            for which, val, poc in (("target", val_t, poc_t), ("pred", val_p, poc_p)):   # :263-285
+                for k, name in enumerate(TV_NAMES):
+                    item[f"{name}_{which}"] = val[b][t][k]
+                    item[f"{name}_{which}_poc_1_x"] = poc[b][t][k][0][0]
+                    item[f"{name}_{which}_poc_1_y"] = poc[b][t][k][0][1]
+                    item[f"{name}_{which}_poc_2_x"] = poc[b][t][k][1][0]
+                    item[f"{name}_{which}_poc_2_y"] = poc[b][t][k][1][1]
+            rows.append(item)
+        pd.DataFrame(rows).to_csv(os.path.join(saves_sentence_dir, "tract_variables.csv"), index=False)

@@ -200,6 +200,54 @@ def golden_critical_loss():
     print("critical_loss:", out["loss64"], out["loss32"], float(loss6))
 
 
+def golden_tv_driver():
+    """tract_variables.csv written by the reference's own frame driver (__init__.py:201-297) for two
+    short sentences (float64 copies of fp32 contours, so its cdist is the exact one)."""
+    import shutil
+    import tempfile
+    drv = ref.tract_variables_driver()
+    names = synthetic.TV_ARTICULATORS
+    frames = synthetic.tv_frames(2 * 6, seed=13).view(2, 6, len(names), 2, 50)
+    pred = frames + 0.01 * torch.randn(frames.shape, generator=torch.Generator().manual_seed(3))
+    pred = pred.float()
+    lengths = [6, 4]
+    frame_ids = [["%04d" % (10 + k) for k in range(6)], ["%04d" % (200 + k) for k in range(4)]]
+    phonemes = [list("abcdef"), list("wxyz")]
+    tmp = tempfile.mkdtemp()
+    drv(["S1", "S2"], frame_ids, pred.double(), frames.double(), lengths, phonemes, list(names), tmp)
+    for sid in ("S1", "S2"):
+        shutil.copy(os.path.join(tmp, sid, "tract_variables.csv"), os.path.join(GOLDEN, f"tv_driver_{sid}.csv"))
+    shutil.rmtree(tmp)
+    np.savez_compressed(os.path.join(GOLDEN, "tv_driver.npz"), pred=pred.numpy(), target=frames.numpy())
+    print("tv_driver: 2 sentences,", sum(lengths), "frames")
+
+
+def golden_run_test():
+    """``info`` returned by the reference's own run_test (evaluation.py:17-160) on the reference
+    ArtSpeech (CPU, seed-0 weights) over a synthetic two-batch loader, plus one of the
+    tract_variables.csv / contour files it wrote."""
+    import json
+    import shutil
+    import tempfile
+    rt = ref.run_test()
+    m = ref.models()
+    pm = ref.p2a_metrics()
+    torch.manual_seed(0)
+    net = m.ArtSpeech(45, 10).eval()
+    tmp = tempfile.mkdtemp()
+    info = rt(3, net, synthetic.loader(), pm.EuclideanDistance("none"), tmp, list(synthetic.ARTICULATORS),
+              device=torch.device("cpu"))
+    info = {k: (float(v) if not isinstance(v, dict) else {a: float(b) for a, b in v.items()}) for k, v in info.items()}
+    with open(os.path.join(GOLDEN, "run_test_info.json"), "w") as f:
+        json.dump(info, f, indent=1, sort_keys=True)
+    shutil.copy(os.path.join(tmp, "3", "S1_2", "tract_variables.csv"), os.path.join(GOLDEN, "run_test_S1_2_tv.csv"))
+    files = sorted(os.listdir(os.path.join(tmp, "3", "S0_0", "contours")))
+    with open(os.path.join(GOLDEN, "run_test_S0_0_files.txt"), "w") as f:
+        f.write("\n".join(files) + "\n")
+    shutil.rmtree(tmp)
+    print("run_test: loss", info["loss"], "tongue", info["tongue"])
+
+
 def golden_area():
     """The parts of area_function.py that run without GEOS: grid, mid_point, argmatrix, rotate and
     area_function (a9, a11).  a10 / a12 need shapely and stay unpinned (oracle/area.py header)."""
@@ -243,4 +291,6 @@ if __name__ == "__main__":
     golden_tv()
     golden_sentence_metrics()
     golden_area()
+    golden_run_test()
+    golden_tv_driver()
     golden_critical_loss()

@@ -131,3 +131,58 @@ def critical_loss():
           "TONGUE": "tongue", "UPPER_INCISOR": "upper-incisor", "UPPER_LIP": "upper-lip"}
     exec(code, ns)
     return ns["CriticalLoss"]
+
+
+def tract_variables_driver():
+    """reference frame driver ``tract_variables(...)`` (phoneme_to_articulation/__init__.py:201-297).
+    The package's __init__ cannot be imported (vt_tools / vt_shape_gen), so ONLY this function's
+    statement is compiled - source text unmodified, cut out with ``ast`` - in a namespace holding
+    ``os``, ``pd`` and the reference's own ``calculate_vocal_tract_variables``."""
+    import ast
+    import pandas as pd
+    path = os.path.join(REFERENCE_ROOT, "phoneme_to_articulation/__init__.py")
+    with open(path) as f:
+        tree = ast.parse(f.read())
+    node = next(n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "tract_variables")
+    code = compile(ast.Module(body=[node], type_ignores=[]), path, "exec")
+    ns = {"os": os, "pd": pd, "calculate_vocal_tract_variables": tract_variables().calculate_vocal_tract_variables}
+    exec(code, ns)
+    return ns["tract_variables"]
+
+
+def _cut(relpath, name, ns, kind="function"):
+    """Compile one top-level statement (function or class ``name``) of a reference file, source text
+    unmodified, in namespace ``ns`` - for modules whose other imports cannot be satisfied here."""
+    import ast
+    path = os.path.join(REFERENCE_ROOT, relpath)
+    with open(path) as f:
+        tree = ast.parse(f.read())
+    want = ast.FunctionDef if kind == "function" else ast.ClassDef
+    node = next(n for n in tree.body if isinstance(n, want) and n.name == name)
+    exec(compile(ast.Module(body=[node], type_ignores=[]), path, "exec"), ns)
+    return ns[name]
+
+
+def run_test():
+    """reference ``run_test`` (phoneme_to_articulation/encoder_decoder/evaluation.py:17-160) assembled
+    from the reference's own pieces: its metrics.py functions, ``make_padding_mask`` (helpers.py:79-91),
+    ``tract_variables`` and ``save_outputs`` (phoneme_to_articulation/__init__.py:128-297) - each cut out
+    as an unmodified statement because the enclosing modules import un-vendored packages."""
+    import numpy as np
+    import pandas as pd
+    import torch
+    from tqdm import tqdm
+    rm = root_metrics()
+    tv = tract_variables()
+    ns_pkg = {"os": os, "pd": pd, "np": np,
+              "calculate_vocal_tract_variables": tv.calculate_vocal_tract_variables}
+    drv = _cut("phoneme_to_articulation/__init__.py", "tract_variables", ns_pkg)
+    save = _cut("phoneme_to_articulation/__init__.py", "save_outputs", ns_pkg)
+    mask = _cut("helpers.py", "make_padding_mask", {"torch": torch})
+    ns = {"np": np, "os": os, "torch": torch, "tqdm": tqdm, "make_padding_mask": mask,
+          "pearsons_correlation": rm.pearsons_correlation, "p2cp_distance": rm.p2cp_distance,
+          "euclidean_distance": rm.euclidean_distance, "save_outputs": save, "tract_variables": drv,
+          "REQUIRED_ARTICULATORS_FOR_TVS": ["lower-lip", "pharynx", "soft-palate-midline", "tongue", "upper-lip",
+                                            "upper-incisor"],
+          "UPPER_INCISOR": "upper-incisor"}
+    return _cut("phoneme_to_articulation/encoder_decoder/evaluation.py", "run_test", ns)

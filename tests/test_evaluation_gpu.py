@@ -129,3 +129,42 @@ def test_sentence_metrics_match_reference_run_test_numbers():
         ref[1] += xc.mean(dim=-1)[0].numpy()
         ref[2] += yc.mean(dim=-1)[0].numpy()
     np.testing.assert_allclose(got.cpu().numpy(), ref, rtol=1e-8, atol=1e-9)
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 2e-4), ("fast", 2e-2)])
+def test_run_test_matches_reference_run_test(golden_dir, tmp_path, precision, tol):
+    """The whole ``run_test`` (evaluation.py:17-160) on the drop-in model against the ``info`` dict
+    the reference's own run_test returned for the reference model on the same synthetic loader
+    (tests/golden/run_test_info.json, written by oracle/make_golden.py), and the files it writes."""
+    import json
+    import os
+
+    import pandas as pd
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from artspeech_b200 import evaluation, metrics, models
+    with open(os.path.join(golden_dir, "run_test_info.json")) as f:
+        want = json.load(f)
+    torch.manual_seed(0)
+    net = models.ArtSpeech(45, 10, precision=precision).cuda()
+    info = evaluation.run_test(3, net, synthetic.loader(), metrics.EuclideanDistance("none"), str(tmp_path),
+                               list(synthetic.ARTICULATORS))
+    assert sorted(info.keys()) == sorted(want.keys())
+    assert abs(info["loss"] - want["loss"]) <= tol * want["loss"]
+    for art in synthetic.ARTICULATORS:
+        for k in ("p2cp", "p2cp_mm", "med", "med_mm"):
+            assert abs(info[art][k] - want[art][k]) <= tol * want[art][k], (art, k, info[art][k], want[art][k])
+        for k in ("x_corr", "y_corr"):
+            assert abs(info[art][k] - want[art][k]) <= 50 * tol, (art, k, info[art][k], want[art][k])
+    # files: same names as the reference wrote, TV table with the same columns and close values
+    files = sorted(os.listdir(os.path.join(str(tmp_path), "3", "S0_0", "contours")))
+    with open(os.path.join(golden_dir, "run_test_S0_0_files.txt")) as f:
+        assert files == f.read().split()
+    got = pd.read_csv(os.path.join(str(tmp_path), "3", "S1_2", "tract_variables.csv"), dtype={"frame": str})
+    ref = pd.read_csv(os.path.join(golden_dir, "run_test_S1_2_tv.csv"), dtype={"frame": str})
+    assert list(got.columns) == list(ref.columns) and list(got["frame"]) == list(ref["frame"])
+    for name in ("LA", "TTCD", "TBCD", "VEL"):
+        a, b = got[f"{name}_target"].to_numpy(), ref[f"{name}_target"].to_numpy()
+        assert (abs(a - b) <= 1e-3 * abs(b)).all()            # the reference's fp32 cdist (finding F2)
+    ph = pd.read_csv(os.path.join(str(tmp_path), "3", "S1_2", "phonemes.csv"), dtype={"frame": str})
+    assert list(ph.columns) == ["sentence", "frame", "phoneme"] and len(ph) == len(got)

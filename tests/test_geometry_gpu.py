@@ -120,3 +120,29 @@ def test_tv_dict_api(asb, golden_dir):
     bad = dict(d); bad.pop("tongue")
     with pytest.raises(KeyError):
         TV.calculate_vocal_tract_variables(bad)
+
+
+def test_tract_variables_driver_csv_matches_reference(golden_dir, tmp_path):
+    """The frame driver (phoneme_to_articulation/__init__.py:201-297): same files, same columns in
+    the same order, same ids; values within 1e-5 relative of the reference driver's own CSVs and
+    the points of closest approach equal to the fp32 inputs they were picked from."""
+    import pandas as pd
+    from artspeech_b200 import tract_variables as TV
+    g = np.load(os.path.join(golden_dir, "tv_driver.npz"))
+    pred, target = torch.from_numpy(g["pred"]), torch.from_numpy(g["target"])
+    frame_ids = [["%04d" % (10 + k) for k in range(6)], ["%04d" % (200 + k) for k in range(4)]]
+    phonemes = [list("abcdef"), list("wxyz")]
+    TV.tract_variables(["S1", "S2"], frame_ids, pred, target, [6, 4], phonemes, list(synthetic.TV_ARTICULATORS),
+                       str(tmp_path))
+    for sid, n in (("S1", 6), ("S2", 4)):
+        got = pd.read_csv(os.path.join(str(tmp_path), sid, "tract_variables.csv"), dtype={"frame": str})
+        want = pd.read_csv(os.path.join(golden_dir, f"tv_driver_{sid}.csv"), dtype={"frame": str})
+        assert list(got.columns) == list(want.columns) and len(got) == len(want) == n
+        for col in ("sentence", "frame", "phoneme"):
+            assert list(got[col]) == list(want[col])
+        for col in want.columns[3:]:
+            a, b = got[col].to_numpy(dtype=np.float64), want[col].to_numpy(dtype=np.float64)
+            if "_poc_" in col:
+                assert np.array_equal(a.astype(np.float32), b.astype(np.float32)), col
+            else:
+                assert np.all(np.abs(a - b) <= 1e-5 * np.abs(b)), col
