@@ -146,3 +146,32 @@ def test_tract_variables_driver_csv_matches_reference(golden_dir, tmp_path):
                 assert np.array_equal(a.astype(np.float32), b.astype(np.float32)), col
             else:
                 assert np.all(np.abs(a - b) <= 1e-5 * np.abs(b)), col
+
+
+def test_config3_full_size_p2cp_and_tv(asb):
+    """BASELINE configs[2]: 1 048 576 frames x 11 articulators x 50 points (4.6 GB per tensor, byte
+    offsets beyond 2^32).  Size-independent properties: the frames are 256 copies of a 4096-frame
+    block, so every copy must reproduce the block's result bit for bit wherever it lies in memory
+    (persistent-CTA tile -> address arithmetic), the block itself is checked against the fp64 oracle,
+    and P2CP of a tensor with itself is exactly zero everywhere."""
+    from oracle import geometry as og
+    M, TV = asb
+    F, blk = 1 << 20, 4096
+    base_t = synthetic.tv_frames(blk, seed=31)
+    base_p = synthetic.perturbed(base_t, seed=32)
+    tgt = base_t.cuda().repeat(F // blk, 1, 1, 1)
+    pred = base_p.cuda().repeat(F // blk, 1, 1, 1)
+    assert tgt.shape == (F, 11, 2, 50) and tgt.numel() * 4 > (1 << 32)
+    p = M.p2cp_distance(pred, tgt)                                    # (F, 11)
+    assert p.shape == (F, 11)
+    want = og.p2cp_distance(base_p, base_t)
+    assert _rel(p[:blk].cpu(), want) <= REL
+    assert torch.equal(p.view(F // blk, blk, 11), p[:blk].unsqueeze(0).expand(F // blk, blk, 11))
+    assert float(M.p2cp_distance(tgt, tgt).abs().max()) == 0.0
+    val, idx, poc = TV.tract_variables_batch(tgt, synthetic.TV_ARTICULATORS)
+    oval, oidx, opoc = og.tract_variables_batch_vectorized(base_t, synthetic.TV_ART_INDEX)
+    assert _rel(val[:blk].cpu(), oval) <= REL
+    assert torch.equal(idx[:blk].cpu(), oidx) and torch.equal(poc[:blk].cpu().double(), opoc)
+    for t in (val, idx, poc):
+        v = t.view(F // blk, blk, -1)
+        assert torch.equal(v, v[:1].expand_as(v))
