@@ -20,7 +20,7 @@
 //   4. touched lines are compacted in grid order (ballot/popc), mid-points, radii and
 //      alpha * r^beta go to shared memory, the cumulative mid-point distance is a warp scan;
 //   5. each lane evaluates the piecewise-linear profile at its share of the n_samples abscissae
-//      (binary search in shared memory) and writes the (2, n_samples) fp32 result coalesced.
+//      (branch-free binary search in shared memory) and writes the (2, n_samples) fp32 result coalesced.
 // All fp64 arithmetic uses the non-fusing intrinsics so that it rounds like NumPy / gcc
 // -ffp-contract=off.
 #include "asb_common.cuh"
@@ -31,6 +31,9 @@ namespace {
 
 using namespace asb;
 
+#ifndef ASB_AREA_ABLATE
+#define ASB_AREA_ABLATE 0   // timing experiments (tools/area_variants.py): 1 = no resampling; 2 = no crossings (then K = 0: staging + filter + NaN rows only); 6 = staging + NaN rows only
+#endif
 #ifndef ASB_AREA_MINB
 #define ASB_AREA_MINB 2
 #endif
@@ -172,59 +175,40 @@ __device__ __forceinline__ u64 candidates(u64 neg, u64 zer, int n_wall) {
 }
 
 // evenly_spaced_fx (:145-159): the polyline (x, fx) of K >= 2 points evaluated at
-// np.linspace(x[0], x[K-1], n_samples); out (2, n_samples) fp32.  One warp.  A lane takes kPerLane
-// consecutive abscissae: one binary search for the first, then the segment index only advances.
-// The ordinates go through `stage` (kStage floats of shared memory) so that the global writes are
-// coalesced; the abscissae are recomputed by the writing lane.
-constexpr int kPerLane = 8;
-constexpr int kStage = 32 * kPerLane;
-
+// np.linspace(x[0], x[K-1], n_samples); out (2, n_samples) fp32.  One warp, one sample per lane and
+// pass, so the global writes are coalesced as they are.  The segment of an abscissa - the first k
+// with x[k] <= xv <= x[k+1], i.e. the number of x[1..K-1] below xv (x is non-decreasing), capped at
+// K-2 - comes from a branch-free binary search with a warp-uniform trip count; the special cases
+// are selects.  (The earlier version gave each lane 8 consecutive abscissae and walked the segment
+// index forward: its divergent loops took 25 % of the kernel's stall samples for 7 % of its work.)
 template <bool kSlope>
 __device__ __forceinline__ void resample(const double* x, const double* fx, const double* slope, int K,
-                                         int n_samples, float* out, int lane, float* stage) {
+                                         int n_samples, float* out, int lane) {
   const double x0 = x[0], x1 = x[K - 1];
   const double step = __ddiv_rn(__dsub_rn(x1, x0), (double)(n_samples - 1));
   const double qnan = __longlong_as_double(0x7ff8000000000000LL);
-  for (int base = 0; base < n_samples; base += kStage) {
-    const int s0 = base + lane * kPerLane;
-    int seg = -1;
-#pragma unroll 1
-    for (int i = 0; i < kPerLane; ++i) {
-      const int s = s0 + i;
-      if (s >= n_samples) break;
-      const double xv = (s == n_samples - 1) ? x1 : __dadd_rn(x0, __dmul_rn((double)s, step));
-      // first segment k with x[k] <= xv <= x[k+1]  ==  smallest k with x[k+1] >= xv
-      if (seg < 0) {
-        int lo = 0, hi = K - 2;
-        while (lo < hi) {
-          const int mid = (lo + hi) >> 1;
-          if (x[mid + 1] >= xv) hi = mid; else lo = mid + 1;
-        }
-        seg = lo;
-      } else {
-        while (seg < K - 2 && x[seg + 1] < xv) ++seg;
-      }
-      const double da = x[seg], db = x[seg + 1];
-      double yv;
-      if (db == da || xv == da) yv = fx[seg];
-      else if (xv == db) yv = fx[seg + 1];
-      else if (kSlope)
-        yv = __dadd_rn(fx[seg], __dmul_rn(__dsub_rn(xv, da), slope[seg]));
-      else
-        yv = __dadd_rn(fx[seg], __dmul_rn(__ddiv_rn(__dsub_rn(xv, da), __dsub_rn(db, da)),
-                                          __dsub_rn(fx[seg + 1], fx[seg])));
-      if (!(da <= xv && xv <= db)) yv = qnan;  // outside the polyline
-      const int q = lane * kPerLane + i;
-      stage[q ^ (lane >> 2)] = (float)yv;     // xor swizzle: lanes 8 floats apart land in different banks
+  const int n = K - 1;                       // candidates x[1..K-1]
+  const int top = 1 << (31 - __clz(n));      // n >= 1
+  for (int s = lane; s < n_samples; s += 32) {
+    const double xv = (s == n_samples - 1) ? x1 : __dadd_rn(x0, __dmul_rn((double)s, step));
+    int pos = 0;                             // number of x[1..K-1] that are < xv
+    for (int half = top; half > 0; half >>= 1) {
+      const int t = pos + half;
+      const double probe = x[t <= n ? t : n];
+      pos = (t <= n && probe < xv) ? t : pos;
     }
-    __syncwarp();
-    for (int q = lane; q < kStage && base + q < n_samples; q += 32) {
-      const int s = base + q;
-      const double xv = (s == n_samples - 1) ? x1 : __dadd_rn(x0, __dmul_rn((double)s, step));
-      out[s] = (float)xv;
-      out[n_samples + s] = stage[q ^ ((q / kPerLane) >> 2)];
-    }
-    __syncwarp();
+    const int seg = pos < K - 2 ? pos : K - 2;
+    const double da = x[seg], db = x[seg + 1], f0 = fx[seg], f1 = fx[seg + 1];
+    double yv;
+    if (kSlope)
+      yv = __dadd_rn(f0, __dmul_rn(__dsub_rn(xv, da), slope[seg]));
+    else
+      yv = __dadd_rn(f0, __dmul_rn(__ddiv_rn(__dsub_rn(xv, da), __dsub_rn(db, da)), __dsub_rn(f1, f0)));
+    yv = (xv == db) ? f1 : yv;
+    yv = (db == da || xv == da) ? f0 : yv;
+    yv = (da <= xv && xv <= db) ? yv : qnan;  // outside the polyline
+    out[s] = (float)xv;
+    out[n_samples + s] = (float)yv;
   }
 }
 
@@ -280,24 +264,52 @@ __global__ void __launch_bounds__(kWarps * 32, ASB_AREA_MINB) area_function_kern
   const int nw = p.n_wall;
   const unsigned lt_mask = (1u << lane) - 1u;
 
-  for (long long f = (long long)blockIdx.x * kWarps + warp; f < p.frames; f += (long long)gridDim.x * kWarps) {
-    // ---- 1. stage the walls
+  // The walls of the NEXT frame are copied global -> shared (cp.async, no registers) while the
+  // current one is processed: the staging loads of a frame used to sit un-overlapped at its start
+  // (12 % of the stall samples on their first consumer, profiles/r1d_geometry_ncu.txt).
+  extern __shared__ __align__(16) float2 sraw_all[];                // [kWarps][2 walls][kMaxWall]
+  float2* sraw = sraw_all + warp * 2 * kMaxWall;
+  const long long fstride = (long long)gridDim.x * kWarps;
+  auto prefetch = [&](long long f) {
+    for (int q = lane; q < 2 * nw; q += 32) {
+      const int which = q >= nw;
+      const int k = q - which * nw;
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(sraw + which * kMaxWall + k)),
+                   "l"((which ? p.we : p.wi) + f * nw + k)
+                   : "memory");
+    }
+  };
+  {
+    const long long f0 = (long long)blockIdx.x * kWarps + warp;
+    if (f0 < p.frames) prefetch(f0);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  for (long long f = (long long)blockIdx.x * kWarps + warp; f < p.frames; f += fstride) {
+    // ---- 1. expand the staged walls to the filter's (x, x, y, y) layout, then refill the staging buffer
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
     float wmax = 0.f;
     for (int q = lane; q < 2 * nw; q += 32) {
       const int which = q >= nw;
       const int k = q - which * nw;
-      const float2 v = __ldg((which ? p.we : p.wi) + f * nw + k);
+      const float2 v = sraw[which * kMaxWall + k];
       swall[warp][which][k] = make_float4(v.x, v.x, v.y, v.y);
       wmax = fmaxf(wmax, fmaxf(fabsf(v.x), fabsf(v.y)));
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) wmax = fmaxf(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
     __syncwarp();
+    if (f + fstride < p.frames) prefetch(f + fstride);
+    asm volatile("cp.async.commit_group;" ::: "memory");
 
     // ---- 2. sign masks
     u64 negI[kRounds], zerI[kRounds], negE[kRounds], zerE[kRounds];
+#if ASB_AREA_ABLATE & 4
+    for (int r = 0; r < kRounds; ++r) { negI[r] = __float_as_uint(wI[lane].x); zerI[r] = 0; negE[r] = __float_as_uint(wE[lane].x); zerE[r] = 0; }
+#else
     wall_masks(wI, nw, lc, lane, sgrid, wmax, negI, zerI);
     wall_masks(wE, nw, lc, lane, sgrid, wmax, negE, zerE);
+#endif
 
     const double eFx = wE[0].x, eFy = wE[0].z, eLx = wE[nw - 1].x, eLy = wE[nw - 1].z;
 
@@ -306,8 +318,12 @@ __global__ void __launch_bounds__(kWarps * 32, ASB_AREA_MINB) area_function_kern
 #pragma unroll 1
     for (int r = 0; r < kRounds; ++r) {
       const int l = r * 32 + lane;
+#if ASB_AREA_ABLATE & 2
+      const u64 cI = (negI[r] ^ negE[r]) == 0x123456789ull, cE = 0;   // never a candidate, masks stay live
+#else
       const u64 cI = candidates(negI[r], zerI[r], nw);
       const u64 cE = candidates(negE[r], zerE[r], nw);
+#endif
       bool anyI = false, anyE = false;
       double ix = 0, iy = 0, ox = 0, oy = 0;  // selected internal / external point
       // Distances are only compared, so the selection works on squared distances.
@@ -440,7 +456,7 @@ __global__ void __launch_bounds__(kWarps * 32, ASB_AREA_MINB) area_function_kern
     __syncwarp();
 
     // ---- 5. evenly_spaced_fx (:145-159); the walls are consumed, their shared memory holds the
-    // per-segment slopes (one division per segment instead of one per sample) and the staging row
+    // per-segment slopes (one division per segment instead of one per sample)
     double* slope = reinterpret_cast<double*>(wI);
 #pragma unroll
     for (int q = 0; q < kRounds; ++q) {
@@ -451,7 +467,9 @@ __global__ void __launch_bounds__(kWarps * 32, ASB_AREA_MINB) area_function_kern
       }
     }
     __syncwarp();
-    resample<true>(dist, fxs, slope, K, p.n_samples, out, lane, reinterpret_cast<float*>(wE));
+#if !(ASB_AREA_ABLATE & 1)
+    resample<true>(dist, fxs, slope, K, p.n_samples, out, lane);
+#endif
     __syncwarp();
   }
 }
@@ -498,8 +516,7 @@ evenly_spaced_kernel(const double* __restrict__ x, const double* __restrict__ fx
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long f = (long long)blockIdx.x * kWarps + warp;
   if (f >= frames) return;
-  __shared__ float stage[kWarps][kStage];
-  resample<false>(x + f * K, fx + f * K, nullptr, K, n_samples, out + f * 2 * (long long)n_samples, lane, stage[warp]);
+  resample<false>(x + f * K, fx + f * K, nullptr, K, n_samples, out + f * 2 * (long long)n_samples, lane);
 }
 
 }  // namespace
@@ -526,7 +543,14 @@ extern "C" int asb_area_function(const float* walls_int, const float* walls_ext,
   const long long want = (frames + kWarps - 1) / kWarps;
   const long long cap = (long long)asb::sm_count() * 4;
   const unsigned blocks = (unsigned)(want < cap ? want : cap);
-  area_function_kernel<<<blocks, kWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  const int raw_bytes = kWarps * 2 * kMaxWall * int(sizeof(float2));   // wall staging buffer (dynamic part)
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(area_function_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, raw_bytes);
+    if (e != cudaSuccess) return asb::check_cuda(e, "asb_area_function: smem attribute");
+    configured = true;
+  }
+  area_function_kernel<<<blocks, kWarps * 32, raw_bytes, static_cast<cudaStream_t>(stream)>>>(a);
   ASB_CHECK_LAUNCH("area_function_kernel");
   return ASB_OK;
 }
