@@ -34,9 +34,13 @@ using namespace asb;
 #ifndef ASB_AREA_ABLATE
 #define ASB_AREA_ABLATE 0   // timing experiments (tools/area_variants.py): 1 = no resampling; 2 = no crossings (then K = 0: staging + filter + NaN rows only); 6 = staging + NaN rows only
 #endif
+#ifndef ASB_AREA_UNROLL
+#define ASB_AREA_UNROLL 1   // rounds of the crossing stage interleaved per trip
+#endif
 #ifndef ASB_AREA_MINB
 #define ASB_AREA_MINB 2
 #endif
+constexpr int kRoundUnroll = ASB_AREA_UNROLL;
 constexpr int kWarps = 8;
 constexpr int kMaxWall = 64;    // vertices per wall (one 64-bit sign mask)
 constexpr int kRounds = 4;      // grid lines per lane
@@ -315,7 +319,7 @@ __global__ void __launch_bounds__(kWarps * 32, ASB_AREA_MINB) area_function_kern
 
     // ---- 3./4. per line: intersections, selection, compaction
     int base = 0;
-#pragma unroll 1
+#pragma unroll(kRoundUnroll)
     for (int r = 0; r < kRounds; ++r) {
       const int l = r * 32 + lane;
 #if ASB_AREA_ABLATE & 2
