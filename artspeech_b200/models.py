@@ -286,7 +286,7 @@ class SimpleArtSpeech(nn.Module):
     decoder kernel (``asb_model_decode``) is run once over the V embedding rows whenever the weights
     change, and ``forward`` is a row gather from that (V, N, 2, n_samples) table (``asb_gather_rows``),
     bound by the 4000 B per frame it writes.  ``lengths`` is accepted and ignored, as in the reference.
-    Inference only (dropout is the identity in eval mode, models.py:64,92)."""
+    Dropout is the identity in eval mode (models.py:64,92); train mode with dropout > 0 is not built."""
 
     def __init__(self, vocab_size, n_articulators, embed_dim=64, hidden_size=128, num_samples=50, dropout=0.,
                  precision="fast"):
@@ -378,12 +378,21 @@ class SimpleArtSpeech(nn.Module):
         return table
 
     def forward(self, x, lengths=None):
-        """x (bs, seq_len) int64 -> (bs, seq_len, n_articulators, 2, n_samples) float32 (models.py:84-96)."""
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
-            raise NotImplementedError("artspeech_b200.SimpleArtSpeech implements inference only; call it under "
-                                      "torch.no_grad()")
+        """x (bs, seq_len) int64 -> (bs, seq_len, n_articulators, 2, n_samples) float32 (models.py:84-96).
+        Under autograd the values still come from the kernels and the backward pass differentiates a
+        recomputed torch graph of the same parameters (``_TrainingForward``)."""
         if self.training and self.dropout.p > 0:
-            raise NotImplementedError("dropout (train mode) is not implemented; call .eval()")
+            raise NotImplementedError("dropout (train mode with dropout > 0) is not implemented")
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            return _TrainingForward.apply(self, x, lengths, *self.parameters())
+        return self._native_forward(x, lengths)
+
+    def _library_graph(self, x, lengths=None):
+        """models.py:84-96 on the parameter containers as a differentiable torch graph (backward only)."""
+        hidden = self.linear(self.dropout(self.embedding(x)))
+        return torch.sigmoid(torch.stack([predictor._graph(hidden) for predictor in self.predictors], dim=2))
+
+    def _native_forward(self, x, lengths=None):
         dev = self.embedding.weight.device
         if dev.type != "cuda":
             raise RuntimeError("artspeech_b200.SimpleArtSpeech runs on CUDA only (call .to('cuda')); no CPU fallback")

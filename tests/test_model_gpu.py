@@ -343,3 +343,28 @@ def test_training_step_gradients_match_reference(mods, golden_dir):
     o2 = net2(x, lengths)
     o2.mean().backward()
     assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in net2.parameters())
+
+
+def test_simple_artspeech_training_step(mods):
+    """SimpleArtSpeech under autograd: native forward values, gradients equal to those of the fp64
+    oracle graph (models.py:84-96), and the per-token table follows an optimizer step."""
+    models, omodel = mods
+    torch.manual_seed(0)
+    net = models.SimpleArtSpeech(45, 10, precision="fp32").cuda().train()
+    sd = {k: v.detach().cpu().double().requires_grad_(True) for k, v in net.state_dict().items()}
+    x = synthetic.tokens(4, 9, 45, seed=6)
+    w = torch.randn(4, 9, 10, 2, 50, generator=torch.Generator().manual_seed(2))
+    out = net(x.cuda(), [9] * 4)
+    assert out.requires_grad
+    (out * w.cuda()).sum().backward()
+    want = omodel.simple_artspeech_forward.__wrapped__(sd, x, torch.float64)
+    (want * w.double()).sum().backward()
+    assert (out.detach().cpu().double() - want.detach()).abs().max().item() <= TOL["fp32"]
+    for k, p in net.named_parameters():
+        g, gw = p.grad.cpu().double(), sd[k].grad
+        assert (g - gw).abs().max().item() <= 1e-4 * max(1.0, gw.abs().max().item()), k
+    opt = torch.optim.SGD(net.parameters(), lr=0.1)
+    opt.step()
+    with torch.no_grad():
+        after = net(x.cuda(), None)
+    assert (after - out.detach()).abs().max().item() > 1e-5
