@@ -36,6 +36,13 @@ class AsbWeights(ctypes.Structure):
     )
 
 
+class AsbPcWeights(ctypes.Structure):
+    """Mirror of `struct asb_pc_weights`."""
+    _fields_ = [(n, ctypes.c_void_p) for n in (
+        "lin_w", "lin_b", "ln0_w", "ln0_b", "fc1_w", "fc1_b", "ln1_w", "ln1_b", "fc2_w", "fc2_b", "ln2_w", "ln2_b",
+        "fc3_w", "fc3_b")]
+
+
 # name -> (restype, argtypes); every symbol include/artspeech_b200.h declares
 SIGNATURES = {
     "asb_abi_version": (ctypes.c_int, []),
@@ -72,6 +79,13 @@ SIGNATURES = {
     "asb_eval_sentence_metrics": (ctypes.c_int, [_c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                                  ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                                  ctypes.c_void_p]),
+    "asb_model_forward_hidden": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                                ctypes.POINTER(ctypes.c_int32), ctypes.c_void_p, ctypes.c_int,
+                                                _c_f32p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]),
+    "asb_pc_head_create": (ctypes.c_int, [ctypes.POINTER(AsbPcWeights), ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                          ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]),
+    "asb_pc_head_destroy": (None, [ctypes.c_void_p]),
+    "asb_pc_head_forward": (ctypes.c_int, [ctypes.c_void_p, _c_f32p, ctypes.c_int64, _c_f32p, ctypes.c_void_p]),
     "asb_model_decode": (ctypes.c_int, [ctypes.c_void_p, _c_f32p, ctypes.c_int64, _c_f32p, ctypes.c_void_p]),
     "asb_gather_rows": (ctypes.c_int, [_c_f32p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_int,
                                        _c_f32p, ctypes.c_void_p]),

@@ -12,6 +12,8 @@
 // streamed from L2 through a 2-stage cp.async ring as ONE continuous chunk sequence across all
 // 31 GEMMs of a tile, so the pipeline never drains between layers.  fp32 mode runs the same code
 // with 3xTF32 error compensation (a_lo*b_hi + a_hi*b_lo + a_hi*b_hi).
+#include <new>
+
 #include "model.cuh"
 
 namespace {
@@ -353,6 +355,110 @@ __global__ void __launch_bounds__(kThreads, 1) linear256_kernel(const LinearArgs
   }
 }
 
+// ---------------------------------------------------------------- principal-components head
+// PrincipalComponentsArtSpeech's tail (phoneme_to_articulation/principal_components/models/rnn.py:
+// 11-33, 70-79, 106-108): linear (2H -> H) + ReLU, then PrincipalComponentsPredictor = LayerNorm(H) ->
+// Linear(H,256) -> ReLU -> LayerNorm(256) -> Linear(256,128) -> ReLU -> LayerNorm(128) ->
+// Linear(128, n_components), then tanh.  Same building blocks as the contour decoder: one 64-frame
+// tile per CTA, activations in shared memory, weights streamed as one chunk sequence of 24 chunks.
+constexpr int kPcMid = 128;    // hidden_features / 2
+constexpr int kPcOutPad = 128; // n_components rows padded to one 128-row weight stage
+
+struct PcWeights {
+  float* lin_w; float* lin_b;    // [H][2H], [H]
+  float* ln0_w; float* ln0_b;    // [H]
+  float* fc1_w; float* fc1_b;    // [256][H], [256]
+  float* ln1_w; float* ln1_b;    // [256]
+  float* fc2_w; float* fc2_b;    // [128][256], [128]
+  float* ln2_w; float* ln2_b;    // [128]
+  float* fc3_w; float* fc3_b;    // [128 (n_components, zero padded)][128], [128]
+};
+
+struct PcArgs {
+  const float* rnn_out;  // (M, 2H)
+  float* out;            // (M, n_components)
+  long long M;
+  int n_components;
+  PcWeights w;
+};
+
+template <bool X3>
+__global__ void __launch_bounds__(kThreads, 1) pc_head_kernel(const PcArgs a) {
+  extern __shared__ __align__(16) float smem[];
+  float* Xs = smem;                       // [64][136]
+  float* Hs = Xs + kBM * kXStride;        // [64][264]
+  float* Ws = Hs + kBM * kHStride;        // 2 weight stages
+  const int tid = threadIdx.x;
+  const long long row0 = (long long)blockIdx.x * kBM;
+  const PcWeights& w = a.w;
+  constexpr int q_end = 8 + 4 + 8 + 4;
+
+  auto next = [&](int q) -> Chunk {
+    if (q < 8) return Chunk{w.lin_w + q * kBK, kH, 2 * kH};
+    if (q < 12) return Chunk{w.fc1_w + (q - 8) * kBK, kFc, kH};
+    if (q < 20) return Chunk{w.fc2_w + (q - 12) * kBK, kPcMid, kFc};
+    return Chunk{w.fc3_w + (q - 20) * kBK, kPcOutPad, kPcMid};
+  };
+
+  issue_chunk(next(0), Ws, tid);
+  load_rows<2 * kH, !X3>(a.rnn_out, row0, a.M, Hs, kHStride, tid);
+  int q = 0;
+  {  // linear + ReLU   (rnn.py:70-73,106)
+    float acc[2][4][4];
+    zero_acc<4>(acc);
+    cta_gemm<4, X3>(acc, Hs, kHStride, 2 * kH, q, q_end, next, Ws, tid);
+    store_bias_relu<4, false>(acc, w.lin_b, Xs, kXStride, tid);
+  }
+  __syncthreads();
+  layer_norm_rows<kH, !X3>(Xs, kXStride, Hs, kHStride, w.ln0_w, w.ln0_b, tid);       // rnn.py:21
+  {  // Linear(H,256) + ReLU   (:22-23)
+    float acc[2][8][4];
+    zero_acc<8>(acc);
+    cta_gemm<8, X3>(acc, Hs, kHStride, kH, q, q_end, next, Ws, tid);
+    __syncthreads();
+    store_bias_relu<8, false>(acc, w.fc1_b, Hs, kHStride, tid);
+  }
+  __syncthreads();
+  layer_norm_rows<kFc, !X3>(Hs, kHStride, Hs, kHStride, w.ln1_w, w.ln1_b, tid);      // :24
+  {  // Linear(256,128) + ReLU   (:25-26); written to Xs, Hs is the operand being read
+    float acc[2][4][4];
+    zero_acc<4>(acc);
+    cta_gemm<4, X3>(acc, Hs, kHStride, kFc, q, q_end, next, Ws, tid);
+    store_bias_relu<4, false>(acc, w.fc2_b, Xs, kXStride, tid);
+  }
+  __syncthreads();
+  layer_norm_rows<kPcMid, !X3>(Xs, kXStride, Hs, kHStride, w.ln2_w, w.ln2_b, tid);   // :27
+  {  // Linear(128, n_components) + tanh   (:28, :107)
+    float acc[2][4][4];
+    zero_acc<4>(acc);
+    cta_gemm<4, X3>(acc, Hs, kHStride, kPcMid, q, q_end, next, Ws, tid);
+    const int w_id = tid >> 5, lane = tid & 31, g = lane >> 2, c = lane & 3;
+    const int wm = w_id >> 2, wn = w_id & 3;
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int col = wn * 32 + nt * 8 + 2 * c + e;
+        if (col < a.n_components) {
+          const float bb = __ldg(w.fc3_b + col);
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+              const long long row = row0 + 32 * wm + 16 * mt + g + 8 * hh;
+              if (row < a.M) {
+                const float z = acc[mt][nt][2 * hh + e] + bb;
+                // tanh(z) = 1 - 2 / (1 + e^{2z}); fp32 mode uses the library tanhf
+                a.out[row * a.n_components + col] =
+                    X3 ? tanhf(z) : 1.f - __fdividef(2.f, 1.f + __expf(2.f * z));
+              }
+            }
+        }
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------- weight packing
 // dst[n][k] = src[n][k] (rows >= rows_src are zero), optionally rounded to tf32
 __global__ void pack_matrix_kernel(const float* __restrict__ src, float* __restrict__ dst, int rows_src,
@@ -470,3 +576,99 @@ int launch_decoder(const asb_model* m, const float* rnn_out, float* out, int M, 
 }
 
 }  // namespace asb
+
+// ---- principal-components head: C ABI -------------------------------------------------------------
+struct asb_pc_head {
+  int n_components, precision;
+  void* arena;
+  PcWeights w;
+};
+
+extern "C" int asb_pc_head_create(const asb_pc_weights* src, int hidden, int n_components, int precision, void* stream,
+                                  asb_pc_head** out) {
+  using namespace asb;
+  if (!src || !out) return set_error(ASB_ERR_INVALID, "asb_pc_head_create: null argument");
+  *out = nullptr;
+  if (hidden != kH) return set_error(ASB_ERR_UNSUPPORTED, "asb_pc_head_create: hidden_size must be %d (got %d)", kH, hidden);
+  if (n_components < 1 || n_components > kPcOutPad)
+    return set_error(ASB_ERR_INVALID, "asb_pc_head_create: need 1 <= n_components <= %d (got %d)", kPcOutPad, n_components);
+  if (precision != ASB_PRECISION_FAST && precision != ASB_PRECISION_FP32)
+    return set_error(ASB_ERR_INVALID, "asb_pc_head_create: bad precision %d", precision);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t counts[14] = {size_t(kH) * 2 * kH, kH, kH, kH, size_t(kFc) * kH, kFc, kFc, kFc,
+                             size_t(kPcMid) * kFc, kPcMid, kPcMid, kPcMid, size_t(kPcOutPad) * kPcMid, kPcOutPad};
+  size_t off[15];
+  off[0] = 0;
+  for (int i = 0; i < 14; ++i) off[i + 1] = off[i] + (counts[i] + 63) / 64 * 64;
+  asb_pc_head* h = new (std::nothrow) asb_pc_head();
+  if (!h) return set_error(ASB_ERR_INVALID, "asb_pc_head_create: out of host memory");
+  cudaError_t e = cudaMalloc(&h->arena, off[14] * sizeof(float));
+  if (e != cudaSuccess) {
+    delete h;
+    return check_cuda(e, "asb_pc_head_create: cudaMalloc");
+  }
+  float* b = static_cast<float*>(h->arena);
+  PcWeights& w = h->w;
+  float** slots[14] = {&w.lin_w, &w.lin_b, &w.ln0_w, &w.ln0_b, &w.fc1_w, &w.fc1_b, &w.ln1_w, &w.ln1_b,
+                       &w.fc2_w, &w.fc2_b, &w.ln2_w, &w.ln2_b, &w.fc3_w, &w.fc3_b};
+  for (int i = 0; i < 14; ++i) *slots[i] = b + off[i];
+  h->n_components = n_components;
+  h->precision = precision;
+  const bool rnd = precision == ASB_PRECISION_FAST;
+  int rc = pack_matrix(src->lin_w, w.lin_w, kH, kH, 2 * kH, rnd, st);
+  if (!rc) rc = pack_vector(src->lin_b, nullptr, 0, w.lin_b, kH, kH, st);
+  if (!rc) rc = pack_vector(src->ln0_w, nullptr, 0, w.ln0_w, kH, kH, st);
+  if (!rc) rc = pack_vector(src->ln0_b, nullptr, 0, w.ln0_b, kH, kH, st);
+  if (!rc) rc = pack_matrix(src->fc1_w, w.fc1_w, kFc, kFc, kH, rnd, st);
+  if (!rc) rc = pack_vector(src->fc1_b, nullptr, 0, w.fc1_b, kFc, kFc, st);
+  if (!rc) rc = pack_vector(src->ln1_w, nullptr, 0, w.ln1_w, kFc, kFc, st);
+  if (!rc) rc = pack_vector(src->ln1_b, nullptr, 0, w.ln1_b, kFc, kFc, st);
+  if (!rc) rc = pack_matrix(src->fc2_w, w.fc2_w, kPcMid, kPcMid, kFc, rnd, st);
+  if (!rc) rc = pack_vector(src->fc2_b, nullptr, 0, w.fc2_b, kPcMid, kPcMid, st);
+  if (!rc) rc = pack_vector(src->ln2_w, nullptr, 0, w.ln2_w, kPcMid, kPcMid, st);
+  if (!rc) rc = pack_vector(src->ln2_b, nullptr, 0, w.ln2_b, kPcMid, kPcMid, st);
+  if (!rc) rc = pack_matrix(src->fc3_w, w.fc3_w, n_components, kPcOutPad, kPcMid, rnd, st);
+  if (!rc) rc = pack_vector(src->fc3_b, nullptr, 0, w.fc3_b, n_components, kPcOutPad, st);
+  if (!rc) rc = check_cuda(cudaStreamSynchronize(st), "asb_pc_head_create: packing kernels");
+  if (rc) {
+    cudaFree(h->arena);
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return ASB_OK;
+}
+
+extern "C" void asb_pc_head_destroy(asb_pc_head* h) {
+  if (!h) return;
+  cudaFree(h->arena);
+  delete h;
+}
+
+extern "C" int asb_pc_head_forward(asb_pc_head* h, const float* features, int64_t rows, float* out, void* stream) {
+  using namespace asb;
+  if (!h) return set_error(ASB_ERR_INVALID, "asb_pc_head_forward: null head");
+  if (rows < 0 || rows > 0x7fffffffLL) return set_error(ASB_ERR_INVALID, "asb_pc_head_forward: bad row count");
+  if (rows == 0) return ASB_OK;
+  if (!features || !out) return set_error(ASB_ERR_INVALID, "asb_pc_head_forward: null pointer");
+  if (reinterpret_cast<uintptr_t>(features) & 15)
+    return set_error(ASB_ERR_INVALID, "asb_pc_head_forward: features must be 16-byte aligned");
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(pc_head_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kDecoderSmem));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(pc_head_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kDecoderSmem));
+    if (e != cudaSuccess) return check_cuda(e, "pc_head_kernel smem attribute");
+    configured = true;
+  }
+  PcArgs a{features, out, rows, h->n_components, h->w};
+  const unsigned grid = unsigned((rows + kBM - 1) / kBM);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (h->precision == ASB_PRECISION_FP32)
+    pc_head_kernel<true><<<grid, kThreads, kDecoderSmem, st>>>(a);
+  else
+    pc_head_kernel<false><<<grid, kThreads, kDecoderSmem, st>>>(a);
+  ASB_CHECK_LAUNCH("pc_head_kernel");
+  return ASB_OK;
+}
+

@@ -170,9 +170,9 @@ extern "C" int asb_model_forward(asb_model* m, const int64_t* x, int T_in, const
   return asb_model_forward_resident(m, x, T_in, lengths_host, nullptr, B, out, workspace, workspace_bytes, stream);
 }
 
-extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host,
-                                          const int32_t* lengths_dev, int B, float* out, void* workspace,
-                                          size_t workspace_bytes, void* stream) {
+static int forward_impl(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host,
+                        const int32_t* lengths_dev, int B, float* out, void* workspace, size_t workspace_bytes,
+                        void* stream, bool hidden_only) {
   if (!m || !x || !lengths_host || !out) return set_error(ASB_ERR_INVALID, "asb_model_forward: null argument");
   if (B <= 0 || T_in <= 0) return set_error(ASB_ERR_INVALID, "asb_model_forward: empty batch");
   // pack_padded_sequence(enforce_sorted=True) semantics, models.py:136
@@ -189,6 +189,7 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
   Workspace ws = plan_workspace(m, workspace, B, T);
   if (!workspace || workspace_bytes < ws.bytes)
     return set_error(ASB_ERR_WORKSPACE, "asb_model_forward: workspace %zu B < required %zu B", workspace_bytes, ws.bytes);
+  if (hidden_only) ws.out1 = out;   // the second recurrent layer writes straight into the caller's buffer
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const long long M = (long long)B * T;
   if (M > 0x7fffffffLL / 64) return set_error(ASB_ERR_INVALID, "asb_model_forward: batch too large");
@@ -249,7 +250,9 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
     if ((rc = launch_recurrent_layer(m, 1, ws.gi, ws.lengths, ws.out1, B, T, st))) return rc;
   }
   mark(4);
-  if (m->decoder_impl == 1) {
+  if (hidden_only) {
+    // nothing: `out` already holds the recurrent output
+  } else if (m->decoder_impl == 1) {
     if ((rc = launch_decoder_umma(m, ws.out1, out, int(M), st))) return rc;
   } else {
     if ((rc = launch_decoder(m, ws.out1, out, int(M), st))) return rc;
@@ -257,6 +260,18 @@ extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_
   mark(5);
   if (prof) m->pending.push_back(ev);
   return ASB_OK;
+}
+
+extern "C" int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host,
+                                          const int32_t* lengths_dev, int B, float* out, void* workspace,
+                                          size_t workspace_bytes, void* stream) {
+  return forward_impl(m, x, T_in, lengths_host, lengths_dev, B, out, workspace, workspace_bytes, stream, false);
+}
+
+extern "C" int asb_model_forward_hidden(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host,
+                                        const int32_t* lengths_dev, int B, float* hidden, void* workspace,
+                                        size_t workspace_bytes, void* stream) {
+  return forward_impl(m, x, T_in, lengths_host, lengths_dev, B, hidden, workspace, workspace_bytes, stream, true);
 }
 
 // Decoder only: linear.0 + ReLU -> every predictor -> sigmoid on caller-supplied feature rows

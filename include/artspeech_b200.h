@@ -204,6 +204,35 @@ ASB_API int asb_model_forward_resident(asb_model* m, const int64_t* x, int T_in,
                                const int32_t* lengths_dev, int B, float* out, void* workspace,
                                size_t workspace_bytes, void* stream);
 
+/* The recurrent stack alone: embedding -> 2-layer bidirectional GRU/LSTM with packed-sequence
+ * semantics (models.py:135-138; principal_components/models/rnn.py:94-104): same arguments as
+ * asb_model_forward_resident, but `hidden` (B, T, 2*hidden) fp32 receives the padded recurrent output
+ * (zeros at t >= length) and the decoder is not run.  lengths_dev may be NULL. */
+ASB_API int asb_model_forward_hidden(asb_model* m, const int64_t* x, int T_in, const int32_t* lengths_host,
+                             const int32_t* lengths_dev, int B, float* hidden, void* workspace,
+                             size_t workspace_bytes, void* stream);
+
+/* Tail of PrincipalComponentsArtSpeech (phoneme_to_articulation/principal_components/models/rnn.py:
+ * 11-33, 70-79, 106-108): Linear(2H,H)+ReLU -> LayerNorm(H) -> Linear(H,256)+ReLU -> LayerNorm(256) ->
+ * Linear(256,128)+ReLU -> LayerNorm(128) -> Linear(128,n_components) -> tanh, fused in one kernel
+ * (64-frame tiles, activations in shared memory).  All pointers are device fp32, row-major like
+ * nn.Linear.weight. */
+typedef struct asb_pc_head asb_pc_head;
+typedef struct asb_pc_weights {
+  const float* lin_w; const float* lin_b;   /* (H, 2H), (H)        linear.0 */
+  const float* ln0_w; const float* ln0_b;   /* (H)                 predictor.linear.0 */
+  const float* fc1_w; const float* fc1_b;   /* (256, H), (256)     predictor.linear.1 */
+  const float* ln1_w; const float* ln1_b;   /* (256)               predictor.linear.3 */
+  const float* fc2_w; const float* fc2_b;   /* (128, 256), (128)   predictor.linear.4 */
+  const float* ln2_w; const float* ln2_b;   /* (128)               predictor.linear.6 */
+  const float* fc3_w; const float* fc3_b;   /* (n_components, 128), (n_components)  predictor.linear.7 */
+} asb_pc_weights;
+ASB_API int asb_pc_head_create(const asb_pc_weights* w, int hidden, int n_components, int precision, void* stream,
+                       asb_pc_head** out);
+ASB_API void asb_pc_head_destroy(asb_pc_head* h);
+/* features (rows, 2H) -> out (rows, n_components) */
+ASB_API int asb_pc_head_forward(asb_pc_head* h, const float* features, int64_t rows, float* out, void* stream);
+
 /* Decoder alone on caller-supplied feature rows: features (rows, 2*hidden) fp32 ->
  * out (rows, n_art, 2, n_samples) = sigmoid(stack(predictor_i(ReLU(linear.0(features))))),
  * models.py:140-145.  SimpleArtSpeech (models.py:53-96) runs through this entry: its features are

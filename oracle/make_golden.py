@@ -91,6 +91,26 @@ def golden_model_grad():
     print("model_grad:", len(keys), "parameters, |grad| total", out["abssums64"].sum())
 
 
+def golden_pc_model():
+    """PrincipalComponentsArtSpeech of the unmodified reference (class statements cut out with ast):
+    GRU and LSTM instances under seed 0, fp32 and fp64 outputs, per-key parameter sums."""
+    PC, RNNType = ref.principal_components_models()
+    x = synthetic.tokens(3, 12, 45, seed=3)
+    lengths = torch.tensor([12, 9, 5], dtype=torch.int32)
+    out = {}
+    for cell in ("GRU", "LSTM"):
+        torch.manual_seed(0)
+        net = PC(45, {"a": 4, "b": 5, "c": 3}, rnn=RNNType[cell]).eval()
+        sd = net.state_dict()
+        out[f"keys_{cell}"] = np.array(sorted(sd.keys()))
+        out[f"sums_{cell}"] = np.array([sd[k].double().sum().item() for k in sorted(sd.keys())])
+        with torch.no_grad():
+            out[f"out32_{cell}"] = net(x, lengths).numpy()
+            out[f"out64_{cell}"] = net.double()(x, lengths).numpy()
+    np.savez_compressed(os.path.join(GOLDEN, "pc_model.npz"), x=x.numpy(), lengths=lengths.numpy(), **out)
+    print("pc_model:", out["out32_GRU"].shape, float(np.abs(out["out32_GRU"]).max()))
+
+
 def golden_p2cp():
     pm = ref.p2a_metrics()
     tgt = synthetic.contours(24, 10, 50, seed=5)
@@ -287,6 +307,7 @@ if __name__ == "__main__":
     os.makedirs(GOLDEN, exist_ok=True)
     golden_model()
     golden_model_grad()
+    golden_pc_model()
     golden_p2cp()
     golden_tv()
     golden_sentence_metrics()

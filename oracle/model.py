@@ -203,3 +203,21 @@ def simple_artspeech_forward(sd, x, dtype=torch.float32):
     n_art = n_articulators_of(sd)
     out = torch.stack([predictor_forward(sd, i, lin, dtype) for i in range(n_art)], dim=2)   # :93-95
     return torch.sigmoid(out)                                                           # :97
+
+
+@torch.no_grad()
+def pc_artspeech_forward(sd, x, lengths, dtype=torch.float32, rnn="stock"):
+    """PrincipalComponentsArtSpeech.forward, principal_components/models/rnn.py:85-109 (predictor :11-33)."""
+    lengths = torch.as_tensor(lengths, dtype=torch.int64).cpu()
+    embed = F.embedding(x.cpu(), sd["embedding.weight"].to(dtype))                      # :94
+    rnn_out = _rnn_stock(sd, embed, lengths, dtype) if rnn == "stock" else \
+        _rnn_equations(sd, embed, lengths, dtype)[:, : int(lengths.max())]              # :95-104
+    g = lambda k: sd[k].to(dtype)
+    h = F.relu(F.linear(rnn_out, g("linear.0.weight"), g("linear.0.bias")))             # :106
+    p = "predictor.linear."
+    h = F.layer_norm(h, (h.shape[-1],), g(p + "0.weight"), g(p + "0.bias"), LN_EPS)     # :21
+    h = F.relu(F.linear(h, g(p + "1.weight"), g(p + "1.bias")))                         # :22-23
+    h = F.layer_norm(h, (h.shape[-1],), g(p + "3.weight"), g(p + "3.bias"), LN_EPS)     # :24
+    h = F.relu(F.linear(h, g(p + "4.weight"), g(p + "4.bias")))                         # :25-26
+    h = F.layer_norm(h, (h.shape[-1],), g(p + "6.weight"), g(p + "6.bias"), LN_EPS)     # :27
+    return torch.tanh(F.linear(h, g(p + "7.weight"), g(p + "7.bias")))                  # :28, :107

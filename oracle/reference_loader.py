@@ -186,3 +186,23 @@ def run_test():
                                             "upper-incisor"],
           "UPPER_INCISOR": "upper-incisor"}
     return _cut("phoneme_to_articulation/encoder_decoder/evaluation.py", "run_test", ns)
+
+
+def principal_components_models():
+    """reference ``PrincipalComponentsPredictor`` / ``PrincipalComponentsArtSpeech``
+    (phoneme_to_articulation/principal_components/models/rnn.py:11-109): the two class statements,
+    unmodified, with ``RNNType`` (phoneme_to_articulation/__init__.py:47-49) and
+    ``make_indices_dict`` (helpers.py:94-114) cut out of their own files the same way."""
+    from enum import Enum
+    from functools import reduce
+
+    import torch
+    import torch.nn as nn
+    from torch.nn.utils.rnn import pack_padded_sequence, pad_packed_sequence
+    rnn_type = _cut("phoneme_to_articulation/__init__.py", "RNNType", {"Enum": Enum, "nn": nn}, kind="class")
+    mid = _cut("helpers.py", "make_indices_dict", {})
+    ns = {"torch": torch, "nn": nn, "reduce": reduce, "pack_padded_sequence": pack_padded_sequence,
+          "pad_packed_sequence": pad_packed_sequence, "make_indices_dict": mid, "RNNType": rnn_type}
+    rel = "phoneme_to_articulation/principal_components/models/rnn.py"
+    _cut(rel, "PrincipalComponentsPredictor", ns, kind="class")
+    return _cut(rel, "PrincipalComponentsArtSpeech", ns, kind="class"), rnn_type

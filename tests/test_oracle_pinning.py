@@ -201,3 +201,23 @@ def test_oracle_gradient_matches_reference(golden_dir):
     assert np.allclose(abssums, g["abssums64"], rtol=1e-9, atol=1e-10)
     for k in ("linear.0.bias", "rnn.bias_hh_l0", "rnn.bias_ih_l1_reverse", "predictors.3.x_coords.bias"):
         assert np.allclose(sd[k].grad.numpy(), g["grad64:" + k], rtol=1e-9, atol=1e-11)
+
+
+@pytest.mark.parametrize("cell", ["GRU", "LSTM"])
+def test_pc_model_constructor_and_oracle_match_reference(golden_dir, cell):
+    """PrincipalComponentsArtSpeech (principal_components/models/rnn.py:36-109): the drop-in's
+    constructor draws the reference's initial weights under the same seed (same state_dict keys),
+    and the oracle restatement reproduces the reference's fp32 / fp64 outputs."""
+    from artspeech_b200 import principal_components as pc
+    g = np.load(os.path.join(golden_dir, "pc_model.npz"))
+    torch.manual_seed(0)
+    net = pc.PrincipalComponentsArtSpeech(45, {"a": 4, "b": 5, "c": 3}, rnn=cell)
+    sd = {k: v.detach() for k, v in net.state_dict().items()}
+    assert sorted(sd.keys()) == list(g[f"keys_{cell}"]) and net.latent_size == 12
+    sums = np.array([sd[k].double().sum().item() for k in sorted(sd.keys())])
+    assert np.array_equal(sums, g[f"sums_{cell}"])
+    x, L = torch.from_numpy(g["x"]), torch.from_numpy(g["lengths"])
+    out32 = omodel.pc_artspeech_forward(sd, x, L, torch.float32)
+    out64 = omodel.pc_artspeech_forward(sd, x, L, torch.float64, rnn="equations")
+    assert np.abs(out32.numpy() - g[f"out32_{cell}"]).max() <= 2e-6
+    assert np.abs(out64.numpy() - g[f"out64_{cell}"]).max() <= 1e-12
