@@ -73,9 +73,13 @@ class EuclideanDistance(nn.Module):
         self.reduction = getattr(torch, reduction, lambda x: x)
 
     def forward(self, outputs, targets):
-        dx = outputs[..., 0, :] - targets[..., 0, :]
-        dy = outputs[..., 1, :] - targets[..., 1, :]
-        return self.reduction(torch.sqrt(dx ** 2 + dy ** 2))
+        # the training criterion (train_phoneme_to_articulation.py:86): differentiable tensor ops, always
+        # evaluated on the CUDA device (CPU inputs are moved there and the result moved back)
+        dev = _lib.device_of(outputs, targets)
+        o, t = outputs.to(dev), targets.to(dev)
+        dx = o[..., 0, :] - t[..., 0, :]
+        dy = o[..., 1, :] - t[..., 1, :]
+        return self.reduction(torch.sqrt(dx ** 2 + dy ** 2)).to(outputs.device)
 
 
 def p2cp_distance(outputs, targets):
@@ -102,8 +106,11 @@ def euclidean_distance(outputs, targets):
 
 def pearsons_correlation(outputs, targets):
     """metrics.py:9-35, including its quirk (x target mean taken from the x outputs, :22).
-    Stays on the tensors' device; (bs, T, N, 2, D) -> x_corr, y_corr (bs, N, D)."""
+    (bs, T, N, 2, D) -> x_corr, y_corr (bs, N, D).  Tensor ops on the CUDA device (the per-sentence
+    form run_test needs is the kernel asb_eval_sentence_metrics)."""
     eps = 1e-5
+    dev, home = _lib.device_of(outputs, targets), outputs.device
+    outputs, targets = outputs.to(dev), targets.to(dev)     # evaluated on the CUDA device, returned where it came from
     xo, yo = outputs[:, :, :, 0, :], outputs[:, :, :, 1, :]
     xt, yt = targets[:, :, :, 0, :], targets[:, :, :, 1, :]
     vxo = xo - xo.mean(dim=1, keepdim=True)
@@ -112,7 +119,7 @@ def pearsons_correlation(outputs, targets):
     vyo = yo - yo.mean(dim=1, keepdim=True)
     vyt = yt - yt.mean(dim=1, keepdim=True)
     y_corr = (vyo * vyt).sum(1) / (torch.sqrt((vyo ** 2).sum(1)) * torch.sqrt((vyt ** 2).sum(1)) + eps)
-    return x_corr, y_corr
+    return x_corr.to(home), y_corr.to(home)
 
 
 class P2CPDistance(nn.Module):

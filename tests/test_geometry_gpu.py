@@ -175,3 +175,24 @@ def test_config3_full_size_p2cp_and_tv(asb):
     for t in (val, idx, poc):
         v = t.view(F // blk, blk, -1)
         assert torch.equal(v, v[:1].expand_as(v))
+
+
+def test_metric_helpers_accept_cpu_tensors_and_run_on_the_gpu(asb):
+    """pearsons_correlation (metrics.py:9-35, quirk of :22 included) and the EuclideanDistance criterion
+    (phoneme_to_articulation/metrics.py:5-24) on CPU inputs, as the reference's evaluation loop passes
+    them: computed on the CUDA device, returned on the CPU, equal to the fp64 oracle."""
+    from oracle import geometry as og
+    M, _ = asb
+    tgt = synthetic.contours(3 * 17, 4, 50, seed=51).view(3, 17, 4, 2, 50)
+    pred = synthetic.perturbed(tgt, seed=52)
+    xc, yc = M.pearsons_correlation(pred, tgt)
+    wx, wy = og.pearsons_correlation(pred, tgt)
+    assert xc.device.type == "cpu" and xc.shape == wx.shape
+    assert torch.allclose(xc.double(), wx, atol=2e-4) and torch.allclose(yc.double(), wy, atol=2e-4)
+    d = M.EuclideanDistance("none")(pred, tgt)
+    assert d.device.type == "cpu" and d.shape == (3, 17, 4, 50)
+    want = torch.sqrt(((pred.double() - tgt.double()) ** 2).sum(dim=-2))
+    assert torch.allclose(d.double(), want, rtol=1e-5, atol=1e-9)
+    p = pred.clone().cuda().requires_grad_(True)
+    M.EuclideanDistance("mean")(p, tgt.cuda()).backward()
+    assert p.grad is not None and torch.isfinite(p.grad).all()
