@@ -302,9 +302,21 @@ def golden_area():
     print("area: grids", grids["default"].shape, grids["rotated"].shape, "K", [len(out[f"fx_{f}"]) for f in range(3)])
 
 
-if __name__ == "__main__":
+def main(out_dir=None):
+    """Run every generator in ONE process, writing into ``out_dir`` (default tests/golden)."""
+    global GOLDEN
     assert ref.available(), "reference checkout not found"
+    keep = GOLDEN
+    if out_dir is not None:
+        GOLDEN = out_dir
     os.makedirs(GOLDEN, exist_ok=True)
+    try:
+        _run_all()
+    finally:
+        GOLDEN = keep
+
+
+def _run_all():
     golden_model()
     golden_model_grad()
     golden_pc_model()
@@ -315,3 +327,7 @@ if __name__ == "__main__":
     golden_run_test()
     golden_tv_driver()
     golden_critical_loss()
+
+
+if __name__ == "__main__":
+    main(sys.argv[1] if len(sys.argv) > 1 else None)

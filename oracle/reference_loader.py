@@ -45,6 +45,28 @@ def _stub_vt_tools():
     sys.modules["vt_tools"] = vt
 
 
+def _stub_vt_metrics():
+    """ONE ``vt_tools.metrics`` stub shared by every loader (the package is un-vendored): each loader
+    needs different names from it, so all of them are always present - ``p2cp_mean`` (imported and
+    unused by root metrics.py:4), ``euclidean`` = sqrt(dx^2 + dy^2) (its published definition; used by
+    area_function.py:128,139) and ``distance_matrix`` (used only next to GEOS calls, which cannot run
+    here).  Loaders may be called in any order in one process."""
+    import numpy as np
+    _stub_vt_tools()
+    vt = sys.modules["vt_tools"]
+    vm = sys.modules.get("vt_tools.metrics")
+    if vm is None:
+        vm = types.ModuleType("vt_tools.metrics")
+        sys.modules["vt_tools.metrics"] = vm
+    if getattr(vm, "euclidean", None) is None:
+        vm.euclidean = lambda u, v: np.sqrt((u[0] - v[0]) ** 2 + (u[1] - v[1]) ** 2)
+    for name in ("p2cp_mean", "distance_matrix"):
+        if not hasattr(vm, name):
+            setattr(vm, name, None)
+    vt.metrics = vm
+    return vm
+
+
 def models():
     """reference phoneme_to_articulation/encoder_decoder/models.py"""
     return _load("_ref_models", "phoneme_to_articulation/encoder_decoder/models.py")
@@ -60,12 +82,7 @@ def root_metrics():
     the un-vendored ``vt_tools.metrics.p2cp_mean`` (unused by these functions) and of the
     ``phoneme_to_articulation`` package (whose __init__ needs vt_tools / vt_shape_gen) are stubbed:
     the package stub only carries the real phoneme_to_articulation/metrics.py module."""
-    _stub_vt_tools()
-    if "vt_tools.metrics" not in sys.modules:
-        m = types.ModuleType("vt_tools.metrics")
-        m.p2cp_mean = None
-        m.euclidean = None
-        sys.modules["vt_tools.metrics"] = m
+    _stub_vt_metrics()
     if "phoneme_to_articulation" not in sys.modules:
         pkg = types.ModuleType("phoneme_to_articulation")
         pkg.__path__ = []
@@ -87,14 +104,7 @@ def area_function():
     area_function); ``vt_tools.metrics.euclidean`` = sqrt(dx^2 + dy^2) (its published definition,
     the package itself is un-vendored); ``np.float`` aliased to ``float`` for :130 (NumPy >= 1.24)."""
     import numpy as np
-    _stub_vt_tools()
-    vt = sys.modules["vt_tools"]
-    if "vt_tools.metrics" not in sys.modules:
-        vm = types.ModuleType("vt_tools.metrics")
-        vm.euclidean = lambda u, v: np.sqrt((u[0] - v[0]) ** 2 + (u[1] - v[1]) ** 2)
-        vm.distance_matrix = None  # only used next to GEOS calls, which cannot run here
-        vt.metrics = vm
-        sys.modules["vt_tools.metrics"] = vm
+    _stub_vt_metrics()
     if "funcy" not in sys.modules:
         fy = types.ModuleType("funcy")
         fy.lmap = lambda fn, seq: list(map(fn, seq))
