@@ -43,10 +43,18 @@ class AsbPcWeights(ctypes.Structure):
         "fc3_w", "fc3_b")]
 
 
+class AsbPredictorWeights(ctypes.Structure):
+    """Mirror of `struct asb_predictor_weights`."""
+    _fields_ = [(n, ctypes.c_void_p) for n in (
+        "ln0_w", "ln0_b", "fc1_w", "fc1_b", "ln1_w", "ln1_b", "fc2_w", "fc2_b", "ln2_w", "ln2_b",
+        "xh_w", "xh_b", "yh_w", "yh_b")]
+
+
 # name -> (restype, argtypes); every symbol include/artspeech_b200.h declares
 SIGNATURES = {
     "asb_abi_version": (ctypes.c_int, []),
     "asb_last_error_string": (ctypes.c_char_p, []),
+    "asb_build_hash": (ctypes.c_char_p, []),
     "asb_launch_count": (ctypes.c_int64, []),
     "asb_p2cp": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_int, ctypes.c_int,
                                 ctypes.c_int, ctypes.c_void_p]),
@@ -86,9 +94,18 @@ SIGNATURES = {
                                           ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]),
     "asb_pc_head_destroy": (None, [ctypes.c_void_p]),
     "asb_pc_head_forward": (ctypes.c_int, [ctypes.c_void_p, _c_f32p, ctypes.c_int64, _c_f32p, ctypes.c_void_p]),
+    "asb_predictor_create": (ctypes.c_int, [ctypes.POINTER(AsbPredictorWeights), ctypes.c_int, ctypes.c_int,
+                                            ctypes.c_int, ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]),
+    "asb_predictor_destroy": (None, [ctypes.c_void_p]),
+    "asb_predictor_forward": (ctypes.c_int, [ctypes.c_void_p, _c_f32p, ctypes.c_int64, _c_f32p, ctypes.c_void_p]),
     "asb_model_decode": (ctypes.c_int, [ctypes.c_void_p, _c_f32p, ctypes.c_int64, _c_f32p, ctypes.c_void_p]),
     "asb_gather_rows": (ctypes.c_int, [_c_f32p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_int,
                                        _c_f32p, ctypes.c_void_p]),
+    "asb_gather_rows_flagged": (ctypes.c_int, [_c_f32p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_int,
+                                               _c_f32p, ctypes.c_void_p, ctypes.c_void_p]),
+    "asb_model_token_status": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int32),
+                                              ctypes.POINTER(ctypes.c_int64), ctypes.c_int]),
+    "asb_model_token_flag_ptr": (ctypes.c_void_p, [ctypes.c_void_p]),
     "asb_model_set_decoder": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "asb_model_set_recurrent": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "asb_model_profile_enable": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
@@ -124,6 +141,12 @@ def lib():
             fn.argtypes = argtypes
         if handle.asb_abi_version() != 1:
             raise RuntimeError("libartspeech_b200.so ABI version mismatch; rebuild the library")
+        from . import build as _build
+        if _build.sources():   # the sources travel with the library: a stale prebuilt .so is refused
+            built, want = handle.asb_build_hash().decode(), _build.source_hash()
+            if built != want:
+                raise RuntimeError(f"{LIB_PATH} was built from other sources (hash {built}, sources {want}): "
+                                   "rebuild it with `python -m artspeech_b200.build`")
         _lib = handle
     return _lib
 

@@ -548,12 +548,13 @@ extern "C" int asb_area_function(const float* walls_int, const float* walls_ext,
   const long long cap = (long long)asb::sm_count() * 4;
   const unsigned blocks = (unsigned)(want < cap ? want : cap);
   const int raw_bytes = kWarps * 2 * kMaxWall * int(sizeof(float2));   // wall staging buffer (dynamic part)
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(area_function_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, raw_bytes);
-    if (e != cudaSuccess) return asb::check_cuda(e, "asb_area_function: smem attribute");
-    configured = true;
-  }
+  static asb::DeviceOnce once;
+  if (int rc = once.run([&] {
+        return asb::check_cuda(cudaFuncSetAttribute(area_function_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                    raw_bytes),
+                               "asb_area_function: smem attribute");
+      }))
+    return rc;
   area_function_kernel<<<blocks, kWarps * 32, raw_bytes, static_cast<cudaStream_t>(stream)>>>(a);
   ASB_CHECK_LAUNCH("area_function_kernel");
   return ASB_OK;

@@ -2,6 +2,7 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdint>
 #include <cstdio>
 
@@ -18,6 +19,21 @@ int set_error(int status, const char* fmt, ...);
 int check_cuda(cudaError_t e, const char* what);
 void count_launch(int n = 1);
 int sm_count();
+
+// cudaFuncSetAttribute is per DEVICE: one flag per (call site, device), so that a process driving
+// several GPUs opts every one of them in.  `fn` returns an asb status; it is retried until it succeeds.
+struct DeviceOnce {
+  std::atomic<int> done[64];
+  template <typename F>
+  int run(F&& fn) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return fn();
+    if (done[dev].load(std::memory_order_acquire)) return ASB_OK;
+    const int rc = fn();
+    if (rc == ASB_OK) done[dev].store(1, std::memory_order_release);
+    return rc;
+  }
+};
 
 #define ASB_CHECK_LAUNCH(what)                                  \
   do {                                                          \

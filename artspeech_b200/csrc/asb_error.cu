@@ -41,6 +41,10 @@ int sm_count() {
 
 }  // namespace asb
 
+#ifndef ASB_SOURCE_HASH
+#define ASB_SOURCE_HASH "unknown"
+#endif
 extern "C" int asb_abi_version(void) { return ASB_ABI_VERSION; }
+extern "C" const char* asb_build_hash(void) { return ASB_SOURCE_HASH; }
 extern "C" const char* asb_last_error_string(void) { return g_err; }
 extern "C" int64_t asb_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }

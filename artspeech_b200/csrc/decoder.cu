@@ -459,6 +459,137 @@ __global__ void __launch_bounds__(kThreads, 1) pc_head_kernel(const PcArgs a) {
   }
 }
 
+
+// ---------------------------------------------------------------- standalone ArticulatorPredictor
+// ArticulatorPredictor.forward (phoneme_to_articulation/encoder_decoder/models.py:23-33) on its own:
+// the class is also instantiated outside ArtSpeech (transformer heads, transformer/models.py:337-339,
+// with in_features = embed_dim).  LayerNorm(C) -> Linear(C,256) -> ReLU -> LayerNorm(256) ->
+// Linear(256,256) -> ReLU -> LayerNorm(256) -> x/y heads, stacked to (rows, 2, D); NO sigmoid (the
+// caller applies its own).  Same building blocks as decoder_kernel; C = in_features is a run-time
+// multiple of 32 up to 256.
+struct PredWeights {
+  float* ln0_w; float* ln0_b;    // [C]
+  float* fc1_w; float* fc1_b;    // [256][C], [256]
+  float* ln1_w; float* ln1_b;    // [256]
+  float* fc2_w; float* fc2_b;    // [256][256], [256]
+  float* ln2_w; float* ln2_b;    // [256]
+  float* head_w; float* head_b;  // [128 (2D rows, zero padded)][256], [128]
+};
+
+struct PredArgs {
+  const float* features;  // (M, C)
+  float* out;             // (M, 2, D)
+  long long M;
+  int C, D;
+  PredWeights w;
+};
+
+// LayerNorm over C = 32 * per columns (run-time), each warp normalises 8 rows
+template <bool ROUND>
+__device__ __forceinline__ void layer_norm_rows_rt(const float* src, int lds, float* dst, int ldd, int C,
+                                                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                   int tid) {
+  const int w = tid >> 5, lane = tid & 31;
+  const int per = C >> 5;
+  const float inv = 1.f / float(C);
+  for (int r = 0; r < 8; ++r) {
+    const int row = 8 * w + r;
+    float x[8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      x[i] = i < per ? src[row * lds + lane + 32 * i] : 0.f;
+      s += x[i];
+    }
+    const float mean = warp_sum(s) * inv;
+    float v = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      x[i] = i < per ? x[i] - mean : 0.f;
+      v = fmaf(x[i], x[i], v);
+    }
+    const float rstd = rsqrtf(warp_sum(v) * inv + 1e-5f);
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (i < per) {
+        float y = fmaf(x[i] * rstd, __ldg(gamma + lane + 32 * i), __ldg(beta + lane + 32 * i));
+        if (ROUND) y = round_tf32(y);
+        dst[row * ldd + lane + 32 * i] = y;
+      }
+  }
+}
+
+template <bool X3>
+__global__ void __launch_bounds__(kThreads, 1) predictor_kernel(const PredArgs a) {
+  extern __shared__ __align__(16) float smem[];
+  float* Hs = smem + kBM * kXStride;      // [64][264] (same carve-up as decoder_kernel; Xs unused)
+  float* Ws = Hs + kBM * kHStride;
+  const int tid = threadIdx.x;
+  const long long row0 = (long long)blockIdx.x * kBM;
+  const PredWeights& w = a.w;
+  const int C = a.C, q1 = C / kBK;
+  const int q_end = q1 + 8 + 8;
+
+  auto next = [&](int q) -> Chunk {
+    if (q < q1) return Chunk{w.fc1_w + q * kBK, kFc, C};
+    if (q < q1 + 8) return Chunk{w.fc2_w + (q - q1) * kBK, kFc, kFc};
+    return Chunk{w.head_w + (q - q1 - 8) * kBK, kHeadPad, kFc};
+  };
+
+  issue_chunk(next(0), Ws, tid);
+  for (int i = tid; i < kBM * (C / 4); i += kThreads) {   // raw fp32 rows: LayerNorm comes first
+    const int r = i / (C / 4), qq = i - r * (C / 4);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (row0 + r < a.M) v = __ldg(reinterpret_cast<const float4*>(a.features + (row0 + r) * C) + qq);
+    *reinterpret_cast<float4*>(Hs + r * kHStride + 4 * qq) = v;
+  }
+  __syncthreads();
+  layer_norm_rows_rt<!X3>(Hs, kHStride, Hs, kHStride, C, w.ln0_w, w.ln0_b, tid);      // models.py:11
+  int q = 0;
+  {  // Linear(C,256) + ReLU   (:12-13)
+    float acc[2][8][4];
+    zero_acc<8>(acc);
+    cta_gemm<8, X3>(acc, Hs, kHStride, C, q, q_end, next, Ws, tid);
+    __syncthreads();
+    store_bias_relu<8, false>(acc, w.fc1_b, Hs, kHStride, tid);
+  }
+  __syncthreads();
+  layer_norm_rows<kFc, !X3>(Hs, kHStride, Hs, kHStride, w.ln1_w, w.ln1_b, tid);        // :14
+  {  // Linear(256,256) + ReLU   (:15-16)
+    float acc[2][8][4];
+    zero_acc<8>(acc);
+    cta_gemm<8, X3>(acc, Hs, kHStride, kFc, q, q_end, next, Ws, tid);
+    __syncthreads();
+    store_bias_relu<8, false>(acc, w.fc2_b, Hs, kHStride, tid);
+  }
+  __syncthreads();
+  layer_norm_rows<kFc, !X3>(Hs, kHStride, Hs, kHStride, w.ln2_w, w.ln2_b, tid);        // :17
+  {  // x_coords / y_coords, stacked on dim 2   (:20-21,29-31)
+    float acc[2][4][4];
+    zero_acc<4>(acc);
+    cta_gemm<4, X3>(acc, Hs, kHStride, kFc, q, q_end, next, Ws, tid);
+    const int w_id = tid >> 5, lane = tid & 31, g = lane >> 2, c = lane & 3;
+    const int wm = w_id >> 2, wn = w_id & 3;
+    const int n_out = 2 * a.D;
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int col = wn * 32 + nt * 8 + 2 * c + e;
+        if (col < n_out) {
+          const float bb = __ldg(w.head_b + col);
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+              const long long row = row0 + 32 * wm + 16 * mt + g + 8 * hh;
+              if (row < a.M) a.out[row * n_out + col] = acc[mt][nt][2 * hh + e] + bb;
+            }
+        }
+      }
+  }
+}
+
 // ---------------------------------------------------------------- weight packing
 // dst[n][k] = src[n][k] (rows >= rows_src are zero), optionally rounded to tf32
 __global__ void pack_matrix_kernel(const float* __restrict__ src, float* __restrict__ dst, int rows_src,
@@ -538,14 +669,14 @@ int launch_linear(const asb_model* m, const float* A, const float* W, const floa
                   int K, cudaStream_t st) {
   if (K != 256 || N % 256 != 0) return set_error(ASB_ERR_UNSUPPORTED, "launch_linear: K must be 256 and N % 256 == 0");
   const size_t smem = (size_t(kBM) * kHStride + 2 * size_t(kWStage)) * sizeof(float);
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(linear256_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(linear256_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-    if (e != cudaSuccess) return check_cuda(e, "linear256_kernel smem attribute");
-    configured = true;
-  }
+  static DeviceOnce once;
+  if (int rc = once.run([&] {
+        cudaError_t e = cudaFuncSetAttribute(linear256_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        if (e == cudaSuccess)
+          e = cudaFuncSetAttribute(linear256_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        return check_cuda(e, "linear256_kernel smem attribute");
+      }))
+    return rc;
   LinearArgs a{A, W, bias, C, M, N};
   dim3 grid((M + kBM - 1) / kBM, N / 256);
   if (m->precision == ASB_PRECISION_FP32)
@@ -557,14 +688,14 @@ int launch_linear(const asb_model* m, const float* A, const float* W, const floa
 }
 
 int launch_decoder(const asb_model* m, const float* rnn_out, float* out, int M, cudaStream_t st) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(decoder_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kDecoderSmem));
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(decoder_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kDecoderSmem));
-    if (e != cudaSuccess) return check_cuda(e, "decoder_kernel smem attribute");
-    configured = true;
-  }
+  static DeviceOnce once;
+  if (int rc = once.run([&] {
+        cudaError_t e = cudaFuncSetAttribute(decoder_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kDecoderSmem));
+        if (e == cudaSuccess)
+          e = cudaFuncSetAttribute(decoder_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kDecoderSmem));
+        return check_cuda(e, "decoder_kernel smem attribute");
+      }))
+    return rc;
   DecoderArgs a{rnn_out, out, M, m->N, m->D, m->w};
   const unsigned grid = unsigned((M + kBM - 1) / kBM);
   if (m->precision == ASB_PRECISION_FP32)
@@ -653,14 +784,14 @@ extern "C" int asb_pc_head_forward(asb_pc_head* h, const float* features, int64_
   if (!features || !out) return set_error(ASB_ERR_INVALID, "asb_pc_head_forward: null pointer");
   if (reinterpret_cast<uintptr_t>(features) & 15)
     return set_error(ASB_ERR_INVALID, "asb_pc_head_forward: features must be 16-byte aligned");
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(pc_head_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kDecoderSmem));
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(pc_head_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kDecoderSmem));
-    if (e != cudaSuccess) return check_cuda(e, "pc_head_kernel smem attribute");
-    configured = true;
-  }
+  static DeviceOnce once;
+  if (int rc = once.run([&] {
+        cudaError_t e = cudaFuncSetAttribute(pc_head_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kDecoderSmem));
+        if (e == cudaSuccess)
+          e = cudaFuncSetAttribute(pc_head_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kDecoderSmem));
+        return check_cuda(e, "pc_head_kernel smem attribute");
+      }))
+    return rc;
   PcArgs a{features, out, rows, h->n_components, h->w};
   const unsigned grid = unsigned((rows + kBM - 1) / kBM);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -672,3 +803,99 @@ extern "C" int asb_pc_head_forward(asb_pc_head* h, const float* features, int64_
   return ASB_OK;
 }
 
+// ---- standalone ArticulatorPredictor: C ABI ---------------------------------------------------------
+struct asb_predictor {
+  int C, D, precision;
+  void* arena;
+  PredWeights w;
+};
+
+extern "C" int asb_predictor_create(const asb_predictor_weights* src, int in_features, int n_samples, int precision,
+                                    void* stream, asb_predictor** out) {
+  using namespace asb;
+  if (!src || !out) return set_error(ASB_ERR_INVALID, "asb_predictor_create: null argument");
+  *out = nullptr;
+  if (in_features < 32 || in_features > 256 || (in_features & 31))
+    return set_error(ASB_ERR_UNSUPPORTED, "asb_predictor_create: in_features must be a multiple of 32 in [32, 256] (got %d)",
+                     in_features);
+  if (n_samples < 1 || 2 * n_samples > kHeadPad)
+    return set_error(ASB_ERR_INVALID, "asb_predictor_create: need 1 <= n_samples <= %d (got %d)", kHeadPad / 2, n_samples);
+  if (precision != ASB_PRECISION_FAST && precision != ASB_PRECISION_FP32)
+    return set_error(ASB_ERR_INVALID, "asb_predictor_create: bad precision %d", precision);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int C = in_features, D = n_samples;
+  const size_t counts[12] = {size_t(C), size_t(C), size_t(kFc) * C, kFc, kFc, kFc, size_t(kFc) * kFc, kFc, kFc, kFc,
+                             size_t(kHeadPad) * kFc, kHeadPad};
+  size_t off[13];
+  off[0] = 0;
+  for (int i = 0; i < 12; ++i) off[i + 1] = off[i] + (counts[i] + 63) / 64 * 64;
+  asb_predictor* h = new (std::nothrow) asb_predictor();
+  if (!h) return set_error(ASB_ERR_INVALID, "asb_predictor_create: out of host memory");
+  cudaError_t e = cudaMalloc(&h->arena, off[12] * sizeof(float));
+  if (e != cudaSuccess) {
+    delete h;
+    return check_cuda(e, "asb_predictor_create: cudaMalloc");
+  }
+  float* b = static_cast<float*>(h->arena);
+  PredWeights& w = h->w;
+  float** slots[12] = {&w.ln0_w, &w.ln0_b, &w.fc1_w, &w.fc1_b, &w.ln1_w, &w.ln1_b, &w.fc2_w, &w.fc2_b,
+                       &w.ln2_w, &w.ln2_b, &w.head_w, &w.head_b};
+  for (int i = 0; i < 12; ++i) *slots[i] = b + off[i];
+  h->C = C; h->D = D; h->precision = precision;
+  const bool rnd = precision == ASB_PRECISION_FAST;
+  int rc = pack_vector(src->ln0_w, nullptr, 0, w.ln0_w, C, C, st);
+  if (!rc) rc = pack_vector(src->ln0_b, nullptr, 0, w.ln0_b, C, C, st);
+  if (!rc) rc = pack_matrix(src->fc1_w, w.fc1_w, kFc, kFc, C, rnd, st);
+  if (!rc) rc = pack_vector(src->fc1_b, nullptr, 0, w.fc1_b, kFc, kFc, st);
+  if (!rc) rc = pack_vector(src->ln1_w, nullptr, 0, w.ln1_w, kFc, kFc, st);
+  if (!rc) rc = pack_vector(src->ln1_b, nullptr, 0, w.ln1_b, kFc, kFc, st);
+  if (!rc) rc = pack_matrix(src->fc2_w, w.fc2_w, kFc, kFc, kFc, rnd, st);
+  if (!rc) rc = pack_vector(src->fc2_b, nullptr, 0, w.fc2_b, kFc, kFc, st);
+  if (!rc) rc = pack_vector(src->ln2_w, nullptr, 0, w.ln2_w, kFc, kFc, st);
+  if (!rc) rc = pack_vector(src->ln2_b, nullptr, 0, w.ln2_b, kFc, kFc, st);
+  if (!rc) rc = pack_matrix(src->xh_w, w.head_w, D, D, kFc, rnd, st);
+  if (!rc) rc = pack_matrix(src->yh_w, w.head_w + (size_t)D * kFc, D, kHeadPad - D, kFc, rnd, st);
+  if (!rc) rc = pack_vector(src->xh_b, nullptr, 0, w.head_b, D, D, st);
+  if (!rc) rc = pack_vector(src->yh_b, nullptr, 0, w.head_b + D, D, kHeadPad - D, st);
+  if (!rc) rc = check_cuda(cudaStreamSynchronize(st), "asb_predictor_create: packing kernels");
+  if (rc) {
+    cudaFree(h->arena);
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return ASB_OK;
+}
+
+extern "C" void asb_predictor_destroy(asb_predictor* h) {
+  if (!h) return;
+  cudaFree(h->arena);
+  delete h;
+}
+
+extern "C" int asb_predictor_forward(asb_predictor* h, const float* features, int64_t rows, float* out, void* stream) {
+  using namespace asb;
+  if (!h) return set_error(ASB_ERR_INVALID, "asb_predictor_forward: null predictor");
+  if (rows < 0 || rows > 0x7fffffffLL) return set_error(ASB_ERR_INVALID, "asb_predictor_forward: bad row count");
+  if (rows == 0) return ASB_OK;
+  if (!features || !out) return set_error(ASB_ERR_INVALID, "asb_predictor_forward: null pointer");
+  if (reinterpret_cast<uintptr_t>(features) & 15)
+    return set_error(ASB_ERR_INVALID, "asb_predictor_forward: features must be 16-byte aligned");
+  static DeviceOnce once;
+  if (int rc = once.run([&] {
+        cudaError_t e = cudaFuncSetAttribute(predictor_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kDecoderSmem));
+        if (e == cudaSuccess)
+          e = cudaFuncSetAttribute(predictor_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kDecoderSmem));
+        return check_cuda(e, "predictor_kernel smem attribute");
+      }))
+    return rc;
+  PredArgs a{features, out, rows, h->C, h->D, h->w};
+  const unsigned grid = unsigned((rows + kBM - 1) / kBM);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (h->precision == ASB_PRECISION_FP32)
+    predictor_kernel<true><<<grid, kThreads, kDecoderSmem, st>>>(a);
+  else
+    predictor_kernel<false><<<grid, kThreads, kDecoderSmem, st>>>(a);
+  ASB_CHECK_LAUNCH("predictor_kernel");
+  return ASB_OK;
+}

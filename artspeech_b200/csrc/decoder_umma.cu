@@ -709,12 +709,12 @@ int pack_umma_image(asb_model* m, const asb_weights* s, cudaStream_t st) {
 }
 
 int launch_decoder_umma(const asb_model* m, const float* rnn_out, float* out, int M, cudaStream_t st) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(decoder_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-    if (e != cudaSuccess) return check_cuda(e, "decoder_umma_kernel smem attribute");
-    configured = true;
-  }
+  static DeviceOnce once;
+  if (int rc = once.run([&] {
+        return check_cuda(cudaFuncSetAttribute(decoder_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes),
+                          "decoder_umma_kernel smem attribute");
+      }))
+    return rc;
   const int sms = sm_count();
   const int n_tiles = (M + kTileM - 1) / kTileM;
   UmmaArgs a;

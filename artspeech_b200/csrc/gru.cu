@@ -50,10 +50,10 @@ __global__ void pack_whh_frag_kernel(const float* __restrict__ whh, uint32_t* __
   frag[i] = uint32_t(__bfloat16_as_ushort(lo)) | (uint32_t(__bfloat16_as_ushort(hi)) << 16);
 }
 
-__global__ void transpose_whh_kernel(const float* __restrict__ whh, float* __restrict__ wt) {
+__global__ void transpose_whh_kernel(const float* __restrict__ whh, float* __restrict__ wt, int GH) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;  // over [k][row]
-  if (i >= kH * kGH) return;
-  const int k = i / kGH, row = i - k * kGH;
+  if (i >= kH * GH) return;
+  const int k = i / GH, row = i - k * GH;
   wt[i] = whh[row * kH + k];
 }
 
@@ -79,7 +79,7 @@ __global__ void copy_slice_kernel(const float* __restrict__ src, float* __restri
 
 // gi[(b*T + t)][dir][:] = tab0[dir][x[b][t]][:]   (one float4 per thread)
 __global__ void gather_gi0_kernel(const float* __restrict__ tab, const long long* __restrict__ x, int T_in,
-                                  float* __restrict__ gi, int B, int T, int V, int GH) {
+                                  float* __restrict__ gi, int B, int T, int V, int GH, int* __restrict__ tok_flag) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long total = (long long)B * T * 2 * (GH / 4);
   if (i >= total) return;
@@ -89,7 +89,13 @@ __global__ void gather_gi0_kernel(const float* __restrict__ tab, const long long
   const long long bt = rest >> 1;
   const int b = int(bt / T), t = int(bt - (long long)b * T);
   long long tok = x[(long long)b * T_in + t];
-  tok = tok < 0 ? 0 : (tok >= V ? V - 1 : tok);
+  if (tok < 0 || tok >= V) {   // nn.Embedding raises here; report it (model.cuh), then clamp
+    if (q == 0 && dir == 0) {
+      tok_flag[1] = int(tok);
+      tok_flag[0] = 1;
+    }
+    tok = tok < 0 ? 0 : V - 1;
+  }
   const float4 val = __ldg(reinterpret_cast<const float4*>(tab + ((long long)dir * V + tok) * GH) + q);
   reinterpret_cast<float4*>(gi)[i] = val;
 }
@@ -282,6 +288,92 @@ gru_fp32_kernel(const float* __restrict__ wt_fwd, const float* __restrict__ wt_b
   }
 }
 
+// ---------------------------------------------------------------- LSTM in fp32 (RNNType.LSTM,
+// phoneme_to_articulation/__init__.py:47-49; used by principal_components/models/rnn.py:58-68)
+// nn.LSTM cell, gate rows i, f, g, o:  i = s(.), f = s(.), g = tanh(.), o = s(.), c' = f c + i g,
+// h' = o tanh(c'); gi already holds W_ih x + b_ih + b_hh.  W_hh^T is 256 KB in fp32 - more than one
+// CTA's shared memory - so the columns of gates i, f, g (192 KB) live in shared memory and the column of
+// gate o of the thread's own hidden unit lives in 128 REGISTERS for the whole sequence.  Same
+// packed-sequence semantics and thread mapping as gru_fp32_kernel (thread = hidden unit x 4 batch rows).
+constexpr int kLG = 4, kLGH = kLG * kH;   // 512
+
+__global__ void __launch_bounds__(256, 1)
+lstm_fp32_kernel(const float* __restrict__ wt_fwd, const float* __restrict__ wt_bwd, const float* __restrict__ gi,
+                 const int* __restrict__ lengths, float* __restrict__ out, int B, int T) {
+  extern __shared__ __align__(16) float smem[];
+  float* W = smem;                  // [k][384]: gates i, f, g
+  float* hsm = smem + kH * kGH;     // [2][8][128]
+  const int tid = threadIdx.x, u = tid & (kH - 1), half = tid >> 7;
+  const int dir = blockIdx.y, b0 = blockIdx.x * 8;
+  const float* wt = dir ? wt_bwd : wt_fwd;   // [k][512]
+  for (int i = tid; i < kH * (kGH / 4); i += 256) {
+    const int k = i / (kGH / 4), q = i - k * (kGH / 4);
+    reinterpret_cast<float4*>(W)[i] = __ldg(reinterpret_cast<const float4*>(wt + (size_t)k * kLGH) + q);
+  }
+  float wo[kH];
+#pragma unroll
+  for (int k = 0; k < kH; ++k) wo[k] = __ldg(wt + (size_t)k * kLGH + 3 * kH + u);
+  for (int i = tid; i < 2 * 8 * kH; i += 256) hsm[i] = 0.f;
+  int len[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int b = b0 + 4 * half + r;
+    len[r] = b < B ? lengths[b] : 0;
+  }
+  const int Lmax = lengths[b0];
+  float h[4] = {0.f, 0.f, 0.f, 0.f}, c[4] = {0.f, 0.f, 0.f, 0.f};
+  __syncthreads();
+  int cur = 0;
+  for (int s = 0; s < Lmax; ++s) {
+    const int t = dir ? Lmax - 1 - s : s;
+    float ai[4], af[4], ag[4], ao[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      if (t < len[r]) {
+        const float* p = gi + (((long long)(b0 + 4 * half + r) * T + t) * 2 + dir) * kLGH + u;
+        ai[r] = __ldg(p); af[r] = __ldg(p + kH); ag[r] = __ldg(p + 2 * kH); ao[r] = __ldg(p + 3 * kH);
+      } else {
+        ai[r] = af[r] = ag[r] = ao[r] = 0.f;
+      }
+    }
+    const float* hc = hsm + cur * 8 * kH + 4 * half * kH;
+#pragma unroll
+    for (int k = 0; k < kH; k += 4) {
+      float4 hv[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) hv[r] = *reinterpret_cast<const float4*>(hc + r * kH + k);
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        const float wi = W[(k + kk) * kGH + u], wf = W[(k + kk) * kGH + kH + u], wg = W[(k + kk) * kGH + 2 * kH + u];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float hk = kk == 0 ? hv[r].x : kk == 1 ? hv[r].y : kk == 2 ? hv[r].z : hv[r].w;
+          ai[r] = fmaf(wi, hk, ai[r]);
+          af[r] = fmaf(wf, hk, af[r]);
+          ag[r] = fmaf(wg, hk, ag[r]);
+          ao[r] = fmaf(wo[k + kk], hk, ao[r]);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const float ig = 1.f / (1.f + expf(-ai[r]));
+      const float fg = 1.f / (1.f + expf(-af[r]));
+      const float gg = tanhf(ag[r]);
+      const float og = 1.f / (1.f + expf(-ao[r]));
+      const float cn = fg * c[r] + ig * gg;
+      const float hn = og * tanhf(cn);
+      const bool valid = t < len[r];
+      c[r] = valid ? cn : c[r];
+      h[r] = valid ? hn : h[r];
+      hsm[(cur ^ 1) * 8 * kH + (4 * half + r) * kH + u] = h[r];
+      if (valid) out[((long long)(b0 + 4 * half + r) * T + t) * (2 * kH) + dir * kH + u] = h[r];
+    }
+    __syncthreads();
+    cur ^= 1;
+  }
+}
+
 }  // namespace
 
 namespace asb {
@@ -290,7 +382,7 @@ int launch_gather_gi0(const asb_model* m, const long long* x, int T_in, float* g
   const int GH = m->G * kH;
   const long long total = (long long)B * T * 2 * (GH / 4);
   const long long blocks = (total + 255) / 256;
-  gather_gi0_kernel<<<unsigned(blocks), 256, 0, st>>>(m->w.tab0, x, T_in, gi, B, T, m->V, GH);
+  gather_gi0_kernel<<<unsigned(blocks), 256, 0, st>>>(m->w.tab0, x, T_in, gi, B, T, m->V, GH, m->tok_flag_dev);
   ASB_CHECK_LAUNCH("gather_gi0_kernel");
   return ASB_OK;
 }
@@ -298,16 +390,29 @@ int launch_gather_gi0(const asb_model* m, const long long* x, int T_in, float* g
 int launch_recurrent_layer(const asb_model* m, int layer, const float* gi, const int* lengths, float* out, int B,
                            int T, cudaStream_t st) {
   const PackedWeights& w = m->w;
-  if (m->G != kG)
-    return set_error(ASB_ERR_UNSUPPORTED, "the mma.sync / fp32 recurrent kernels implement the GRU cell only");
-  if (m->precision == ASB_PRECISION_FP32) {
-    static bool configured = false;
+  if (m->G == kLG && m->precision == ASB_PRECISION_FP32) {
+    static DeviceOnce once;
     const int smem = (kH * kGH + 2 * 8 * kH) * int(sizeof(float));
-    if (!configured) {
-      cudaError_t e = cudaFuncSetAttribute(gru_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-      if (e != cudaSuccess) return check_cuda(e, "gru_fp32_kernel smem attribute");
-      configured = true;
-    }
+    if (int rc = once.run([&] {
+          return check_cuda(cudaFuncSetAttribute(lstm_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
+                            "lstm_fp32_kernel smem attribute");
+        }))
+      return rc;
+    dim3 grid((B + 7) / 8, 2);
+    lstm_fp32_kernel<<<grid, 256, smem, st>>>(w.whh_t[layer][0], w.whh_t[layer][1], gi, lengths, out, B, T);
+    ASB_CHECK_LAUNCH("lstm_fp32_kernel");
+    return ASB_OK;
+  }
+  if (m->G != kG)
+    return set_error(ASB_ERR_UNSUPPORTED, "the mma.sync recurrent kernel implements the GRU cell only");
+  if (m->precision == ASB_PRECISION_FP32) {
+    static DeviceOnce once;
+    const int smem = (kH * kGH + 2 * 8 * kH) * int(sizeof(float));
+    if (int rc = once.run([&] {
+          return check_cuda(cudaFuncSetAttribute(gru_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
+                            "gru_fp32_kernel smem attribute");
+        }))
+      return rc;
     dim3 grid((B + 7) / 8, 2);
     gru_fp32_kernel<<<grid, 256, smem, st>>>(w.whh_t[layer][0], w.whh_t[layer][1], w.bhh_n[layer][0],
                                               w.bhh_n[layer][1], gi, lengths, out, B, T);
@@ -339,13 +444,22 @@ int pack_recurrent_weights(asb_model* m, const asb_weights* src, cudaStream_t st
                                                         GH, m->G == kG ? 2 * kH : GH);
     ASB_CHECK_LAUNCH("build_tab0_kernel");
   }
-  if (m->G != kG) return ASB_OK;  // LSTM: only the tcgen05 kernel (gru_umma.cu) has it; b_hh is folded entirely
+  if (m->G != kG) {
+    // LSTM: b_hh is folded entirely; fast precision runs the tcgen05 kernel (gru_umma.cu), fp32 precision
+    // lstm_fp32_kernel on W_hh^T
+    for (int layer = 0; layer < 2; ++layer)
+      for (int dir = 0; dir < 2; ++dir) {
+        transpose_whh_kernel<<<(kH * kLGH + 255) / 256, 256, 0, st>>>(src->rnn_w_hh[layer][dir], w.whh_t[layer][dir], kLGH);
+        ASB_CHECK_LAUNCH("transpose_whh_kernel");
+      }
+    return ASB_OK;
+  }
   for (int layer = 0; layer < 2; ++layer)
     for (int dir = 0; dir < 2; ++dir) {
       const int nf = 8 * kG * 8 * 32 * 4;
       pack_whh_frag_kernel<<<(nf + 255) / 256, 256, 0, st>>>(src->rnn_w_hh[layer][dir], w.whh_frag[layer][dir]);
       ASB_CHECK_LAUNCH("pack_whh_frag_kernel");
-      transpose_whh_kernel<<<(kH * kGH + 255) / 256, 256, 0, st>>>(src->rnn_w_hh[layer][dir], w.whh_t[layer][dir]);
+      transpose_whh_kernel<<<(kH * kGH + 255) / 256, 256, 0, st>>>(src->rnn_w_hh[layer][dir], w.whh_t[layer][dir], kGH);
       ASB_CHECK_LAUNCH("transpose_whh_kernel");
       copy_slice_kernel<<<1, kH, 0, st>>>(src->rnn_b_hh[layer][dir] + 2 * kH, w.bhh_n[layer][dir], kH);
       ASB_CHECK_LAUNCH("copy_slice_kernel");

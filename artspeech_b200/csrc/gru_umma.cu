@@ -88,6 +88,7 @@ struct RnnArgs {
   const long long* tokens;       //   (B, T_in) token ids and
   const float* tab;              //   tab0[dir][token][G*H] = embedding . W_ih_l0^T + folded biases (model.cuh)
   int T_in, V;
+  int* tok_flag;                 // {1, id} is stored here when a token id is outside [0, V) (model.cuh)
   const int* lengths;            // (B) sorted descending
   float* out;                    // (B, T, 2H); every element is written (zeros at t >= length)
   int B, T;
@@ -124,7 +125,12 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
     for (int i = tid; i < 2 * CPT * a.T; i += kThreads) {
       const int row = i / a.T, t = i - row * a.T;
       long long tok = (b0 + row < a.B) ? a.tokens[(long long)(b0 + row) * a.T_in + t] : 0;
-      Toks[i] = int(tok < 0 ? 0 : (tok >= a.V ? a.V - 1 : tok));
+      if (tok < 0 || tok >= a.V) {   // nn.Embedding raises here; report it, then clamp to stay in bounds
+        a.tok_flag[1] = int(tok);
+        a.tok_flag[0] = 1;
+        tok = tok < 0 ? 0 : a.V - 1;
+      }
+      Toks[i] = int(tok);
     }
   }
   fence_proxy_async();
@@ -331,26 +337,34 @@ int pack_whh_umma(asb_model* m, const asb_weights* src, cudaStream_t st) {
 
 constexpr int kMaxTokenBytes = 64 * 1024;   // token ids staged per CTA (16 rows x 1024 steps)
 
+// Batch rows per warp column: the fewest rows per CTA that still fit one wave of the machine (the
+// gate math bounds a step).  -DASB_RNN_CPT=2|4|8 pins it for experiments (tools/rnn_variants.py).
+static int rows_per_column(int B) {
+#ifdef ASB_RNN_CPT
+  return ASB_RNN_CPT;
+#else
+  const int sms = sm_count();
+  return (2 * ((B + 3) / 4) <= sms) ? 2 : (2 * ((B + 7) / 8) <= sms) ? 4 : 8;
+#endif
+}
+
 template <int G>
 static int launch_rnn_umma_g(const asb_model* m, RnnArgs& a, int B, bool use_tokens, cudaStream_t st) {
-  const int sms = sm_count();
-  // fewest rows per CTA that still fit one wave of the machine (the gate math bounds a step)
-  int cpt = (2 * ((B + 3) / 4) <= sms) ? 2 : (2 * ((B + 7) / 8) <= sms) ? 4 : 8;
-  if (const char* e = getenv("ASB_RNN_CPT")) cpt = atoi(e) == 8 ? 8 : (atoi(e) == 4 ? 4 : (atoi(e) == 2 ? 2 : cpt));   // experiment knob
+  const int cpt = rows_per_column(B);
   const int tok_bytes = 2 * cpt * a.T * 4;
   if (!use_tokens || tok_bytes > kMaxTokenBytes) a.tokens = nullptr;   // the caller materialised gi instead
   const int smem = kHsBytes + 64 + 1024 + kGiSlots * cpt * G * 1024 + (a.tokens ? tok_bytes : 0);
-  static bool configured = false;
-  if (!configured) {
-    const int max_smem = kHsBytes + 64 + 1024 + kGiSlots * 8 * G * 1024 + kMaxTokenBytes;
-    cudaError_t e = cudaFuncSetAttribute(rnn_umma_kernel<G, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(rnn_umma_kernel<G, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(rnn_umma_kernel<G, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-    if (e != cudaSuccess) return check_cuda(e, "rnn_umma_kernel smem attribute");
-    configured = true;
-  }
+  static DeviceOnce once;   // one instance per G (function template)
+  if (int rc = once.run([&] {
+        const int max_smem = kHsBytes + 64 + 1024 + kGiSlots * 8 * G * 1024 + kMaxTokenBytes;
+        cudaError_t e = cudaFuncSetAttribute(rnn_umma_kernel<G, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess)
+          e = cudaFuncSetAttribute(rnn_umma_kernel<G, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess)
+          e = cudaFuncSetAttribute(rnn_umma_kernel<G, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        return check_cuda(e, "rnn_umma_kernel smem attribute");
+      }))
+    return rc;
   if (cpt == 2) {
     rnn_umma_kernel<G, 2><<<dim3((B + 3) / 4, 2), kThreads, smem, st>>>(a);
   } else if (cpt == 4) {
@@ -364,9 +378,7 @@ static int launch_rnn_umma_g(const asb_model* m, RnnArgs& a, int B, bool use_tok
 
 // layer 0 may read its input pre-activations through the token table instead of a materialised gi
 bool rnn_umma_reads_tokens(const asb_model* m, int B, int T) {
-  const int sms = sm_count();
-  int cpt = (2 * ((B + 3) / 4) <= sms) ? 2 : (2 * ((B + 7) / 8) <= sms) ? 4 : 8;
-  if (const char* e = getenv("ASB_RNN_CPT")) cpt = atoi(e) == 8 ? 8 : (atoi(e) == 4 ? 4 : (atoi(e) == 2 ? 2 : cpt));
+  const int cpt = rows_per_column(B);
   return rnn_umma_supported(m) && 2 * cpt * T * 4 <= kMaxTokenBytes;
 }
 
@@ -378,7 +390,7 @@ int launch_rnn_umma(const asb_model* m, int layer, const float* gi, const long l
     a.bhhn[d] = m->w.bhh_n[layer][d];
   }
   a.gi = gi; a.lengths = lengths; a.out = out; a.B = B; a.T = T;
-  a.tokens = tokens; a.tab = m->w.tab0; a.T_in = T_in; a.V = m->V;
+  a.tokens = tokens; a.tab = m->w.tab0; a.T_in = T_in; a.V = m->V; a.tok_flag = m->tok_flag_dev;
   const bool use_tokens = tokens != nullptr && layer == 0;
   return m->G == 3 ? launch_rnn_umma_g<3>(m, a, B, use_tokens, st) : launch_rnn_umma_g<4>(m, a, B, use_tokens, st);
 }

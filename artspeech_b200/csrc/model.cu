@@ -59,8 +59,6 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   if (hidden != kH) return set_error(ASB_ERR_UNSUPPORTED, "asb_model_create: hidden_size must be %d (got %d)", kH, hidden);
   if (cell != ASB_CELL_GRU && cell != ASB_CELL_LSTM)
     return set_error(ASB_ERR_INVALID, "asb_model_create: cell must be ASB_CELL_GRU or ASB_CELL_LSTM");
-  if (cell == ASB_CELL_LSTM && precision != ASB_PRECISION_FAST)
-    return set_error(ASB_ERR_UNSUPPORTED, "asb_model_create: the LSTM cell exists in fast precision only (tcgen05 recurrent kernel)");
   if (vocab <= 0 || n_art <= 0 || embed_dim <= 0 || n_samples <= 0 || 2 * n_samples > kHeadPad)
     return set_error(ASB_ERR_INVALID, "asb_model_create: bad sizes (vocab %d, n_art %d, embed %d, n_samples %d <= %d)",
                      vocab, n_art, embed_dim, n_samples, kHeadPad / 2);
@@ -110,6 +108,17 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
     return check_cuda(e, "asb_model_create: cudaMalloc of the weight arena");
   }
   m->arena_bytes = p.total;
+  e = cudaHostAlloc(reinterpret_cast<void**>(&m->tok_flag_host), 2 * sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable);
+  if (e == cudaSuccess) {
+    m->tok_flag_host[0] = m->tok_flag_host[1] = 0;
+    e = cudaHostGetDevicePointer(reinterpret_cast<void**>(&m->tok_flag_dev), m->tok_flag_host, 0);
+  }
+  if (e != cudaSuccess) {
+    if (m->tok_flag_host) cudaFreeHost(m->tok_flag_host);
+    cudaFree(m->arena);
+    delete m;
+    return check_cuda(e, "asb_model_create: mapped token-status word");
+  }
   char* b = static_cast<char*>(m->arena);
   auto F = [&](size_t off) { return reinterpret_cast<float*>(b + off); };
   PackedWeights& w = m->w;
@@ -142,6 +151,7 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   if (!rc && rnnu) rc = pack_whh_umma(m, src, st);
   if (!rc) rc = check_cuda(cudaStreamSynchronize(st), "asb_model_create: packing kernels");
   if (rc) {
+    cudaFreeHost(m->tok_flag_host);
     cudaFree(m->arena);
     delete m;
     return rc;
@@ -156,9 +166,21 @@ extern "C" void asb_model_destroy(asb_model* m) {
     for (auto e : set) cudaEventDestroy(e);
   for (auto& set : m->free_sets)
     for (auto e : set) cudaEventDestroy(e);
+  if (m->tok_flag_host) cudaFreeHost(m->tok_flag_host);
   cudaFree(m->arena);
   delete m;
 }
+
+extern "C" int asb_model_token_status(asb_model* m, int32_t* bad_out, int64_t* token_out, int reset) {
+  if (!m || !bad_out) return set_error(ASB_ERR_INVALID, "asb_model_token_status: null argument");
+  volatile int* f = m->tok_flag_host;
+  *bad_out = f[0];
+  if (token_out) *token_out = f[1];
+  if (reset) f[0] = f[1] = 0;
+  return ASB_OK;
+}
+
+extern "C" int32_t* asb_model_token_flag_ptr(asb_model* m) { return m ? m->tok_flag_dev : nullptr; }
 
 extern "C" size_t asb_model_workspace_bytes(const asb_model* m, int B, int T) {
   if (!m || B <= 0 || T <= 0) return 0;

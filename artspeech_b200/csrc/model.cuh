@@ -53,6 +53,11 @@ struct asb_model {
   // optional per-stage timing (asb_model_profile_*): one event set per profiled forward
   int decoder_impl = 0;  // 0 = mma.sync (decoder.cu), 1 = tcgen05/TMEM (decoder_umma.cu, proj_umma.cu)
   int rnn_impl = 0;      // 0 = register-resident mma.sync / fp32 (gru.cu), 1 = tcgen05, W_hh in tensor memory (gru_umma.cu; fast-mode default)
+  // out-of-range token ids (nn.Embedding raises IndexError, models.py:135): the kernels that read tokens
+  // store {1, offending id} here and clamp; the word lives in mapped pinned host memory so that the host
+  // reads it without a device synchronisation (asb_model_token_status)
+  int* tok_flag_host = nullptr;
+  int* tok_flag_dev = nullptr;
   bool profile = false;
   std::vector<std::array<cudaEvent_t, ASB_N_STAGES + 1>> pending;
   std::vector<std::array<cudaEvent_t, ASB_N_STAGES + 1>> free_sets;

@@ -251,13 +251,13 @@ extern "C" int asb_p2cp(const float* u, const float* v, float* out, int64_t item
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool aligned = ((reinterpret_cast<uintptr_t>(u) | reinterpret_cast<uintptr_t>(v)) & 15) == 0;
   if (n == kD && m == kD && layout == ASB_LAYOUT_PLANAR && aligned) {
-    static bool configured = false;
-    if (!configured) {
-      cudaError_t e = cudaFuncSetAttribute(p2cp50_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           int(kSmemBytes));
-      if (e != cudaSuccess) return asb::check_cuda(e, "asb_p2cp: smem attribute");
-      configured = true;
-    }
+    static asb::DeviceOnce once;
+    if (int rc = once.run([&] {
+          return asb::check_cuda(cudaFuncSetAttribute(p2cp50_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                      int(kSmemBytes)),
+                                 "asb_p2cp: smem attribute");
+        }))
+      return rc;
     const long long n_tiles = (items + kTile - 1) / kTile;
     const int grid = int(n_tiles < asb::sm_count() ? n_tiles : asb::sm_count());
     p2cp50_kernel<<<grid, kThreads, kSmemBytes, st>>>(u, v, out, items);

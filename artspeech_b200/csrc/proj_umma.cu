@@ -255,12 +255,12 @@ int pack_proj_image(asb_model* m, cudaStream_t st) {
 }
 
 int launch_proj_umma(const asb_model* m, const float* A, float* C, int M, cudaStream_t st) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(proj_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-    if (e != cudaSuccess) return check_cuda(e, "proj_umma_kernel smem attribute");
-    configured = true;
-  }
+  static DeviceOnce once;
+  if (int rc = once.run([&] {
+        return check_cuda(cudaFuncSetAttribute(proj_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes),
+                          "proj_umma_kernel smem attribute");
+      }))
+    return rc;
   ProjArgs a;
   a.image = m->w.proj_image;
   a.bias = m->w.bih1;

@@ -115,7 +115,7 @@ def _side_stream(dev):
 
 @torch.no_grad()
 def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_incisor=None, mark=None,
-                   lengths_dev=None, overlap_target=True):
+                   lengths_dev=None, overlap_target=True, workspace=None):
     """One evaluation step on the model's device.
 
     tokens (B, T) int64, lengths sorted descending, targets (B, T, N, 2, 50) fp32, on the GPU (host
@@ -144,7 +144,7 @@ def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_inc
         tgt = tgt.contiguous()
     fork = torch.cuda.Event()
     fork.record(cur)
-    outputs = model(tokens, lengths, lengths_dev=lengths_dev)         # evaluation.py:57
+    outputs = model(tokens, lengths, lengths_dev=lengths_dev, workspace=workspace)    # evaluation.py:57
     # The branch is enqueued AFTER the forward's kernels (it depends only on `fork`): a full wave of
     # tract-variable CTAs takes every register of every SM, so the recurrent kernel (B/16 CTAs per
     # direction, the critical path) has to be placed first.  Measured on B200 at batch 256 x 100
@@ -200,7 +200,14 @@ class GraphedEvaluator:
                  overlap_target=True):
         dev = model.embedding.weight.device
         self.model = model
+        # The captured graph holds raw pointers into the model's packed-weight arena and into a scratch
+        # buffer.  The evaluator therefore (1) owns its scratch buffer (no eager call can re-allocate it,
+        # and several evaluators can run side by side), (2) keeps a strong reference to the native handle
+        # it captured, so the arena cannot be freed under the graph, and (3) remembers the weights key: a
+        # replay after the weights changed re-captures instead of silently running the old weights.
         self.lengths = [int(v) for v in lengths]
+        T_run = max(1, min(self.lengths[0], tokens.shape[1])) if self.lengths else 1
+        self.workspace = torch.empty(model.workspace_bytes(len(self.lengths), T_run), dtype=torch.uint8, device=dev)
         self.lengths_dev = torch.as_tensor(self.lengths, dtype=torch.int32).to(dev)
         self.tokens = tokens.to(dev).clone()
         self.targets = targets.to(dev).clone()
@@ -209,7 +216,8 @@ class GraphedEvaluator:
 
         def run():
             return evaluate_batch(model, self.tokens, self.lengths, self.targets, self.articulators,
-                                  self.upper_incisor, lengths_dev=self.lengths_dev, overlap_target=overlap_target)
+                                  self.upper_incisor, lengths_dev=self.lengths_dev, overlap_target=overlap_target,
+                                  workspace=self.workspace)
 
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
@@ -218,17 +226,41 @@ class GraphedEvaluator:
                 run()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
+        self._run = run
+        self._capture()
+
+    def _capture(self):
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
-            self.result = run()
+            self.result = self._run()
+        self._handle = self.model._native          # strong reference: the arena the graph points into
+        self._key = self.model._weights_key()
+
+    def stale(self):
+        """True if the model's weights or packed arena are no longer the captured ones."""
+        return self.model._native is not self._handle or self.model._weights_key() != self._key
+
+    def replay(self):
+        if self.stale():
+            # weights changed (optimizer step, load_state_dict, .to()): capture again with the current ones
+            # (one eager step first, on a side stream, so that the weights are packed outside the capture)
+            dev = self.tokens.device
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                self._run()
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            self._capture()
+        self.graph.replay()
+        return self.result
 
     def __call__(self, tokens=None, targets=None):
         if tokens is not None:
             self.tokens.copy_(tokens, non_blocking=True)
         if targets is not None:
             self.targets.copy_(targets, non_blocking=True)
-        self.graph.replay()
-        return self.result
+        return self.replay()
 
 
 class StreamedEvaluator:
@@ -271,7 +303,7 @@ class StreamedEvaluator:
                 slot.targets.copy_(tgt, non_blocking=True)
                 self.copied[s].record(self.copy_stream)
             cur.wait_event(self.copied[s])
-            slot.graph.replay()
+            slot.replay()
             reduce_accumulators(slot.result["acc"])
             self.acc_host[s].copy_(slot.result["acc"], non_blocking=True)
             self.done[s].record(cur)

@@ -24,11 +24,74 @@ from . import _lib
 PRECISIONS = {"fast": _lib.PRECISION_FAST, "bf16": _lib.PRECISION_FAST, "fp32": _lib.PRECISION_FP32}
 
 
-class ArticulatorPredictor(nn.Module):
-    """models.py:7-33 (parameter container; evaluated inside the fused decoder kernel)."""
+def _token_error(handle, vocab):
+    """IndexError (what nn.Embedding raises, models.py:63,135) if a kernel of this model has seen a token
+    id outside [0, vocab) since the last check.  Reads a mapped host word: no device synchronisation, so
+    it reports the forwards that have COMPLETED (``check_tokens()`` synchronises first)."""
+    bad, tok = ctypes.c_int32(0), ctypes.c_int64(0)
+    _lib.check(_lib.lib().asb_model_token_status(handle, ctypes.byref(bad), ctypes.byref(tok), 1))
+    if bad.value:
+        raise IndexError(f"index out of range in self (token id {tok.value} is outside [0, {vocab}))")
 
-    def __init__(self, in_features, n_samples):
+
+def _host_token_check(x, vocab):
+    """Tokens that arrive on the host are range-checked there, before anything is launched."""
+    if not x.is_cuda and x.numel():
+        lo, hi = int(x.min()), int(x.max())
+        if lo < 0 or hi >= vocab:
+            raise IndexError(f"index out of range in self (token id {lo if lo < 0 else hi} is outside [0, {vocab}))")
+
+
+class _PredictorHandle:
+    def __init__(self, ptr, key):
+        self.ptr = ptr
+        self.key = key
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                _lib.lib().asb_predictor_destroy(self.ptr)
+        except Exception:
+            pass
+        self.ptr = None
+
+
+class _PredictorForward(torch.autograd.Function):
+    """Standalone predictor under autograd: values from the kernel, gradient through the torch graph of
+    the same parameters (library code, like ``_TrainingForward``)."""
+
+    @staticmethod
+    def forward(ctx, module, inputs, *params):
+        ctx.module = module
+        ctx.save_for_backward(inputs)
+        with torch.no_grad():
+            return module._native_forward(inputs)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        module = ctx.module
+        (inputs,) = ctx.saved_tensors
+        params = list(module.parameters())
+        with torch.enable_grad():
+            xin = inputs.detach().requires_grad_(True)
+            out = module._graph(xin)
+            need = [xin] + [p for p in params if p.requires_grad]
+            grads = torch.autograd.grad(out, need, grad_out.to(out.dtype), allow_unused=True)
+        it = iter(grads[1:])
+        return (None, grads[0]) + tuple(next(it) if p.requires_grad else None for p in params)
+
+
+class ArticulatorPredictor(nn.Module):
+    """models.py:7-33.  Inside ``ArtSpeech`` the predictors are parameter containers evaluated by the
+    fused decoder kernel; called on its own (the transformer model builds its heads from this class,
+    phoneme_to_articulation/transformer/models.py:6,337-339) ``forward`` runs ``asb_predictor_forward``:
+    (..., in_features) -> (..., 2, n_samples), no sigmoid.  ``precision`` as for ``ArtSpeech``."""
+
+    def __init__(self, in_features, n_samples, precision="fast"):
         super().__init__()
+        self.precision = precision
+        self._dims = (in_features, n_samples)
+        self._native = None
         self.linear = nn.Sequential(
             nn.LayerNorm([in_features]),
             nn.Linear(in_features=in_features, out_features=256),
@@ -41,9 +104,63 @@ class ArticulatorPredictor(nn.Module):
         self.x_coords = nn.Linear(in_features=256, out_features=n_samples)
         self.y_coords = nn.Linear(in_features=256, out_features=n_samples)
 
+    def _apply(self, fn, *args, **kwargs):
+        self._native = None
+        return super()._apply(fn, *args, **kwargs)
+
+    def _ensure_native(self, dev):
+        if self.precision not in PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(PRECISIONS)}")
+        key = (self.precision,) + tuple((p.data_ptr(), p._version) for p in self.parameters())
+        if self._native is not None and self._native.key == key:
+            return self._native.ptr
+        self._native = None
+        sd = {k: v.detach() for k, v in self.named_parameters()}
+        for k, v in sd.items():
+            if not v.is_cuda or v.device != dev:
+                raise RuntimeError(f"parameter {k} is on {v.device}; artspeech_b200.ArticulatorPredictor runs on CUDA "
+                                   "only (call .to('cuda')) - there is no CPU fallback")
+            if v.dtype != torch.float32 or not v.is_contiguous():
+                raise RuntimeError(f"parameter {k} must be contiguous float32")
+        w = _lib.AsbPredictorWeights()
+        for field, name in (("ln0_w", "linear.0.weight"), ("ln0_b", "linear.0.bias"), ("fc1_w", "linear.1.weight"),
+                            ("fc1_b", "linear.1.bias"), ("ln1_w", "linear.3.weight"), ("ln1_b", "linear.3.bias"),
+                            ("fc2_w", "linear.4.weight"), ("fc2_b", "linear.4.bias"), ("ln2_w", "linear.6.weight"),
+                            ("ln2_b", "linear.6.bias"), ("xh_w", "x_coords.weight"), ("xh_b", "x_coords.bias"),
+                            ("yh_w", "y_coords.weight"), ("yh_b", "y_coords.bias")):
+            setattr(w, field, sd[name].data_ptr())
+        handle = ctypes.c_void_p()
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().asb_predictor_create(ctypes.byref(w), self._dims[0], self._dims[1],
+                                                       PRECISIONS[self.precision], _lib.stream_ptr(dev),
+                                                       ctypes.byref(handle)))
+        self._native = _PredictorHandle(handle, key)
+        return handle
+
     def forward(self, inputs):
-        raise RuntimeError("ArticulatorPredictor is evaluated inside ArtSpeech's fused CUDA decoder; "
-                           "it has no standalone forward in artspeech_b200")
+        """models.py:23-33: inputs (B, T, in_features) -> (B, T, 2, n_samples)."""
+        if torch.is_grad_enabled() and (inputs.requires_grad or any(p.requires_grad for p in self.parameters())):
+            return _PredictorForward.apply(self, inputs, *self.parameters())
+        return self._native_forward(inputs)
+
+    def _native_forward(self, inputs):
+        dev = self.x_coords.weight.device
+        if dev.type != "cuda":
+            raise RuntimeError("artspeech_b200.ArticulatorPredictor runs on CUDA only (call .to('cuda')); no CPU fallback")
+        in_features, n_samples = self._dims
+        if inputs.shape[-1] != in_features:
+            raise RuntimeError(f"expected inputs with last dimension {in_features}, got {tuple(inputs.shape)}")
+        x = inputs.detach().to(device=dev, dtype=torch.float32).reshape(-1, in_features).contiguous()
+        out = torch.empty(x.shape[0], 2, n_samples, dtype=torch.float32, device=dev)
+        handle = self._ensure_native(dev)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().asb_predictor_forward(handle, _lib.ptr(x), x.shape[0], _lib.ptr(out),
+                                                        _lib.stream_ptr(dev)))
+        if inputs.dim() == 3:                       # (B, T, C) -> (B, T, 2, D): the layout the kernel writes
+            return out.view(*inputs.shape[:-1], 2, n_samples)
+        # the reference stacks on dim 2 literally (models.py:31), whatever the input rank is
+        lead = inputs.shape[:-1]
+        return torch.stack([out[:, 0].reshape(*lead, n_samples), out[:, 1].reshape(*lead, n_samples)], dim=2)
 
     def _graph(self, inputs):
         """models.py:23-33 as a differentiable torch graph.  The forward pass never comes here (the
@@ -102,7 +219,9 @@ class ArtSpeech(nn.Module):
     """models.py:99-145.  ``precision``: "fast" (bf16 recurrent GEMM, tf32 elsewhere, fp32
     accumulate/state; contours within 2e-3 of the fp32 reference) or "fp32" (within 1e-5).
     ``rnn``: "gru" (the reference's cell, models.py:111) or "lstm" (the other member of RNNType,
-    phoneme_to_articulation/__init__.py:47-49; same state_dict keys as nn.LSTM; fast precision only)."""
+    phoneme_to_articulation/__init__.py:47-49; same state_dict keys as nn.LSTM).
+    Token ids outside [0, vocab_size) raise IndexError like nn.Embedding (models.py:135): at once for host
+    tensors; for device tensors the kernels record it and the NEXT call or ``check_tokens()`` raises."""
 
     def __init__(self, vocab_size, n_articulators, embed_dim=64, hidden_size=128, n_samples=50, dropout=0.,
                  precision="fast", rnn="gru"):
@@ -184,6 +303,12 @@ class ArtSpeech(nn.Module):
         self._workspace = None
         return super()._apply(fn, *args, **kwargs)
 
+    def invalidate_packed_weights(self):
+        """Drop the packed copy of the weights so that the next forward re-packs them.  Needed only after
+        edits that bypass autograd's version counter (``p.data.copy_()``, ``p.data.mul_()`` ...): ordinary
+        in-place updates (optimizer steps, ``load_state_dict``, ``p.add_()``) are detected by themselves."""
+        self._native = None
+
     def set_decoder(self, impl):
         """"tcgen05" (default in fast precision) or "mma" (mma.sync kernel) for the fused decoder."""
         dev = self.embedding.weight.device
@@ -196,6 +321,13 @@ class ArtSpeech(nn.Module):
         dev = self.embedding.weight.device
         code = {"tcgen05": 1, "mma": 0}[impl]
         _lib.check(_lib.lib().asb_model_set_recurrent(self._ensure_native(dev), code))
+
+    def check_tokens(self):
+        """Synchronise the model's device and raise IndexError if any forward since the last check was
+        given a token id outside [0, vocab_size) (nn.Embedding semantics, models.py:135)."""
+        if self._native is not None:
+            torch.cuda.synchronize(self.embedding.weight.device)
+            _token_error(self._native.ptr, self._dims[0])
 
     # ------------------------------------------------------------------ per-stage timing
     STAGES = ("gather", "gru_l0", "proj_l1", "gru_l1", "decoder")
@@ -215,13 +347,16 @@ class ArtSpeech(nn.Module):
         return {name: (float(ms[k]), int(calls[k])) for k, name in enumerate(self.STAGES)}
 
     # ------------------------------------------------------------------ forward
-    def forward(self, x, lengths, lengths_dev=None):
+    def forward(self, x, lengths, lengths_dev=None, workspace=None):
         """
         Args:
             x (torch.tensor): Torch tensor of shape (bs, seq_len), int64 tokens.
             lengths (list): Lengths of the input sequences sorted in decreasing order.
             lengths_dev (optional, extension): int32 CUDA tensor holding the same lengths; when given
                 no host->device copy is enqueued, which makes the call capturable in a CUDA graph.
+            workspace (optional, extension): uint8 CUDA tensor of at least ``workspace_bytes(bs, T)`` bytes
+                used instead of the module's own scratch buffer (callers that run several forwards
+                concurrently, or capture one in a CUDA graph, own their scratch).
 
         Return:
             output (torch.tensor): (bs, max(lengths), n_articulators, 2, n_samples) float32
@@ -229,11 +364,16 @@ class ArtSpeech(nn.Module):
         if self.training and self.rnn.dropout > 0:
             raise NotImplementedError("inter-layer dropout (train mode with dropout > 0) is not implemented")
         if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
-            if lengths_dev is not None:
-                raise ValueError("lengths_dev is an inference-only extension")
+            if lengths_dev is not None or workspace is not None:
+                raise ValueError("lengths_dev / workspace are inference-only extensions")
             L = lengths.detach().cpu().tolist() if torch.is_tensor(lengths) else list(lengths)
             return _TrainingForward.apply(self, x, [int(v) for v in L], *self.parameters())
-        return self._native_forward(x, lengths, lengths_dev)
+        return self._native_forward(x, lengths, lengths_dev, workspace)
+
+    def workspace_bytes(self, batch, seq_len):
+        """Scratch bytes one forward of a (batch, seq_len) input needs (asb_model_workspace_bytes)."""
+        dev = self.embedding.weight.device
+        return int(_lib.lib().asb_model_workspace_bytes(self._ensure_native(dev), int(batch), int(seq_len)))
 
     def _library_graph(self, x, lengths):
         """models.py:126-145 on the parameter containers as a differentiable torch graph (backward only)."""
@@ -243,7 +383,7 @@ class ArtSpeech(nn.Module):
         hidden = self.linear(rnn_out)
         return torch.sigmoid(torch.stack([predictor._graph(hidden) for predictor in self.predictors], dim=2))
 
-    def _native_forward(self, x, lengths, lengths_dev=None):
+    def _native_forward(self, x, lengths, lengths_dev=None, workspace=None):
         dev = self.embedding.weight.device
         if not dev.type == "cuda":
             raise RuntimeError("artspeech_b200.ArtSpeech runs on CUDA only (call .to('cuda')); no CPU fallback")
@@ -257,13 +397,21 @@ class ArtSpeech(nn.Module):
         if len(L) != B:
             raise RuntimeError(f"Expected `len(lengths)` to be equal to batch_size, but got {len(L)} "
                                f"(batch_size={B})")
+        _host_token_check(x, self._dims[0])
         xd = x.detach().to(device=dev, dtype=torch.int64).contiguous()
         handle = self._ensure_native(dev)
+        if not torch.cuda.is_current_stream_capturing():
+            _token_error(handle, self._dims[0])      # lazily: ids seen by the forwards that have completed
         T = max(1, min(L[0], T_in)) if L else 0
         lib = _lib.lib()
         need = int(lib.asb_model_workspace_bytes(handle, B, T))
-        if self._workspace is None or self._workspace.numel() < need or self._workspace.device != dev:
-            self._workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+        if workspace is not None:
+            if workspace.dtype != torch.uint8 or workspace.device != dev or workspace.numel() < need:
+                raise ValueError(f"workspace must be a uint8 tensor of >= {need} bytes on {dev}")
+        else:
+            if self._workspace is None or self._workspace.numel() < need or self._workspace.device != dev:
+                self._workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+            workspace = self._workspace
         vocab, n_art, _, _, n_samples = self._dims
         out = torch.empty(B, T, n_art, 2, n_samples, dtype=torch.float32, device=dev)
         c_len = (ctypes.c_int32 * B)(*L)
@@ -274,7 +422,7 @@ class ArtSpeech(nn.Module):
             ldev = _lib.ptr(lengths_dev)
         with torch.cuda.device(dev):
             _lib.check(lib.asb_model_forward_resident(handle, _lib.ptr(xd), T_in, c_len, ldev, B, _lib.ptr(out),
-                                                      _lib.ptr(self._workspace), self._workspace.numel(),
+                                                      _lib.ptr(workspace), workspace.numel(),
                                                       _lib.stream_ptr(dev)))
         return out
 
@@ -403,10 +551,21 @@ class SimpleArtSpeech(nn.Module):
         row = n_art * 2 * n_samples
         if row % 4:
             raise ValueError("n_articulators * 2 * num_samples must be a multiple of 4")
+        _host_token_check(x, vocab)
         xd = x.detach().to(device=dev, dtype=torch.int64).contiguous()
         B, T = xd.shape
         out = torch.empty(B, T, n_art, 2, n_samples, dtype=torch.float32, device=dev)
+        lib = _lib.lib()
+        if not torch.cuda.is_current_stream_capturing():
+            _token_error(self._native.ptr, vocab)
         with torch.cuda.device(dev):
-            _lib.check(_lib.lib().asb_gather_rows(_lib.ptr(table), _lib.ptr(xd), B * T, vocab, row, _lib.ptr(out),
-                                                  _lib.stream_ptr(dev)))
+            _lib.check(lib.asb_gather_rows_flagged(_lib.ptr(table), _lib.ptr(xd), B * T, vocab, row, _lib.ptr(out),
+                                                   ctypes.c_void_p(lib.asb_model_token_flag_ptr(self._native.ptr)),
+                                                   _lib.stream_ptr(dev)))
         return out
+
+    def check_tokens(self):
+        """Synchronise and raise IndexError if a token id outside [0, vocab_size) was seen (models.py:63)."""
+        if self._native is not None:
+            torch.cuda.synchronize(self.embedding.weight.device)
+            _token_error(self._native.ptr, self._dims[0])

@@ -72,7 +72,7 @@ class _HeadHandle:
 
 
 class PrincipalComponentsArtSpeech(nn.Module):
-    """rnn.py:36-109.  ``precision``: "fast" (bf16 recurrent GEMM, tf32 elsewhere) or "fp32" (GRU only)."""
+    """rnn.py:36-109.  ``precision``: "fast" (bf16 recurrent GEMM, tf32 elsewhere) or "fp32"; both for GRU and LSTM."""
 
     def __init__(self, vocab_size, indices_dict, embed_dim=64, hidden_size=128, rnn_dropout=0., rnn=RNNType.GRU,
                  precision="fast"):

@@ -46,6 +46,9 @@ typedef enum asb_status {
 
 ASB_API int asb_abi_version(void);
 ASB_API const char* asb_last_error_string(void);
+/* Hash of the sources, headers and compiler flags this library was built from (artspeech_b200/build.py
+ * source_hash()); the Python binding refuses a library whose hash differs from the sources beside it. */
+ASB_API const char* asb_build_hash(void);
 /* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
 ASB_API int64_t asb_launch_count(void);
 
@@ -158,7 +161,7 @@ typedef struct asb_model asb_model;
 
 #define ASB_CELL_GRU 3  /* nn.GRU, gate rows r, z, n (models.py:111) - both precisions                       */
 #define ASB_CELL_LSTM 4 /* nn.LSTM, gate rows i, f, g, o (RNNType.LSTM, phoneme_to_articulation/__init__.py:47-49)
-                           - ASB_PRECISION_FAST only; ASB_PRECISION_FP32 returns ASB_ERR_UNSUPPORTED */
+                           - both precisions (fast: tcgen05 kernel; fp32: lstm_fp32_kernel) */
 #define ASB_PRECISION_FAST 0 /* bf16 recurrent GEMM, tf32 elsewhere, fp32 accumulate/state (2e-3 gate) */
 #define ASB_PRECISION_FP32 1 /* 3xTF32 / FFMA everywhere (1e-5 gate)                                  */
 
@@ -233,6 +236,28 @@ ASB_API void asb_pc_head_destroy(asb_pc_head* h);
 /* features (rows, 2H) -> out (rows, n_components) */
 ASB_API int asb_pc_head_forward(asb_pc_head* h, const float* features, int64_t rows, float* out, void* stream);
 
+/* ArticulatorPredictor.forward on its own (phoneme_to_articulation/encoder_decoder/models.py:7-33): the
+ * class is also used outside ArtSpeech - the transformer model builds its heads from it
+ * (phoneme_to_articulation/transformer/models.py:6,337-339, in_features = embed_dim).
+ * LayerNorm(C) -> Linear(C,256) -> ReLU -> LayerNorm(256) -> Linear(256,256) -> ReLU -> LayerNorm(256) ->
+ * x_coords / y_coords stacked on dim 2; NO sigmoid.  in_features: multiple of 32 in [32, 256];
+ * n_samples <= 64.  All weight pointers are device fp32, row-major like nn.Linear.weight. */
+typedef struct asb_predictor asb_predictor;
+typedef struct asb_predictor_weights {
+  const float* ln0_w; const float* ln0_b;   /* (C)             linear.0 */
+  const float* fc1_w; const float* fc1_b;   /* (256, C), (256) linear.1 */
+  const float* ln1_w; const float* ln1_b;   /* (256)           linear.3 */
+  const float* fc2_w; const float* fc2_b;   /* (256,256),(256) linear.4 */
+  const float* ln2_w; const float* ln2_b;   /* (256)           linear.6 */
+  const float* xh_w; const float* xh_b;     /* (D, 256), (D)   x_coords */
+  const float* yh_w; const float* yh_b;     /* (D, 256), (D)   y_coords */
+} asb_predictor_weights;
+ASB_API int asb_predictor_create(const asb_predictor_weights* w, int in_features, int n_samples, int precision,
+                         void* stream, asb_predictor** out);
+ASB_API void asb_predictor_destroy(asb_predictor* p);
+/* features (rows, in_features) -> out (rows, 2, n_samples) */
+ASB_API int asb_predictor_forward(asb_predictor* p, const float* features, int64_t rows, float* out, void* stream);
+
 /* Decoder alone on caller-supplied feature rows: features (rows, 2*hidden) fp32 ->
  * out (rows, n_art, 2, n_samples) = sigmoid(stack(predictor_i(ReLU(linear.0(features))))),
  * models.py:140-145.  SimpleArtSpeech (models.py:53-96) runs through this entry: its features are
@@ -245,6 +270,20 @@ ASB_API int asb_model_decode(asb_model* m, const float* features, int64_t rows, 
  * [0, vocab) yields a row of NaNs. */
 ASB_API int asb_gather_rows(const float* table, const int64_t* tokens, int64_t rows, int vocab, int row_floats,
                     float* out, void* stream);
+
+/* Same with a status word: token_flag (device-accessible int32[2], may be NULL) receives {1, id} when a token
+ * id lies outside [0, vocab) - what nn.Embedding reports as IndexError (models.py:63,135). */
+ASB_API int asb_gather_rows_flagged(const float* table, const int64_t* tokens, int64_t rows, int vocab,
+                            int row_floats, float* out, int32_t* token_flag, void* stream);
+
+/* Token-id range status of a model: nn.Embedding raises IndexError for ids outside [0, vocab)
+ * (models.py:135).  The kernels that read tokens clamp such an id (memory safety) and store {1, id} in a
+ * status word in mapped pinned host memory.  asb_model_token_status reads it WITHOUT synchronising (it
+ * reflects the forwards that have completed): *bad_out = 1 if an id was out of range, *token_out (may be
+ * NULL) one offending id; reset != 0 clears it.  asb_model_token_flag_ptr is the word's device address
+ * (for asb_gather_rows_flagged). */
+ASB_API int asb_model_token_status(asb_model* m, int32_t* bad_out, int64_t* token_out, int reset);
+ASB_API int32_t* asb_model_token_flag_ptr(asb_model* m);
 
 /* Decoder implementation: 1 = tcgen05/TMEM kernel (default in fast precision with n_samples = 50),
  * 0 = mma.sync kernel (always used in fp32 precision).  Both compute models.py:140-145.  The

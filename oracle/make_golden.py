@@ -66,6 +66,33 @@ def golden_model():
     print("model_small:", tuple(out32.shape), "params", sum(v.numel() for v in sd.values()))
 
 
+def golden_predictor():
+    """Standalone ArticulatorPredictor (models.py:7-33; instantiated on its own by
+    transformer/models.py:337-339) of the unmodified reference: seed-0 instances with LayerNorm affines
+    perturbed, fp32 and fp64 outputs, per-key parameter sums."""
+    m = ref.models()
+    out = {}
+    for tag, (c, d, shape) in {"a": (64, 50, (5, 13)), "b": (256, 30, (70,)), "c": (128, 50, (2, 3, 4))}.items():
+        torch.manual_seed(0)
+        net = m.ArticulatorPredictor(c, d).eval()
+        g = torch.Generator().manual_seed(17)
+        with torch.no_grad():
+            for k, v in net.state_dict().items():      # exercise the affine terms
+                if k.startswith("linear.") and v.dim() == 1 and k.split(".")[1] in ("0", "3", "6"):
+                    v.add_(0.3 * torch.randn(v.shape, generator=g))
+        sd = net.state_dict()
+        keys = sorted(sd.keys())
+        x = torch.randn(*shape, c, generator=torch.Generator().manual_seed(18))
+        with torch.no_grad():
+            o32 = net(x)
+            o64 = net.double()(x.double())
+        out.update({f"x_{tag}": x.numpy(), f"out32_{tag}": o32.numpy(), f"out64_{tag}": o64.numpy(),
+                    f"keys_{tag}": np.array(keys),
+                    f"sums_{tag}": np.array([sd[k].double().sum().item() for k in keys])})
+    np.savez_compressed(os.path.join(GOLDEN, "predictor.npz"), **out)
+    print("predictor:", out["out32_a"].shape, out["out32_b"].shape, out["out32_c"].shape)
+
+
 def golden_model_grad():
     """Gradients of the unmodified reference ArtSpeech (fp32 and fp64) for a seeded linear functional
     of its output: per-parameter sums / abs-sums plus the full gradient of the small tensors."""
@@ -318,6 +345,7 @@ def main(out_dir=None):
 
 def _run_all():
     golden_model()
+    golden_predictor()
     golden_model_grad()
     golden_pc_model()
     golden_p2cp()

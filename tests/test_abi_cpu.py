@@ -31,3 +31,12 @@ def test_argument_errors_do_not_need_a_gpu():
     assert lib.asb_p2cp(None, None, None, 0, 50, 50, 0, None) == _lib.ASB_OK   # empty input is a no-op
     idx = (ctypes.c_int32 * 6)(0, 1, 2, 3, 99, 5)
     assert lib.asb_tract_variables(None, 4, 11, idx, None, None, None, None) == _lib.ASB_ERR_INVALID
+
+
+def test_library_carries_the_hash_of_the_sources_beside_it():
+    """build() proves it compiled this tree: asb_build_hash() == hash(sources + headers + flags); the
+    binding refuses a library built from other sources."""
+    from artspeech_b200 import build
+    assert build.library_hash() == build.source_hash()
+    assert _lib.lib().asb_build_hash().decode() == build.source_hash()
+    assert len(build.source_hash()) == 16

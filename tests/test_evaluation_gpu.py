@@ -168,3 +168,67 @@ def test_run_test_matches_reference_run_test(golden_dir, tmp_path, precision, to
         assert (abs(a - b) <= 1e-3 * abs(b)).all()            # the reference's fp32 cdist (finding F2)
     ph = pd.read_csv(os.path.join(str(tmp_path), "3", "S1_2", "phonemes.csv"), dtype={"frame": str})
     assert list(ph.columns) == ["sentence", "frame", "phoneme"] and len(ph) == len(got)
+
+
+def test_two_shards_accumulate_to_the_one_shard_vector(setup):
+    """SURVEY.md 8e on hardware: the utterances of a batch split r::2 over two shards, each evaluated on
+    its own stream with its own scratch (as two ranks would), and the two `accumulate_device` vectors
+    summed (what the all-reduce does) equal the one-shard vector; the per-frame results are bit-equal."""
+    evaluation, net, x, L, tgt = setup
+    whole = evaluation.evaluate_batch(net, x, L, tgt)
+    torch.cuda.synchronize()
+    B = x.shape[0]
+    total = torch.zeros_like(whole["acc"])
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    parts = []
+    for r in range(2):
+        idx = evaluation.shard_utterances(B, r, 2)
+        Lr = [int(L[i]) for i in idx]                      # still sorted descending
+        ws = torch.empty(net.workspace_bytes(len(idx), max(Lr)), dtype=torch.uint8, device="cuda")
+        streams[r].wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(streams[r]):
+            res = evaluation.evaluate_batch(net, x[idx], Lr, tgt[idx], workspace=ws, overlap_target=False)
+        parts.append((idx, Lr, res, ws))
+    for s in streams:
+        torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    for idx, Lr, res, _ in parts:
+        total += res["acc"]
+        T_r = res["outputs"].shape[1]
+        for k, b in enumerate(idx):
+            n = Lr[k]
+            assert torch.equal(res["outputs"][k, :n], whole["outputs"][b, :n])
+            assert torch.equal(res["p2cp"][k, :n], whole["p2cp"][b, :n])
+            assert torch.equal(res["tv_pred"][k, :n], whole["tv_pred"][b, :n])
+        assert T_r == max(Lr)
+    rel = ((total - whole["acc"]).abs() / whole["acc"].abs().clamp_min(1e-300)).max().item()
+    print(f"2-shard accumulators vs 1-shard: max rel {rel:.2e}")
+    assert rel <= 1e-12
+    n = 10
+    assert total[n].item() == B and total[n + 13].item() == float(sum(int(v) for v in L))
+
+
+def test_graphed_evaluator_follows_weight_changes(setup):
+    """A captured step must never run stale weights or freed memory: after an in-place parameter update
+    or a load_state_dict the next replay re-captures."""
+    evaluation, _, x, L, tgt = setup
+    from artspeech_b200 import models
+    torch.manual_seed(1)
+    net = models.ArtSpeech(45, 10).cuda().eval()
+    g = evaluation.GraphedEvaluator(net, x, L, tgt)
+    a = g()["outputs"].clone()
+    assert not g.stale()
+    with torch.no_grad():
+        net.linear[0].bias.add_(0.5)                       # bumps the parameter version
+    assert g.stale()
+    net(x[:2, :5], [5, 5])                                 # an eager call with another shape in between
+    b = g()["outputs"].clone()
+    torch.cuda.synchronize()
+    want = evaluation.evaluate_batch(net, x, L, tgt)["outputs"]
+    assert torch.equal(b, want) and (a - b).abs().max().item() > 1e-4
+    net.to("cuda")                                         # _apply drops the packed arena
+    sd = {k: v.clone() for k, v in net.state_dict().items()}
+    net.load_state_dict(sd)
+    c = g()["outputs"]
+    torch.cuda.synchronize()
+    assert torch.equal(c, want)

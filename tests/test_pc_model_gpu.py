@@ -25,7 +25,7 @@ def mods():
     return pc, omodel
 
 
-@pytest.mark.parametrize("cell,precision", [("GRU", "fast"), ("GRU", "fp32"), ("LSTM", "fast")])
+@pytest.mark.parametrize("cell,precision", [("GRU", "fast"), ("GRU", "fp32"), ("LSTM", "fast"), ("LSTM", "fp32")])
 def test_pc_model_golden(mods, golden_dir, cell, precision):
     pc, omodel = mods
     g = np.load(os.path.join(golden_dir, "pc_model.npz"))
