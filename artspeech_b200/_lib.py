@@ -43,6 +43,13 @@ class AsbPcWeights(ctypes.Structure):
         "fc3_w", "fc3_b")]
 
 
+class AsbEvalBuffers(ctypes.Structure):
+    """Mirror of `struct asb_eval_buffers`."""
+    _fields_ = [(n, ctypes.c_void_p) for n in (
+        "outputs", "p2cp", "tv_pred", "tv_pred_idx", "tv_pred_poc", "tv_target", "tv_target_idx", "tv_target_poc",
+        "scratch", "acc", "total", "workspace")] + [("workspace_bytes", ctypes.c_size_t)]
+
+
 class AsbPredictorWeights(ctypes.Structure):
     """Mirror of `struct asb_predictor_weights`."""
     _fields_ = [(n, ctypes.c_void_p) for n in (
@@ -84,6 +91,13 @@ SIGNATURES = {
                                                   _c_f32p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]),
     "asb_eval_accumulate": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                            ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
+    "asb_eval_accumulate_total": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                                                 ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                                 ctypes.c_void_p]),
+    "asb_eval_step": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int32),
+                                     ctypes.c_void_p, ctypes.c_int, _c_f32p, ctypes.POINTER(ctypes.c_int32), _c_f32p,
+                                     ctypes.c_int64, ctypes.POINTER(AsbEvalBuffers), ctypes.c_void_p,
+                                     ctypes.c_void_p]),
     "asb_eval_sentence_metrics": (ctypes.c_int, [_c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                                  ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                                  ctypes.c_void_p]),

@@ -52,7 +52,7 @@ utterance_partials_kernel(const float* __restrict__ p2cp, const float* __restric
 // dependent loads)
 __global__ void __launch_bounds__(1024)
 reduce_partials_kernel(const double* __restrict__ partial, const int* __restrict__ lengths, int B, int T, int n_art,
-                       double* __restrict__ acc) {
+                       double* __restrict__ acc, double* __restrict__ total) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, cols = n_art + 12;
   for (int j = warp; j <= cols; j += 32) {
     double s = 0.0;
@@ -63,11 +63,19 @@ reduce_partials_kernel(const double* __restrict__ partial, const int* __restrict
     }
     s = warp_sum_f64(s);
     if (lane == 0) {
+      // `total` (optional) is the running sum over the batches of an evaluation: one writer per element,
+      // batches are stream-ordered, so its summation order is fixed as well
       if (j < cols) {
-        acc[j < n_art ? j : j + 1] = s;
+        const int o = j < n_art ? j : j + 1;
+        acc[o] = s;
+        if (total) total[o] += s;
       } else {
         acc[n_art] = double(B);
         acc[n_art + 13] = s;
+        if (total) {
+          total[n_art] += double(B);
+          total[n_art + 13] += s;
+        }
       }
     }
   }
@@ -143,6 +151,12 @@ reduce_sentence_metrics_kernel(const double* __restrict__ partial, int B, int n_
 extern "C" int asb_eval_accumulate(const float* p2cp, const float* tv_pred, const float* tv_target,
                                    const int32_t* lengths_dev, int B, int T, int n_art, double* scratch, double* acc,
                                    void* stream) {
+  return asb_eval_accumulate_total(p2cp, tv_pred, tv_target, lengths_dev, B, T, n_art, scratch, acc, nullptr, stream);
+}
+
+extern "C" int asb_eval_accumulate_total(const float* p2cp, const float* tv_pred, const float* tv_target,
+                                         const int32_t* lengths_dev, int B, int T, int n_art, double* scratch,
+                                         double* acc, double* total, void* stream) {
   if (B <= 0 || T <= 0 || n_art <= 0 || n_art + 13 > 64)
     return asb::set_error(ASB_ERR_INVALID, "asb_eval_accumulate: bad shape (B %d, T %d, n_art %d)", B, T, n_art);
   if (!p2cp || !tv_pred || !tv_target || !lengths_dev || !scratch || !acc)
@@ -150,7 +164,7 @@ extern "C" int asb_eval_accumulate(const float* p2cp, const float* tv_pred, cons
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   utterance_partials_kernel<<<B, 256, 0, st>>>(p2cp, tv_pred, tv_target, lengths_dev, T, n_art, scratch);
   ASB_CHECK_LAUNCH("utterance_partials_kernel");
-  reduce_partials_kernel<<<1, 1024, 0, st>>>(scratch, lengths_dev, B, T, n_art, acc);
+  reduce_partials_kernel<<<1, 1024, 0, st>>>(scratch, lengths_dev, B, T, n_art, acc, total);
   ASB_CHECK_LAUNCH("reduce_partials_kernel");
   return ASB_OK;
 }

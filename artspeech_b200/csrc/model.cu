@@ -167,6 +167,8 @@ extern "C" void asb_model_destroy(asb_model* m) {
   for (auto& set : m->free_sets)
     for (auto e : set) cudaEventDestroy(e);
   if (m->tok_flag_host) cudaFreeHost(m->tok_flag_host);
+  if (m->ev_fork) cudaEventDestroy(m->ev_fork);
+  if (m->ev_join) cudaEventDestroy(m->ev_join);
   cudaFree(m->arena);
   delete m;
 }

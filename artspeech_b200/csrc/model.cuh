@@ -58,6 +58,7 @@ struct asb_model {
   // reads it without a device synchronisation (asb_model_token_status)
   int* tok_flag_host = nullptr;
   int* tok_flag_dev = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // asb_eval_step: fork / join of the target-side branch
   bool profile = false;
   std::vector<std::array<cudaEvent_t, ASB_N_STAGES + 1>> pending;
   std::vector<std::array<cudaEvent_t, ASB_N_STAGES + 1>> free_sets;

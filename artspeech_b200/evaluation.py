@@ -50,18 +50,24 @@ def accumulate(p2cp, tv_pred, tv_tgt, lengths):
     return acc
 
 
-def accumulate_device(p2cp, tv_pred, tv_tgt, lengths_dev):
-    """Same vector as ``accumulate`` computed by the library (asb_eval_accumulate): two launches,
-    fixed summation order.  All tensors on the GPU; lengths_dev (B) int32."""
+def accumulate_device(p2cp, tv_pred, tv_tgt, lengths_dev, total=None):
+    """Same vector as ``accumulate`` computed by the library (asb_eval_accumulate_total): two launches,
+    fixed summation order.  All tensors on the GPU; lengths_dev (B) int32.  ``total`` (optional fp64
+    vector of the same size on the GPU) also receives the batch's vector ADDED to it: the running sum
+    of an evaluation, reduced over ranks once at its end."""
     from . import _lib
     B, T, n = p2cp.shape
     dev = p2cp.device
     scratch = torch.empty(B * (n + 12), dtype=torch.float64, device=dev)
     acc = torch.empty(accumulator_size(n), dtype=torch.float64, device=dev)
+    if total is not None and (total.dtype != torch.float64 or total.device != dev or total.numel() != acc.numel()
+                              or not total.is_contiguous()):
+        raise ValueError("total must be a contiguous float64 tensor of accumulator_size(n) elements on the GPU")
     with torch.cuda.device(dev):
-        _lib.check(_lib.lib().asb_eval_accumulate(
+        _lib.check(_lib.lib().asb_eval_accumulate_total(
             _lib.ptr(p2cp.contiguous()), _lib.ptr(tv_pred.contiguous()), _lib.ptr(tv_tgt.contiguous()),
-            _lib.ptr(lengths_dev), B, T, n, _lib.ptr(scratch), _lib.ptr(acc), _lib.stream_ptr(dev)))
+            _lib.ptr(lengths_dev), B, T, n, _lib.ptr(scratch), _lib.ptr(acc),
+            _lib.ptr(total) if total is not None else None, _lib.stream_ptr(dev)))
     return acc
 
 
@@ -113,58 +119,141 @@ def _side_stream(dev):
     return _SIDE_STREAMS[key]
 
 
+class EvalBuffers:
+    """Every buffer one evaluation step of a (B, T) batch writes (``asb_eval_buffers``): contours, P2CP,
+    tract variables of prediction and target (values, index pairs, points of constriction), the fp64
+    accumulator vector, the forward's scratch and - with ``total=True`` - the running sum over the steps
+    that use these buffers.  Allocated once and reused by every step of the same shape, so that a step is a
+    single native call with no allocation."""
+
+    def __init__(self, model, B, T, total=False, workspace=None):
+        from . import _lib
+        dev = model.embedding.weight.device
+        n, d = model._dims[1], model._dims[4]
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.shape = (int(B), int(T))
+        self.outputs = torch.empty(B, T, n, 2, d, **f32)
+        self.p2cp = torch.empty(B, T, n, **f32)
+        self.tv_pred, self.tv_target = torch.empty(B, T, 4, **f32), torch.empty(B, T, 4, **f32)
+        self.tv_pred_idx = torch.empty(B, T, 4, 2, dtype=torch.int32, device=dev)
+        self.tv_target_idx = torch.empty(B, T, 4, 2, dtype=torch.int32, device=dev)
+        self.tv_pred_poc, self.tv_target_poc = torch.empty(B, T, 4, 2, 2, **f32), torch.empty(B, T, 4, 2, 2, **f32)
+        self.scratch = torch.empty(B * (n + 12), dtype=torch.float64, device=dev)
+        self.acc = torch.empty(accumulator_size(n), dtype=torch.float64, device=dev)
+        self.total = torch.zeros(accumulator_size(n), dtype=torch.float64, device=dev) if total else None
+        need = model.workspace_bytes(B, T)
+        if workspace is not None and (workspace.dtype != torch.uint8 or workspace.device != dev
+                                      or workspace.numel() < need):
+            raise ValueError(f"workspace must be a uint8 tensor of >= {need} bytes on {dev}")
+        self.workspace = workspace if workspace is not None else torch.empty(need, dtype=torch.uint8, device=dev)
+        c = _lib.AsbEvalBuffers()
+        for name in ("outputs", "p2cp", "tv_pred", "tv_pred_idx", "tv_pred_poc", "tv_target", "tv_target_idx",
+                     "tv_target_poc", "scratch", "acc", "workspace"):
+            setattr(c, name, getattr(self, name).data_ptr())
+        c.total = self.total.data_ptr() if self.total is not None else None
+        c.workspace_bytes = self.workspace.numel()
+        self.c = c
+
+    def result(self):
+        return {"outputs": self.outputs, "p2cp": self.p2cp, "tv_pred": self.tv_pred, "tv_target": self.tv_target,
+                "tv_pred_idx": self.tv_pred_idx, "tv_target_idx": self.tv_target_idx, "tv_pred_poc": self.tv_pred_poc,
+                "tv_target_poc": self.tv_target_poc, "acc": self.acc}
+
+
+def _tv_rows(articulators, external_upper_incisor):
+    import ctypes
+
+    from .tract_variables import _ABI_ORDER, UPPER_INCISOR
+    index = articulators if isinstance(articulators, dict) else {name: k for k, name in enumerate(articulators)}
+    if external_upper_incisor:
+        index = dict(index)
+        index.setdefault(UPPER_INCISOR, -1)
+    return (ctypes.c_int32 * 6)(*[index[name] for name in _ABI_ORDER])     # KeyError like the reference
+
+
+@torch.no_grad()
+def evaluate_step(model, tokens, lengths, lengths_dev, targets, buffers, articulators=None, upper_incisor=None,
+                  side_stream=None):
+    """The native step (``asb_eval_step``) on device-resident inputs into preallocated ``EvalBuffers``: ONE
+    library call enqueues forward, P2CP, both tract-variable launches and the accumulation on the current
+    stream (the target's tract variables on ``side_stream``).  tokens (B, T_in) int64 and targets
+    (B, T, N, 2, 50) fp32 contiguous, both on the model's device; ``lengths`` the host list (sorted
+    descending, lengths[0] == T == the buffers' T), ``lengths_dev`` the same as an int32 device tensor."""
+    import ctypes
+
+    from . import _lib
+    from .models import _token_error
+    dev = model.embedding.weight.device
+    B, T = buffers.shape
+    L = [int(v) for v in lengths]
+    if len(L) != B or not L or L[0] != T:
+        raise ValueError(f"lengths must hold {B} values with lengths[0] == {T}")
+    if tokens.device != dev or targets.device != dev or tokens.dtype != torch.int64 or targets.dtype != torch.float32:
+        raise ValueError("evaluate_step needs int64 tokens and float32 targets on the model's device")
+    if not tokens.is_contiguous() or not targets.is_contiguous() or tuple(targets.shape[:2]) != (B, T):
+        raise ValueError(f"targets must be contiguous (B, T, ...) = ({B}, {T}, ...); tokens contiguous")
+    articulators = articulators or synthetic.ARTICULATORS
+    ui = synthetic.UPPER_INCISOR_REF if upper_incisor is None else upper_incisor
+    if ui.device != dev or ui.dtype != torch.float32 or not ui.is_contiguous():
+        ui = ui.to(device=dev, dtype=torch.float32).contiguous()
+    if ui.shape[-2:] != (2, 50) or ui.numel() not in (100, B * T * 100):
+        raise ValueError(f"upper_incisor must be (2, 50) or one (2, 50) contour per frame, got {tuple(ui.shape)}")
+    rows = _tv_rows(articulators, True)
+    handle = model._ensure_native(dev)
+    if not torch.cuda.is_current_stream_capturing():
+        _token_error(handle, model._dims[0])
+    cur = torch.cuda.current_stream(dev)
+    side = cur if side_stream is None else side_stream
+    buffers._keep = (ui, tokens, targets, lengths_dev)      # alive until the next step reuses the buffers
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().asb_eval_step(
+            handle, _lib.ptr(tokens), tokens.shape[1], (ctypes.c_int32 * B)(*L), _lib.ptr(lengths_dev), B,
+            _lib.ptr(targets), rows, _lib.ptr(ui), 0 if ui.numel() == 100 else 100, ctypes.byref(buffers.c),
+            ctypes.c_void_p(cur.cuda_stream), ctypes.c_void_p(side.cuda_stream)))
+    return buffers.result()
+
+
 @torch.no_grad()
 def evaluate_batch(model, tokens, lengths, targets, articulators=None, upper_incisor=None, mark=None,
-                   lengths_dev=None, overlap_target=True, workspace=None):
+                   lengths_dev=None, overlap_target=True, workspace=None, total=None, buffers=None):
     """One evaluation step on the model's device.
 
     tokens (B, T) int64, lengths sorted descending, targets (B, T, N, 2, 50) fp32, on the GPU (host
     tensors are copied to the model's device first).
-    Returns dict(outputs, p2cp (B,T,N), tv_pred (B,T,4), tv_target (B,T,4), acc (N+14,) fp64).
-    ``mark(name)``, if given, is called at the stage boundaries (bench.py records CUDA events there).
-    """
+    Returns dict(outputs, p2cp (B,T,N), tv_pred (B,T,4), tv_target (B,T,4), acc (N+14,) fp64, and the
+    tract variables' index pairs / points of constriction).  The whole step is one native call
+    (``evaluate_step``); ``buffers`` (an ``EvalBuffers`` of the right shape) avoids its allocations.
+    ``total``: fp64 vector that also receives the accumulators added to it.
+    ``mark(name)``, if given, is called before and after the step."""
     mark = mark or (lambda name: None)
-    articulators = articulators or synthetic.ARTICULATORS
-    if upper_incisor is None:
-        upper_incisor = synthetic.UPPER_INCISOR_REF
     dev = model.embedding.weight.device
+    from .models import _host_token_check
+    _host_token_check(tokens, model._dims[0])
     tokens = tokens.to(dev, non_blocking=True)        # host batches (pinned) are copied here
     targets = targets.to(dev, non_blocking=True)
+    L = [int(v) for v in (lengths.tolist() if torch.is_tensor(lengths) else lengths)]
+    if len(L) != tokens.shape[0]:
+        raise RuntimeError(f"Expected `len(lengths)` to be equal to batch_size, but got {len(L)} "
+                           f"(batch_size={tokens.shape[0]})")
     if lengths_dev is None:
-        lengths_dev = torch.as_tensor([int(v) for v in lengths], dtype=torch.int32).to(dev)
+        lengths_dev = torch.as_tensor(L, dtype=torch.int32).to(dev)
+    T = max(1, min(L[0], tokens.shape[1])) if L else 1
+    tgt = targets[:, :T]
+    if not tgt.is_contiguous() or tgt.dtype != torch.float32:
+        tgt = tgt.to(torch.float32).contiguous()
+    tok = tokens if (tokens.dtype == torch.int64 and tokens.is_contiguous()) else tokens.to(torch.int64).contiguous()
+    if buffers is None:
+        buffers = EvalBuffers(model, len(L), T, workspace=workspace)
+        if total is not None:
+            buffers.total = total
+            buffers.c.total = total.data_ptr()
     mark("start")
-    # The target's tract variables do not depend on the forward pass: they run on a side stream
-    # (forked here, joined before the accumulation) and fill the SMs the recurrent kernels leave
-    # idle (2 directions x B/16 CTAs).  Inside a CUDA-graph capture this becomes a parallel branch.
     cur = torch.cuda.current_stream(dev)
     side = _side_stream(dev) if overlap_target else cur
-    T_in = min(int(max(lengths)), tokens.shape[1]) if len(lengths) else 0
-    tgt = targets[:, :max(1, T_in)]
-    if not tgt.is_contiguous():
-        tgt = tgt.contiguous()
-    fork = torch.cuda.Event()
-    fork.record(cur)
-    outputs = model(tokens, lengths, lengths_dev=lengths_dev, workspace=workspace)    # evaluation.py:57
-    # The branch is enqueued AFTER the forward's kernels (it depends only on `fork`): a full wave of
-    # tract-variable CTAs takes every register of every SM, so the recurrent kernel (B/16 CTAs per
-    # direction, the critical path) has to be placed first.  Measured on B200 at batch 256 x 100
-    # (tools/overlap_check.py): 0.500 -> 0.479 ms per step; capping the branch's grid
-    # (tract_variables_batch(max_ctas=...)) to leave SMs free did not improve on that.
-    side.wait_event(fork)
-    with torch.cuda.stream(side):
-        tv_tgt, _, _ = tract_variables_batch(tgt, articulators, upper_incisor)    # __init__.py:261
-    mark("forward")
-    assert outputs.shape[1] == tgt.shape[1], (outputs.shape, tgt.shape)
-    p2cp = p2cp_distance(outputs, tgt)                                # evaluation.py:72 (all sentences at once)
-    mark("p2cp")
-    tv_pred, _, _ = tract_variables_batch(outputs, articulators, upper_incisor)   # __init__.py:256
-    cur.wait_stream(side)
-    if side is not cur and not torch.cuda.is_current_stream_capturing():
-        tv_tgt.record_stream(cur)
-    mark("tv")
-    acc = accumulate_device(p2cp, tv_pred, tv_tgt, lengths_dev)       # evaluation.py:68-84,142-156
+    res = evaluate_step(model, tok, [T] + L[1:] if L and L[0] > T else L, lengths_dev, tgt, buffers, articulators,
+                        upper_incisor, side)
     mark("reduce")
-    return {"outputs": outputs, "p2cp": p2cp, "tv_pred": tv_pred, "tv_target": tv_tgt, "acc": acc}
+    return res
 
 
 def reduce_accumulators(acc):
@@ -191,34 +280,40 @@ def summarize(acc, n_articulators, articulators=None):
 
 
 class GraphedEvaluator:
-    """``evaluate_batch`` for a fixed (batch, lengths) shape captured once in a CUDA graph and replayed:
-    the step is ~10 short kernels, so eager launches leave the GPU idle between them.  Inputs are
-    copied into static device buffers (``tokens``, ``targets``); results are the static tensors of
-    the captured step (valid until the next replay)."""
+    """``evaluate_batch`` for a fixed (batch, T) shape captured once in a CUDA graph and replayed: the
+    step is ~10 short kernels, and a replay costs the host one launch.  Inputs are copied into static
+    device buffers (``tokens``, ``targets``, ``lengths_dev``); results are the static tensors of the
+    captured step (valid until the next replay); ``total`` is the running sum of the accumulator vectors
+    of all replays since ``reset_total()``.
+
+    The captured graph holds raw pointers into the model's packed-weight arena and into buffers.  The
+    evaluator therefore (1) owns its buffers, scratch included (no eager call can re-allocate them, and
+    several evaluators can run side by side), (2) keeps a strong reference to the native handle it
+    captured, so the arena cannot be freed under the graph, and (3) remembers the weights key: a replay
+    after the weights changed re-captures instead of silently running the old weights."""
 
     def __init__(self, model, tokens, lengths, targets, articulators=None, upper_incisor=None, warmup=3,
                  overlap_target=True):
         dev = model.embedding.weight.device
         self.model = model
-        # The captured graph holds raw pointers into the model's packed-weight arena and into a scratch
-        # buffer.  The evaluator therefore (1) owns its scratch buffer (no eager call can re-allocate it,
-        # and several evaluators can run side by side), (2) keeps a strong reference to the native handle
-        # it captured, so the arena cannot be freed under the graph, and (3) remembers the weights key: a
-        # replay after the weights changed re-captures instead of silently running the old weights.
         self.lengths = [int(v) for v in lengths]
-        T_run = max(1, min(self.lengths[0], tokens.shape[1])) if self.lengths else 1
-        self.workspace = torch.empty(model.workspace_bytes(len(self.lengths), T_run), dtype=torch.uint8, device=dev)
+        self.T = max(1, min(self.lengths[0], tokens.shape[1])) if self.lengths else 1
         self.lengths_dev = torch.as_tensor(self.lengths, dtype=torch.int32).to(dev)
-        self.tokens = tokens.to(dev).clone()
-        self.targets = targets.to(dev).clone()
+        self.tokens = tokens.to(dev).to(torch.int64).clone().contiguous()
+        self.targets = targets.to(dev)[:, :self.T].to(torch.float32).clone().contiguous()
         self.upper_incisor = (synthetic.UPPER_INCISOR_REF if upper_incisor is None else upper_incisor).to(dev)
+        self.upper_incisor = self.upper_incisor.to(torch.float32).contiguous()
         self.articulators = articulators
+        self.buffers = EvalBuffers(model, len(self.lengths), self.T, total=True)
+        self.total = self.buffers.total
+        self.side = torch.cuda.Stream(device=dev) if overlap_target else None
 
         def run():
-            return evaluate_batch(model, self.tokens, self.lengths, self.targets, self.articulators,
-                                  self.upper_incisor, lengths_dev=self.lengths_dev, overlap_target=overlap_target,
-                                  workspace=self.workspace)
+            host = [self.T] + self.lengths[1:]
+            return evaluate_step(model, self.tokens, host, self.lengths_dev, self.targets, self.buffers,
+                                 self.articulators, self.upper_incisor, self.side)
 
+        self._run = run
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
@@ -226,8 +321,8 @@ class GraphedEvaluator:
                 run()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
-        self._run = run
         self._capture()
+        self.reset_total()
 
     def _capture(self):
         self.graph = torch.cuda.CUDAGraph()
@@ -240,11 +335,26 @@ class GraphedEvaluator:
         """True if the model's weights or packed arena are no longer the captured ones."""
         return self.model._native is not self._handle or self.model._weights_key() != self._key
 
+    def reset_total(self):
+        self.total.zero_()
+
+    def set_lengths(self, lengths):
+        """New per-utterance lengths for the next replays (sorted descending, none above the captured T):
+        the kernels read the lengths from the device vector, so one captured step serves every batch of
+        its (B, T) shape; frames at t >= length are computed as padded frames and masked out of the
+        accumulators."""
+        L = [int(v) for v in lengths]
+        if len(L) != len(self.lengths) or L[0] > self.T or min(L) < 1 or any(a < b for a, b in zip(L, L[1:])):
+            raise RuntimeError(f"lengths must be {len(self.lengths)} values in [1, {self.T}] sorted in decreasing order")
+        self.lengths = L
+        self.lengths_dev.copy_(torch.as_tensor(L, dtype=torch.int32), non_blocking=True)
+
     def replay(self):
         if self.stale():
             # weights changed (optimizer step, load_state_dict, .to()): capture again with the current ones
             # (one eager step first, on a side stream, so that the weights are packed outside the capture)
             dev = self.tokens.device
+            keep = self.total.clone()
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream(dev))
             with torch.cuda.stream(side):
@@ -252,15 +362,71 @@ class GraphedEvaluator:
             torch.cuda.current_stream(dev).wait_stream(side)
             torch.cuda.synchronize(dev)
             self._capture()
+            self.total.copy_(keep)
         self.graph.replay()
         return self.result
 
-    def __call__(self, tokens=None, targets=None):
+    def __call__(self, tokens=None, targets=None, lengths=None):
         if tokens is not None:
             self.tokens.copy_(tokens, non_blocking=True)
         if targets is not None:
-            self.targets.copy_(targets, non_blocking=True)
+            self.targets.copy_(targets if targets.shape[1] == self.T else targets[:, :self.T], non_blocking=True)
+        if lengths is not None:
+            self.set_lengths(lengths)
         return self.replay()
+
+
+class PipelinedEvaluator:
+    """Evaluation of device-resident batches with ``depth`` steps in flight on ``depth`` streams.
+
+    A step is a chain of kernels that do not fill the machine one by one (the two recurrent layers run
+    2 x B/16 CTAs for T dependent time steps; the geometry kernels are fp32-pipe bound): with the next
+    step's chain on another stream the recurrent kernels of step i+1 run beside the geometry kernels of
+    step i.  Every slot owns its buffers and its running total; ``finish()`` joins the streams, adds
+    the slots' totals and sums them over ranks with ONE all-reduce per evaluation (run_test aggregates
+    once, evaluation.py:142-159)."""
+
+    def __init__(self, model, batch, seq_len, articulators=None, upper_incisor=None, depth=2):
+        dev = model.embedding.weight.device
+        self.model, self.device, self.depth = model, dev, depth
+        self.articulators = articulators
+        ui = synthetic.UPPER_INCISOR_REF if upper_incisor is None else upper_incisor
+        self.upper_incisor = ui.to(device=dev, dtype=torch.float32).contiguous()
+        self.buffers = [EvalBuffers(model, batch, seq_len, total=True) for _ in range(depth)]
+        least, greatest = torch.cuda.Stream.priority_range()
+        self.streams = [torch.cuda.Stream(device=dev, priority=greatest) for _ in range(depth)]
+        self.sides = [torch.cuda.Stream(device=dev, priority=least) for _ in range(depth)]
+        self.step_index = 0
+        self._fork = torch.cuda.Event()
+
+    def begin(self):
+        """Zero the running totals and order the slots' streams after the current stream."""
+        cur = torch.cuda.current_stream(self.device)
+        for b in self.buffers:
+            b.total.zero_()
+        self._fork.record(cur)
+        for s in self.streams:
+            s.wait_event(self._fork)
+        self.step_index = 0
+
+    def step(self, tokens, lengths, lengths_dev, targets):
+        """Enqueue one batch on the next slot's stream (returns at once)."""
+        k = self.step_index % self.depth
+        self.step_index += 1
+        with torch.cuda.stream(self.streams[k]):
+            return evaluate_step(self.model, tokens, lengths, lengths_dev, targets, self.buffers[k],
+                                 self.articulators, self.upper_incisor, self.sides[k])
+
+    def finish(self, reduce=True):
+        """Join the slots into the current stream; returns the evaluation's accumulator vector (summed over
+        the slots and, with ``reduce``, over the ranks - one all-reduce)."""
+        cur = torch.cuda.current_stream(self.device)
+        for s in self.streams:
+            cur.wait_stream(s)
+        total = self.buffers[0].total.clone()
+        for b in self.buffers[1:]:
+            total += b.total
+        return reduce_accumulators(total) if reduce else total
 
 
 class StreamedEvaluator:

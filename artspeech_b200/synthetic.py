@@ -56,25 +56,28 @@ def sorted_lengths(batch, lo, hi, seed=0):
     return torch.sort(L, descending=True).values.to(torch.int32)
 
 
-def contours(n_frames, n_articulators=10, n_samples=50, seed=0, noise=0.002):
+def contours(n_frames, n_articulators=10, n_samples=50, seed=0, noise=0.002, device=None):
     """(F, N, 2, D) fp32 arcs: centre U(0.3,0.7)^2, radius U(0.05,0.15), phase U(0,2pi),
-    point k at angle phase + 3k/(D-1), plus N(0, noise^2)."""
-    g = torch.Generator().manual_seed(seed)
+    point k at angle phase + 3k/(D-1), plus N(0, noise^2).  ``device``: generate there with that
+    device's generator (the million-frame workloads of bench.py; same law, other bytes)."""
+    dev = torch.device("cpu") if device is None else torch.device(device)
+    g = torch.Generator(device=dev).manual_seed(seed)
     F, N, D = n_frames, n_articulators, n_samples
-    c = 0.3 + 0.4 * torch.rand(F, N, 2, 1, generator=g)
-    r = 0.05 + 0.10 * torch.rand(F, N, 1, 1, generator=g)
-    ph = 2 * math.pi * torch.rand(F, N, 1, 1, generator=g)
-    k = torch.arange(D, dtype=torch.float32).view(1, 1, 1, D)
+    c = 0.3 + 0.4 * torch.rand(F, N, 2, 1, generator=g, device=dev)
+    r = 0.05 + 0.10 * torch.rand(F, N, 1, 1, generator=g, device=dev)
+    ph = 2 * math.pi * torch.rand(F, N, 1, 1, generator=g, device=dev)
+    k = torch.arange(D, dtype=torch.float32, device=dev).view(1, 1, 1, D)
     ang = ph + 3.0 * k / (D - 1)
     pts = torch.cat([torch.cos(ang), torch.sin(ang)], dim=2)
-    out = c + r * pts + noise * torch.randn(F, N, 2, D, generator=g)
+    out = c + r * pts + noise * torch.randn(F, N, 2, D, generator=g, device=dev)
     return out.to(torch.float32).contiguous()
 
 
 def perturbed(target, seed=1, sigma=0.01):
-    """A stand-in 'prediction' = target + N(0, sigma^2) when no model is run."""
-    g = torch.Generator().manual_seed(seed)
-    return (target + sigma * torch.randn(target.shape, generator=g)).to(torch.float32).contiguous()
+    """A stand-in 'prediction' = target + N(0, sigma^2) when no model is run (on the target's device)."""
+    g = torch.Generator(device=target.device).manual_seed(seed)
+    noise = torch.randn(target.shape, generator=g, device=target.device)
+    return (target + sigma * noise).to(torch.float32).contiguous()
 
 
 def inject_upper_incisor(x):
@@ -111,19 +114,20 @@ def _tract_path(u, rho, center=(0.5, 0.5)):
     return x, y
 
 
-def walls(n_frames, n_points=50, seed=0, noise=0.0005):
+def walls(n_frames, n_points=50, seed=0, noise=0.0005, device=None):
     """Internal and external vocal-tract walls, two (F, n_points, 2) fp32 tensors: a smooth open
     curve through the grid region at depth rho(u) = U(0.10,0.16) + U(0.01,0.04) sin(...), the
     external wall offset outward by U(0.02,0.05) +- 0.01 (so 0.01..0.06), both ends of each wall
     trimmed independently by U(0, 0.08) so that some grid lines meet only one wall, plus
     N(0, noise^2)."""
-    g = torch.Generator().manual_seed(seed)
+    dev = torch.device("cpu") if device is None else torch.device(device)
+    g = torch.Generator(device=dev).manual_seed(seed)
     F = n_frames
     total = _MOUTH_LEN + _ARC_LEN + _LARYNX_LEN
-    r = lambda lo, hi: lo + (hi - lo) * torch.rand(F, 1, generator=g, dtype=torch.float64)
+    r = lambda lo, hi: lo + (hi - lo) * torch.rand(F, 1, generator=g, dtype=torch.float64, device=dev)
     rho0, amp, freq, ph = r(0.10, 0.16), r(0.01, 0.04), r(0.5, 2.0), r(0.0, 2 * math.pi)
     off0, oamp, ofreq, oph = r(0.02, 0.05), r(0.0, 0.01), r(0.5, 3.0), r(0.0, 2 * math.pi)
-    k = torch.arange(n_points, dtype=torch.float64).view(1, -1) / (n_points - 1)
+    k = torch.arange(n_points, dtype=torch.float64, device=dev).view(1, -1) / (n_points - 1)
     out = []
     for is_ext in (False, True):
         u0, u1 = r(0.0, 0.08), total - r(0.0, 0.08)
@@ -133,7 +137,7 @@ def walls(n_frames, n_points=50, seed=0, noise=0.0005):
             rho = rho + off0 + oamp * torch.sin(2 * math.pi * ofreq * u / total + oph)
         x, y = _tract_path(u, rho)
         pts = torch.stack([x, y], dim=-1)
-        pts = pts + noise * torch.randn(pts.shape, generator=g, dtype=torch.float64)
+        pts = pts + noise * torch.randn(pts.shape, generator=g, dtype=torch.float64, device=dev)
         out.append(pts.to(torch.float32).contiguous())
     return out[0], out[1]
 

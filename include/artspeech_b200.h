@@ -144,6 +144,13 @@ ASB_API int asb_eval_accumulate(const float* p2cp, const float* tv_pred, const f
                         const int32_t* lengths_dev, int B, int T, int n_art, double* scratch,
                         double* acc, void* stream);
 
+/* Same, and the batch's vector is also ADDED into `total` (n_art+14 doubles, may be NULL; the caller zeroes it
+ * before the first batch): run_test aggregates over all batches ONCE at the end (evaluation.py:142-159), so a
+ * multi-GPU evaluation keeps this running sum on the device and all-reduces it once per evaluation. */
+ASB_API int asb_eval_accumulate_total(const float* p2cp, const float* tv_pred, const float* tv_target,
+                              const int32_t* lengths_dev, int B, int T, int n_art, double* scratch,
+                              double* acc, double* total, void* stream);
+
 /* The other per-sentence numbers of run_test (evaluation.py:68-84): outputs/targets
  * (B,T,n_art,2,n_points) fp32 planar, lengths_dev (B) DEVICE int32.  Per sentence and articulator:
  * the mean over valid frames of euclidean_distance (metrics.py:54-68) and, over the valid frames as
@@ -284,6 +291,29 @@ ASB_API int asb_gather_rows_flagged(const float* table, const int64_t* tokens, i
  * (for asb_gather_rows_flagged). */
 ASB_API int asb_model_token_status(asb_model* m, int32_t* bad_out, int64_t* token_out, int reset);
 ASB_API int32_t* asb_model_token_flag_ptr(asb_model* m);
+
+/* One evaluation step of run_test as one call (encoder_decoder/evaluation.py:53-128 with the frame driver
+ * phoneme_to_articulation/__init__.py:201-297 batched): forward -> P2CP of every (frame, articulator) ->
+ * tract variables of prediction and target -> length-masked accumulation.  All buffers are the caller's:
+ *   outputs (B,T,N,2,50) fp32; p2cp (B,T,N) fp32; tv_* (B,T,4) fp32 with idx (B,T,4,2) int32 and poc (B,T,4,2,2)
+ *   fp32 as asb_tract_variables; scratch B*(N+12) doubles; acc N+14 doubles (overwritten); total N+14 doubles or
+ *   NULL (added to, asb_eval_accumulate_total); workspace >= asb_model_workspace_bytes(m, B, T) bytes,
+ * with T = lengths_host[0].  tokens (B, T_in) int64; targets (B, T, N, 2, 50) fp32 CONTIGUOUS; lengths as for
+ * asb_model_forward_resident (lengths_dev required); art_index_host / upper_incisor / upper_incisor_stride as for
+ * asb_tract_variables_ex.  side_stream (may be NULL or == stream): the target's tract variables are forked onto
+ * it and joined before the accumulation, so that they run beside the forward pass.  Nothing synchronises. */
+typedef struct asb_eval_buffers {
+  float* outputs;
+  float* p2cp;
+  float* tv_pred; int32_t* tv_pred_idx; float* tv_pred_poc;
+  float* tv_target; int32_t* tv_target_idx; float* tv_target_poc;
+  double* scratch; double* acc; double* total;
+  void* workspace; size_t workspace_bytes;
+} asb_eval_buffers;
+ASB_API int asb_eval_step(asb_model* m, const int64_t* tokens, int T_in, const int32_t* lengths_host,
+                  const int32_t* lengths_dev, int B, const float* targets, const int32_t* art_index_host,
+                  const float* upper_incisor, int64_t upper_incisor_stride, const asb_eval_buffers* buffers,
+                  void* stream, void* side_stream);
 
 /* Decoder implementation: 1 = tcgen05/TMEM kernel (default in fast precision with n_samples = 50),
  * 0 = mma.sync kernel (always used in fp32 precision).  Both compute models.py:140-145.  The

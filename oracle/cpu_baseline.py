@@ -84,18 +84,77 @@ def evaluate_batch_cpu(sd, tokens, lengths, targets):
     return torch.stack(per_utt), tv_p, tv_t, frames
 
 
-def time_cpu_baseline(sd, batch, seq_len, repeats=1, seed=0, threads=None):
-    """Wall-clock frames/s of ``evaluate_batch_cpu`` on (batch, seq_len) synthetic utterances."""
+class ReferencePath:
+    """The reference's OWN code for the path, loaded by file path from the checkout or from the copies
+    staged under oracle/_ref/ (oracle/stage_ref.py): ``ArtSpeech`` (encoder_decoder/models.py:99-145),
+    ``p2cp_distance`` / ``euclidean_distance`` / ``pearsons_correlation`` (metrics.py:9-68) and
+    ``calculate_vocal_tract_variables`` (tract_variables.py:73-125), driven exactly like run_test's inner
+    loops (encoder_decoder/evaluation.py:53-84) and the frame driver
+    (phoneme_to_articulation/__init__.py:222-261)."""
+
+    def __init__(self, sd, vocab=45, n_art=10):
+        from oracle import reference_loader as ref
+        if not ref.baseline_available():
+            raise RuntimeError("neither /root/reference nor oracle/_ref is present")
+        self.metrics = ref.root_metrics()
+        self.tv = ref.tract_variables().calculate_vocal_tract_variables
+        self.net = ref.models().ArtSpeech(vocab, n_art).eval()
+        self.net.load_state_dict(sd)
+
+    @torch.no_grad()
+    def evaluate_batch(self, tokens, lengths, targets):
+        m = self.metrics
+        outputs = self.net(tokens, lengths)                                         # evaluation.py:57
+        targets = targets[:, :outputs.shape[1]]
+        per_utt = []
+        for so, st, L in zip(outputs, targets, lengths):                            # evaluation.py:68-84
+            so, st = so[:int(L)].unsqueeze(dim=0), st[:int(L)].unsqueeze(dim=0)
+            p2cp = m.p2cp_distance(so, st).mean(dim=1)
+            m.euclidean_distance(so, st).mean(dim=1)
+            x_corr, y_corr = m.pearsons_correlation(so, st)
+            x_corr.mean(dim=-1)[0], y_corr.mean(dim=-1)[0]
+            per_utt.append(p2cp[0])
+        out11 = synthetic.inject_upper_incisor(outputs)                             # evaluation.py:93-109
+        tgt11 = synthetic.inject_upper_incisor(targets)
+        names = synthetic.TV_ARTICULATORS
+        tv_p, tv_t, frames = [0.0] * 4, [0.0] * 4, 0
+        for so, st, L in zip(out11, tgt11, lengths):                                # __init__.py:222-261
+            for out, target in zip(so[:int(L)], st[:int(L)]):
+                a = self.tv({art: tensor.T for art, tensor in zip(names, out)})
+                b = self.tv({art: tensor.T for art, tensor in zip(names, target)})
+                for k, name in enumerate(("LA", "TTCD", "TBCD", "VEL")):
+                    tv_p[k] += a[name]["value"]
+                    tv_t[k] += b[name]["value"]
+                frames += 1
+        return torch.stack(per_utt), tv_p, tv_t, frames
+
+
+def make_evaluator(sd, prefer_reference=True):
+    """(kind, evaluate(tokens, lengths, targets)): the reference's own files when they are present
+    ("reference"), else the op-for-op port above ("port")."""
+    if prefer_reference:
+        try:
+            path = ReferencePath(sd)
+            return "reference", path.evaluate_batch
+        except Exception:
+            pass
+    return "port", lambda tokens, lengths, targets: evaluate_batch_cpu(sd, tokens, lengths, targets)
+
+
+def time_cpu_baseline(sd, batch, seq_len, repeats=1, seed=0, threads=None, prefer_reference=True):
+    """Wall-clock frames/s of the CPU evaluation of (batch, seq_len) synthetic utterances.
+    Returns (frames/s, seconds, kind)."""
     if threads:
         torch.set_num_threads(threads)
+    kind, evaluate = make_evaluator(sd, prefer_reference)
     tokens = synthetic.tokens(batch, seq_len, 45, seed=seed)
     lengths = [seq_len] * batch
     targets = synthetic.contours(batch * seq_len, 10, 50, seed=seed + 1).view(batch, seq_len, 10, 2, 50)
-    evaluate_batch_cpu(sd, tokens[:1, :8], [8], targets[:1, :8])  # warm-up of the op dispatch paths
+    evaluate(tokens[:1, :8], [8], targets[:1, :8])  # warm-up of the op dispatch paths
     best = None
     for _ in range(repeats):
         t0 = time.perf_counter()
-        evaluate_batch_cpu(sd, tokens, lengths, targets)
+        evaluate(tokens, lengths, targets)
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
-    return batch * seq_len / best, best
+    return batch * seq_len / best, best, kind

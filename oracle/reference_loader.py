@@ -19,14 +19,29 @@ import sys
 import types
 
 REFERENCE_ROOT = os.environ.get("ARTSPEECH_REFERENCE", "/root/reference")
+STAGED_ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
 
 
 def available():
+    """The full checkout is present (build container)."""
     return os.path.isfile(os.path.join(REFERENCE_ROOT, "tract_variables.py"))
 
 
+def baseline_available():
+    """The files the timed CPU baseline needs are present: the checkout, or the copies staged under
+    oracle/_ref/ by oracle/stage_ref.py (those travel to the GPU box)."""
+    if available():
+        return True
+    from oracle import stage_ref
+    return stage_ref.staged()
+
+
+def _root():
+    return REFERENCE_ROOT if available() else STAGED_ROOT
+
+
 def _load(name, relpath):
-    spec = importlib.util.spec_from_file_location(name, os.path.join(REFERENCE_ROOT, relpath))
+    spec = importlib.util.spec_from_file_location(name, os.path.join(_root(), relpath))
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     return mod
