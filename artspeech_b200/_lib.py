@@ -120,6 +120,24 @@ SIGNATURES = {
     "asb_model_token_status": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int32),
                                               ctypes.POINTER(ctypes.c_int64), ctypes.c_int]),
     "asb_model_token_flag_ptr": (ctypes.c_void_p, [ctypes.c_void_p]),
+    "asb_gemm": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int64,
+                                ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, _c_f32p, ctypes.c_int,
+                                ctypes.c_int, ctypes.c_void_p]),
+    "asb_colsum": (ctypes.c_int, [_c_f32p, ctypes.c_int64, ctypes.c_int, ctypes.c_int64, _c_f32p, ctypes.c_int,
+                                  ctypes.c_void_p]),
+    "asb_layernorm_fwd": (ctypes.c_int, [_c_f32p, ctypes.c_int64, ctypes.c_int, _c_f32p, _c_f32p, _c_f32p, _c_f32p,
+                                         _c_f32p, ctypes.c_void_p]),
+    "asb_layernorm_bwd": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, _c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_int,
+                                         _c_f32p, ctypes.c_int, _c_f32p, _c_f32p, ctypes.c_int, ctypes.c_void_p]),
+    "asb_sigmoid_bwd": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_void_p]),
+    "asb_relu_mask": (ctypes.c_int, [_c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_void_p]),
+    "asb_scatter_add_rows": (ctypes.c_int, [_c_f32p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_int,
+                                            _c_f32p, ctypes.c_void_p]),
+    "asb_dropout": (ctypes.c_int, [_c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_float, ctypes.c_uint64, ctypes.c_void_p]),
+    "asb_gru_train_forward": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int,
+                                             ctypes.c_int, ctypes.c_int, _c_f32p, _c_f32p, ctypes.c_void_p]),
+    "asb_gru_train_backward": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int,
+                                              ctypes.c_int, ctypes.c_int, _c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p]),
     "asb_model_set_decoder": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "asb_model_set_recurrent": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "asb_model_profile_enable": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),

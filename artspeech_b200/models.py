@@ -361,13 +361,23 @@ class ArtSpeech(nn.Module):
         Return:
             output (torch.tensor): (bs, max(lengths), n_articulators, 2, n_samples) float32
         """
-        if self.training and self.rnn.dropout > 0:
-            raise NotImplementedError("inter-layer dropout (train mode with dropout > 0) is not implemented")
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+        needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
+        drops = self.training and self.rnn.dropout > 0
+        if needs_grad or (drops and self._cell == _lib.CELL_GRU):
             if lengths_dev is not None or workspace is not None:
                 raise ValueError("lengths_dev / workspace are inference-only extensions")
             L = lengths.detach().cpu().tolist() if torch.is_tensor(lengths) else list(lengths)
-            return _TrainingForward.apply(self, x, [int(v) for v in L], *self.parameters())
+            L = [int(v) for v in L]
+            if self._cell == _lib.CELL_GRU:
+                # training (train_phoneme_to_articulation.py:84-96): forward with saved activations and
+                # hand-written backward kernels (artspeech_b200/training.py), dropout included
+                from .training import ArtSpeechTrainingFunction
+                return ArtSpeechTrainingFunction.apply(self, x, L, *self.parameters())
+            if self.training and self.rnn.dropout > 0:
+                raise NotImplementedError("inter-layer dropout is implemented for the GRU cell only")
+            return _TrainingForward.apply(self, x, L, *self.parameters())
+        if drops:
+            raise NotImplementedError("inter-layer dropout is implemented for the GRU cell only")
         return self._native_forward(x, lengths, lengths_dev, workspace)
 
     def workspace_bytes(self, batch, seq_len):
@@ -529,10 +539,10 @@ class SimpleArtSpeech(nn.Module):
         """x (bs, seq_len) int64 -> (bs, seq_len, n_articulators, 2, n_samples) float32 (models.py:84-96).
         Under autograd the values still come from the kernels and the backward pass differentiates a
         recomputed torch graph of the same parameters (``_TrainingForward``)."""
-        if self.training and self.dropout.p > 0:
-            raise NotImplementedError("dropout (train mode with dropout > 0) is not implemented")
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
-            return _TrainingForward.apply(self, x, lengths, *self.parameters())
+        needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
+        if needs_grad or (self.training and self.dropout.p > 0):
+            from .training import SimpleArtSpeechTrainingFunction
+            return SimpleArtSpeechTrainingFunction.apply(self, x, lengths, *self.parameters())
         return self._native_forward(x, lengths)
 
     def _library_graph(self, x, lengths=None):

@@ -315,6 +315,50 @@ ASB_API int asb_eval_step(asb_model* m, const int64_t* tokens, int T_in, const i
                   const float* upper_incisor, int64_t upper_incisor_stride, const asb_eval_buffers* buffers,
                   void* stream, void* side_stream);
 
+/* ------------------------------------------------------------------ training (row N2)
+ * train_phoneme_to_articulation.py:84-96 runs loss.backward() through the model.  The fused inference kernels
+ * save no activations; training runs an unfused fp32 path built from the primitives below (forward with saved
+ * activations + backward), composed by artspeech_b200/training.py.  All pointers are device fp32 unless noted. */
+
+/* C[i, j] (+)= sum_l A[i*a_i + l*a_l] * B[l*b_l + j*b_j] (+ bias[j]), i < M, j < N, l < K; C row stride ldc.
+ * act: 0 none, 1 ReLU, 2 sigmoid (applied after bias / accumulation).  The three forms of nn.Linear:
+ * y = x W^T + b (a_l = 1, b_l = 1, b_j = K), dx = dy W (b_l = K', b_j = 1), dW = dy^T x (a_i = 1, a_l = N'). */
+ASB_API int asb_gemm(const float* A, const float* B, float* C, int64_t M, int N, int K, int64_t a_i, int64_t a_l,
+             int64_t b_l, int64_t b_j, int64_t ldc, const float* bias, int act, int accumulate, void* stream);
+/* out[j] (+)= sum_i X[i*ldx + j]: bias gradients */
+ASB_API int asb_colsum(const float* X, int64_t M, int N, int64_t ldx, float* out, int accumulate, void* stream);
+/* nn.LayerNorm(C) forward over rows (biased variance, eps 1e-5; models.py:11,14,17): saves xhat (M,C), rstd (M) */
+ASB_API int asb_layernorm_fwd(const float* x, int64_t M, int C, const float* gamma, const float* beta, float* xhat,
+                      float* rstd, float* y, void* stream);
+/* its backward: dx (+)= rstd (g - mean g - xhat mean(g xhat)), g = dy gamma, zeroed where relu_src <= 0 (relu_src
+ * may be NULL); dgamma / dbeta (may be NULL) (+)= column sums.  dx may alias dy. */
+ASB_API int asb_layernorm_bwd(const float* dy, const float* xhat, const float* rstd, const float* gamma,
+                      const float* relu_src, int64_t M, int C, float* dx, int accumulate_dx, float* dgamma,
+                      float* dbeta, int accumulate_params, void* stream);
+ASB_API int asb_sigmoid_bwd(const float* dy, const float* y, float* dz, int64_t n, void* stream);   /* dz = dy y (1-y) */
+ASB_API int asb_relu_mask(float* dx, const float* f, int64_t n, void* stream);                     /* dx = 0 where f <= 0 */
+/* dst[tokens[r], :] += src[r, :]: gradient of nn.Embedding (models.py:110,135) */
+ASB_API int asb_scatter_add_rows(const float* src, const int64_t* tokens, int64_t rows, int width, int vocab,
+                         float* dst, void* stream);
+/* inverted dropout (nn.GRU(dropout=p) between the layers, models.py:111; nn.Dropout, models.py:65): out = x * keep /
+ * (1 - p) with keep drawn from a counter-based generator keyed by (seed, element index); calling it again on the
+ * gradient with the same seed applies the same mask. */
+ASB_API int asb_dropout(const float* x, float* out, int64_t n, float p, uint64_t seed, void* stream);
+/* One bidirectional GRU layer with packed-sequence semantics (models.py:111,136-138), training forward:
+ * gi (B*T, 2, 3H) = W_ih x + b_ih per direction; whh (3H, H), bhh (3H) as nn.GRU stores them; lengths_dev sorted
+ * descending.  out (B, T, 2H) must be zeroed by the caller (padded steps stay zero); gates (B*T, 2, 4, H) receives
+ * r, z, n and hn = W_hn h + b_hn of every valid step. */
+ASB_API int asb_gru_train_forward(const float* whh_fwd, const float* whh_bwd, const float* bhh_fwd, const float* bhh_bwd,
+                          const float* gi, const int32_t* lengths_dev, int B, int T, int hidden, float* out,
+                          float* gates, void* stream);
+/* BPTT through that layer: dout (B, T, 2H) gradient wrt its output -> dgi (B*T, 2, 3H) gradient wrt gi (= wrt b_ih
+ * rows), dgh (B*T, 2, 3H) gradient wrt W_hh h + b_hh, hprev (B*T, 2, H) the h each step started from; all three
+ * must be zeroed by the caller (padded steps stay zero).  Weight gradients follow as GEMMs over all steps:
+ * dW_ih = dgi^T x, dW_hh = dgh^T hprev, db_ih = colsum dgi, db_hh = colsum dgh, dx = dgi W_ih. */
+ASB_API int asb_gru_train_backward(const float* whh_fwd, const float* whh_bwd, const float* dout, const float* out,
+                           const float* gates, const int32_t* lengths_dev, int B, int T, int hidden, float* dgi,
+                           float* dgh, float* hprev, void* stream);
+
 /* Decoder implementation: 1 = tcgen05/TMEM kernel (default in fast precision with n_samples = 50),
  * 0 = mma.sync kernel (always used in fp32 precision).  Both compute models.py:140-145.  The
  * layer-1 input projection follows the same switch (tcgen05 proj_umma.cu / mma.sync linear256). */
