@@ -99,22 +99,22 @@ __global__ void __launch_bounds__(256) gemm_kernel(const GemmArgs a) {
   }
 }
 
-// out[j] (+)= sum_i X[i * ldx + j]
+// out[j] += sum_i X[i * ldx + j]  (out zeroed by the launcher unless accumulating); grid = (column tiles, row chunks)
 __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ X, long long M, int N, long long ldx,
-                                                     float* __restrict__ out, int accumulate) {
+                                                     float* __restrict__ out) {
   __shared__ float red[8][33];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int j = blockIdx.x * 32 + lane;
   float s = 0.f;
   if (j < N)
-    for (long long i = w; i < M; i += 8) s += X[i * ldx + j];
+    for (long long i = (long long)blockIdx.y * 8 + w; i < M; i += 8LL * gridDim.y) s += X[i * ldx + j];
   red[w][lane] = s;
   __syncthreads();
   if (w == 0 && j < N) {
     float t = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) t += red[k][lane];
-    out[j] = accumulate ? out[j] + t : t;
+    atomicAdd(out + j, t);
   }
 }
 
@@ -183,17 +183,17 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const float* __restr
     }
 }
 
-// dgamma[c] += sum_rows dy * xhat, dbeta[c] += sum_rows dy  (block = 32 columns x 8 row phases)
+// dgamma[c] += sum_rows dy * xhat, dbeta[c] += sum_rows dy  (grid = (column tiles, row chunks), outputs zeroed
+// by the launcher unless accumulating)
 __global__ void __launch_bounds__(256) layernorm_param_grad_kernel(const float* __restrict__ dy,
                                                                    const float* __restrict__ xhat, long long M, int C,
-                                                                   float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                                   int accumulate) {
+                                                                   float* __restrict__ dgamma, float* __restrict__ dbeta) {
   __shared__ float rg[8][33], rb[8][33];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + lane;
   float sg = 0.f, sb = 0.f;
   if (c < C)
-    for (long long i = w; i < M; i += 8) {
+    for (long long i = (long long)blockIdx.y * 8 + w; i < M; i += 8LL * gridDim.y) {
       const float d = dy[i * C + c];
       sg = fmaf(d, xhat[i * C + c], sg);
       sb += d;
@@ -208,8 +208,8 @@ __global__ void __launch_bounds__(256) layernorm_param_grad_kernel(const float* 
       tg += rg[k][lane];
       tb += rb[k][lane];
     }
-    dgamma[c] = accumulate ? dgamma[c] + tg : tg;
-    dbeta[c] = accumulate ? dbeta[c] + tb : tb;
+    atomicAdd(dgamma + c, tg);
+    atomicAdd(dbeta + c, tb);
   }
 }
 
@@ -425,7 +425,11 @@ extern "C" int asb_gemm(const float* A, const float* B, float* C, int64_t M, int
 extern "C" int asb_colsum(const float* X, int64_t M, int N, int64_t ldx, float* out, int accumulate, void* stream) {
   if (M < 0 || N <= 0) return asb::set_error(ASB_ERR_INVALID, "asb_colsum: bad shape");
   if (!X || !out) return asb::set_error(ASB_ERR_INVALID, "asb_colsum: null pointer");
-  colsum_kernel<<<(N + 31) / 32, 256, 0, static_cast<cudaStream_t>(stream)>>>(X, M, N, ldx, out, accumulate);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (!accumulate)
+    if (int rc = asb::check_cuda(cudaMemsetAsync(out, 0, sizeof(float) * N, st), "asb_colsum: memset")) return rc;
+  const unsigned chunks = unsigned(M >= 8192 ? 64 : (M + 127) / 128);
+  colsum_kernel<<<dim3((N + 31) / 32, chunks ? chunks : 1), 256, 0, st>>>(X, M, N, ldx, out);
   ASB_CHECK_LAUNCH("colsum_kernel");
   return ASB_OK;
 }
@@ -450,7 +454,12 @@ extern "C" int asb_layernorm_bwd(const float* dy, const float* xhat, const float
   if (!dy || !xhat || !rstd || !gamma || !dx) return asb::set_error(ASB_ERR_INVALID, "asb_layernorm_bwd: null pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dgamma && dbeta) {   // before dx: dx may alias dy
-    layernorm_param_grad_kernel<<<(C + 31) / 32, 256, 0, st>>>(dy, xhat, M, C, dgamma, dbeta, accumulate_params);
+    if (!accumulate_params) {
+      if (int rc = asb::check_cuda(cudaMemsetAsync(dgamma, 0, sizeof(float) * C, st), "asb_layernorm_bwd: memset")) return rc;
+      if (int rc = asb::check_cuda(cudaMemsetAsync(dbeta, 0, sizeof(float) * C, st), "asb_layernorm_bwd: memset")) return rc;
+    }
+    const unsigned chunks = unsigned(M >= 8192 ? 64 : (M + 127) / 128);
+    layernorm_param_grad_kernel<<<dim3((C + 31) / 32, chunks ? chunks : 1), 256, 0, st>>>(dy, xhat, M, C, dgamma, dbeta);
     ASB_CHECK_LAUNCH("layernorm_param_grad_kernel");
   }
   unsigned g;

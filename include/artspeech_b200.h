@@ -331,7 +331,7 @@ ASB_API int asb_colsum(const float* X, int64_t M, int N, int64_t ldx, float* out
 ASB_API int asb_layernorm_fwd(const float* x, int64_t M, int C, const float* gamma, const float* beta, float* xhat,
                       float* rstd, float* y, void* stream);
 /* its backward: dx (+)= rstd (g - mean g - xhat mean(g xhat)), g = dy gamma, zeroed where relu_src <= 0 (relu_src
- * may be NULL); dgamma / dbeta (may be NULL) (+)= column sums.  dx may alias dy. */
+ * may be NULL); dgamma / dbeta (may be NULL) (+)= column sums.  dx must not alias dy. */
 ASB_API int asb_layernorm_bwd(const float* dy, const float* xhat, const float* rstd, const float* gamma,
                       const float* relu_src, int64_t M, int C, float* dx, int accumulate_dx, float* dgamma,
                       float* dbeta, int accumulate_params, void* stream);
