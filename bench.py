@@ -174,10 +174,10 @@ def run_reference(args):
     from oracle import model as omodel
     from artspeech_b200 import synthetic
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
     sd = omodel.make_state_dict(VOCAB, N_ART, seed=0)
     kind, evaluate = cb.make_evaluator(sd)
+    # all host threads it can USE: the count (of those available) at which this path runs fastest
+    cores = cb.best_thread_count(evaluate, len(os.sched_getaffinity(0)) or os.cpu_count() or 1)
     sb, sl = args.ref_batch, args.seq_len
     tokens = synthetic.tokens(sb, sl, VOCAB, seed=0)
     lengths = [sl] * sb
@@ -526,8 +526,8 @@ def run_ours(args):
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import cpu_baseline as cb
-        cores = os.cpu_count() or 1
         sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+        cores = cb.best_thread_count(cb.make_evaluator(sd)[1], len(os.sched_getaffinity(0)) or os.cpu_count() or 1)
         v, secs, kind = cb.time_cpu_baseline(sd, args.cpu_batch, T, repeats=1, threads=cores)
         cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
                         "sample": f"{args.cpu_batch} utterances x {T} frames of the same workload ({secs:.1f} s of host "

@@ -141,12 +141,30 @@ def make_evaluator(sd, prefer_reference=True):
     return "port", lambda tokens, lengths, targets: evaluate_batch_cpu(sd, tokens, lengths, targets)
 
 
+def best_thread_count(evaluate, cores):
+    """The path is thousands of tiny torch ops (per-frame cdist / min / .item()): more intra-op threads can
+    make it SLOWER.  Try a few counts on a small sample and keep the fastest, so that the CPU gets its best."""
+    tokens = synthetic.tokens(1, 24, 45, seed=3)
+    targets = synthetic.contours(24, 10, 50, seed=4).view(1, 24, 10, 2, 50)
+    best, best_t = None, cores
+    for t in sorted({cores, max(1, cores // 2), min(cores, 4), 1}, reverse=True):
+        torch.set_num_threads(t)
+        evaluate(tokens[:, :4], [4], targets[:, :4])
+        t0 = time.perf_counter()
+        evaluate(tokens, [24], targets)
+        dt = time.perf_counter() - t0
+        if best is None or dt < best:
+            best, best_t = dt, t
+    torch.set_num_threads(best_t)
+    return best_t
+
+
 def time_cpu_baseline(sd, batch, seq_len, repeats=1, seed=0, threads=None, prefer_reference=True):
     """Wall-clock frames/s of the CPU evaluation of (batch, seq_len) synthetic utterances.
     Returns (frames/s, seconds, kind)."""
+    kind, evaluate = make_evaluator(sd, prefer_reference)
     if threads:
         torch.set_num_threads(threads)
-    kind, evaluate = make_evaluator(sd, prefer_reference)
     tokens = synthetic.tokens(batch, seq_len, 45, seed=seed)
     lengths = [seq_len] * batch
     targets = synthetic.contours(batch * seq_len, 10, 50, seed=seed + 1).view(batch, seq_len, 10, 2, 50)
