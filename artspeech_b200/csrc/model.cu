@@ -94,6 +94,7 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   const size_t o_head_w = p.take(sizeof(float) * N * kHeadPad * kFc), o_head_b = p.take(sizeof(float) * N * kHeadPad);
   const bool umma = umma_decoder_supported(m);
   const size_t o_umma = umma ? p.take(sizeof(float) * umma_image_floats(n_art)) : 0;
+  const size_t o_umma16 = umma ? p.take(sizeof(float) * umma16_image_floats(n_art)) : 0;
   const bool rnnu = rnn_umma_supported(m);
   size_t o_whhu[2][2] = {{0, 0}, {0, 0}};
   if (rnnu)
@@ -138,15 +139,17 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   w.ln2_w = F(o_ln2_w); w.ln2_b = F(o_ln2_b);
   w.head_w = F(o_head_w); w.head_b = F(o_head_b);
   w.umma_image = umma ? F(o_umma) : nullptr;
+  w.umma16_image = umma ? F(o_umma16) : nullptr;
   w.proj_image = proj ? F(o_proj) : nullptr;
   for (int l = 0; l < 2; ++l)
     for (int d = 0; d < 2; ++d) w.whh_umma[l][d] = rnnu ? static_cast<void*>(b + o_whhu[l][d]) : nullptr;
-  m->decoder_impl = umma ? 1 : 0;
+  m->decoder_impl = umma ? 2 : 0;   // fast precision: the fp16-operand tcgen05 decoder
   m->rnn_impl = rnnu ? 1 : 0;   // fast precision: the tcgen05 kernel (W_hh in tensor memory); the LSTM cell exists only there
 
   int rc = pack_recurrent_weights(m, src, st);
   if (!rc) rc = pack_dense_weights(m, src, st);
   if (!rc && umma) rc = pack_umma_image(m, src, st);
+  if (!rc && umma) rc = pack_umma16_image(m, src, st);
   if (!rc && proj) rc = pack_proj_image(m, st);
   if (!rc && rnnu) rc = pack_whh_umma(m, src, st);
   if (!rc) rc = check_cuda(cudaStreamSynchronize(st), "asb_model_create: packing kernels");
@@ -262,7 +265,7 @@ static int forward_impl(asb_model* m, const int64_t* x, int T_in, const int32_t*
     if ((rc = launch_recurrent_layer(m, 0, ws.gi, ws.lengths, ws.out0, B, T, st))) return rc;
   }
   mark(2);
-  if (m->w.proj_image && m->decoder_impl == 1) {  // the tcgen05 kernels are selected together
+  if (m->w.proj_image && m->decoder_impl >= 1) {  // the tcgen05 kernels are selected together
     if ((rc = launch_proj_umma(m, ws.out0, ws.gi, int(M), st))) return rc;
   } else {
     if ((rc = launch_linear(m, ws.out0, m->w.wih1, m->w.bih1, ws.gi, int(M), 2 * m->G * kH, 2 * kH, st))) return rc;
@@ -276,6 +279,8 @@ static int forward_impl(asb_model* m, const int64_t* x, int T_in, const int32_t*
   mark(4);
   if (hidden_only) {
     // nothing: `out` already holds the recurrent output
+  } else if (m->decoder_impl == 2) {
+    if ((rc = launch_decoder_umma16(m, ws.out1, out, int(M), st))) return rc;
   } else if (m->decoder_impl == 1) {
     if ((rc = launch_decoder_umma(m, ws.out1, out, int(M), st))) return rc;
   } else {
@@ -308,6 +313,7 @@ extern "C" int asb_model_decode(asb_model* m, const float* features, int64_t row
   if (reinterpret_cast<uintptr_t>(features) & 15)
     return set_error(ASB_ERR_INVALID, "asb_model_decode: features must be 16-byte aligned");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (m->decoder_impl == 2) return launch_decoder_umma16(m, features, out, int(rows), st);
   return m->decoder_impl == 1 ? launch_decoder_umma(m, features, out, int(rows), st)
                               : launch_decoder(m, features, out, int(rows), st);
 }
@@ -325,9 +331,9 @@ extern "C" int asb_model_set_recurrent(asb_model* m, int impl) {
 
 extern "C" int asb_model_set_decoder(asb_model* m, int impl) {
   if (!m) return set_error(ASB_ERR_INVALID, "asb_model_set_decoder: null model");
-  if (impl == 1 && !m->w.umma_image)
+  if (impl >= 1 && !m->w.umma_image)
     return set_error(ASB_ERR_UNSUPPORTED, "asb_model_set_decoder: the tcgen05 decoder needs fast precision and n_samples = 50");
-  if (impl != 0 && impl != 1) return set_error(ASB_ERR_INVALID, "asb_model_set_decoder: impl must be 0 or 1");
+  if (impl < 0 || impl > 2) return set_error(ASB_ERR_INVALID, "asb_model_set_decoder: impl must be 0, 1 or 2");
   m->decoder_impl = impl;
   return ASB_OK;
 }

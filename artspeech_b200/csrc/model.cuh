@@ -33,6 +33,8 @@ struct PackedWeights {
   float* head_w; float* head_b;   // [N][128][256] (x rows 0..D-1, y rows D..2D-1, rest zero), [N][128]
   // pre-swizzled tf32 weight image streamed by the tcgen05 decoder (decoder_umma.cu); fast mode only
   float* umma_image;
+  // the fp16-operand variant of that image (decoder_umma16.cu): half the bytes, kind::f16 at twice the tf32 rate
+  float* umma16_image;
   // pre-swizzled tf32 image of wih1 for the tcgen05 layer-1 projection (proj_umma.cu); fast mode only
   float* proj_image;
   // bf16 W_hh images (K-major, 128-byte swizzle) kept in shared memory by the tcgen05 recurrent
@@ -51,7 +53,7 @@ struct asb_model {
   size_t arena_bytes;
   asb::PackedWeights w;
   // optional per-stage timing (asb_model_profile_*): one event set per profiled forward
-  int decoder_impl = 0;  // 0 = mma.sync (decoder.cu), 1 = tcgen05/TMEM (decoder_umma.cu, proj_umma.cu)
+  int decoder_impl = 0;  // 0 = mma.sync (decoder.cu), 1 = tcgen05/TMEM tf32 (decoder_umma.cu, proj_umma.cu), 2 = tcgen05 fp16 operands (decoder_umma16.cu)
   int rnn_impl = 0;      // 0 = register-resident mma.sync / fp32 (gru.cu), 1 = tcgen05, W_hh in tensor memory (gru_umma.cu; fast-mode default)
   // out-of-range token ids (nn.Embedding raises IndexError, models.py:135): the kernels that read tokens
   // store {1, offending id} here and clamp; the word lives in mapped pinned host memory so that the host
@@ -89,6 +91,12 @@ size_t umma_image_floats(int n_art);
 bool umma_decoder_supported(const asb_model* m);
 int pack_umma_image(asb_model* m, const asb_weights* w, cudaStream_t st);
 int launch_decoder_umma(const asb_model* m, const float* rnn_out, float* out, int M, cudaStream_t st);
+
+// ---- tcgen05 decoder, fp16 operands (decoder_umma16.cu) -------------------------------
+size_t umma16_image_floats(int n_art);
+bool umma16_decoder_supported(const asb_model* m);
+int pack_umma16_image(asb_model* m, const asb_weights* w, cudaStream_t st);
+int launch_decoder_umma16(const asb_model* m, const float* rnn_out, float* out, int M, cudaStream_t st);
 
 // ---- tcgen05 layer-1 input projection (proj_umma.cu) --------------------------------
 size_t proj_image_floats(const asb_model* m);

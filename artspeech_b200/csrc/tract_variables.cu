@@ -375,32 +375,61 @@ static int tv_launch(const float* sets_ptr, int64_t sets, int n_art, const int32
     sg.n_slots = n;
     if (uinc != nullptr) sg.slot_pos[S_UINC] = n;   // its own slot after the set's contours (unused when shared)
   }
-  // 14 compute warps when five contours are staged per set (the shared upper incisor), 8 when six
+  // Compute warps per CTA (4 sets each): up to 14 when five contours are staged per set (the shared upper
+  // incisor), up to 8 when six (shared memory).  A CTA works in rounds of one set per team, so a mid-sized
+  // input is cut into ceil(groups / SMs) rounds: the warp count is chosen to minimise rounds x warps (e.g.
+  // 25 600 sets on 148 SMs: 11 warps = 4 rounds of 44 sets instead of 4 rounds of 56), larger counts winning ties.
   const int slots = sg.n_slots + ((uinc != nullptr && uinc_stride != 0) ? 1 : 0);
-  const bool wide = slots <= 5;
-  const size_t smem = wide ? tv_smem_bytes(14, slots) : tv_smem_bytes(8, slots);
+  const int max_nw = slots <= 5 ? 14 : 8;
+  const long long sms = (max_ctas > 0 && max_ctas < asb::sm_count()) ? max_ctas : asb::sm_count();
+  int nw = max_nw;
+  double best = 1e300;
+  for (int cand = max_nw; cand >= 8; --cand) {
+    const long long groups = (sets + cand * kTeamsPerWarp - 1) / (cand * kTeamsPerWarp);
+    const long long rounds = (groups + sms - 1) / sms;
+    const double cost = double(rounds) * cand * (1.0 + 0.015 * (max_nw - cand));
+    if (cost < best * 0.999) {
+      best = cost;
+      nw = cand;
+    }
+  }
+  const size_t smem = tv_smem_bytes(nw, slots);
   static asb::DeviceOnce once;
   if (int rc = once.run([&] {
-        cudaError_t e = cudaFuncSetAttribute(tract_variables_kernel<14>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             int(tv_smem_bytes(14, 5)));
-        if (e == cudaSuccess)
-          e = cudaFuncSetAttribute(tract_variables_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   int(tv_smem_bytes(8, 6)));
+        cudaError_t e = cudaSuccess;
+        auto opt_in = [&](auto kernel, int w) {
+          if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(tv_smem_bytes(w, w > 8 ? 5 : 6)));
+        };
+        opt_in(tract_variables_kernel<8>, 8);
+        opt_in(tract_variables_kernel<9>, 9);
+        opt_in(tract_variables_kernel<10>, 10);
+        opt_in(tract_variables_kernel<11>, 11);
+        opt_in(tract_variables_kernel<12>, 12);
+        opt_in(tract_variables_kernel<13>, 13);
+        opt_in(tract_variables_kernel<14>, 14);
         return asb::check_cuda(e, "asb_tract_variables: smem attribute");
       }))
     return rc;
-  const int per_group = (wide ? 14 : 8) * kTeamsPerWarp;
+  const int per_group = nw * kTeamsPerWarp;
   long long blocks = (sets + per_group - 1) / per_group;
-  const long long resident = asb::sm_count();   // persistent: one CTA per SM
-  if (blocks > resident) blocks = resident;
-  if (max_ctas > 0 && blocks > max_ctas) blocks = max_ctas;   // the groups are strided over whatever grid there is
+  if (blocks > sms) blocks = sms;   // persistent: one CTA per SM, the groups strided over whatever grid there is
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (wide)
-    tract_variables_kernel<14><<<unsigned(blocks), 15 * 32, smem, st>>>(sets_ptr, sets, n_art, sg, uinc, uinc_stride,
-                                                                       val, idx, poc);
-  else
-    tract_variables_kernel<8><<<unsigned(blocks), 9 * 32, smem, st>>>(sets_ptr, sets, n_art, sg, uinc, uinc_stride,
-                                                                     val, idx, poc);
+#define ASB_TV_LAUNCH(NW)                                                                                       \
+  case NW:                                                                                                      \
+    tract_variables_kernel<NW><<<unsigned(blocks), (NW + 1) * 32, smem, st>>>(sets_ptr, sets, n_art, sg, uinc,  \
+                                                                               uinc_stride, val, idx, poc);     \
+    break;
+  switch (nw) {
+    ASB_TV_LAUNCH(8)
+    ASB_TV_LAUNCH(9)
+    ASB_TV_LAUNCH(10)
+    ASB_TV_LAUNCH(11)
+    ASB_TV_LAUNCH(12)
+    ASB_TV_LAUNCH(13)
+    ASB_TV_LAUNCH(14)
+  }
+#undef ASB_TV_LAUNCH
   ASB_CHECK_LAUNCH("tract_variables_kernel");
   return ASB_OK;
 }

@@ -310,9 +310,10 @@ class ArtSpeech(nn.Module):
         self._native = None
 
     def set_decoder(self, impl):
-        """"tcgen05" (default in fast precision) or "mma" (mma.sync kernel) for the fused decoder."""
+        """"tcgen05" (fp16 operands, default in fast precision), "tcgen05-tf32" (the round-1 kernel) or "mma"
+        (mma.sync kernel) for the fused decoder."""
         dev = self.embedding.weight.device
-        code = {"tcgen05": 1, "mma": 0}[impl]
+        code = {"tcgen05": 2, "tcgen05-tf32": 1, "mma": 0}[impl]
         _lib.check(_lib.lib().asb_model_set_decoder(self._ensure_native(dev), code))
 
     def set_recurrent(self, impl):

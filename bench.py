@@ -447,10 +447,9 @@ def run_ours(args):
                          (peaks["tflops_sustained"] if v[0] == "tensor" else peaks["hbm_gbs"])) if v[2] > 0 else None
     roofline = {"kernel": top, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit,
                 "frac": achieved / peak if peak else None,
-                "frac_of_tf32_rate": (achieved / (0.5 * peak) if peak and bound == "tensor" else None),
                 "traffic": traffic, "traffic_source": traffic_source,
-                "peak_source": f"{peaks['source']} (dense bf16 cuBLAS sustained; this kernel computes in tf32, whose "
-                               f"tensor rate is half: frac_of_tf32_rate)" if bound == "tensor" else peaks["source"],
+                "peak_source": f"{peaks['source']} (dense bf16 cuBLAS sustained; the decoder's GEMMs are tcgen05 kind::f16 "
+                               f"with fp16 operands, the same tensor rate)" if bound == "tensor" else peaks["source"],
                 "ms_per_launch": ms,
                 "all_kernels_ms": {k: round(v[2], 4) for k, v in kernels.items()},
                 "all_kernels_frac": {k: (round(frac_of(v), 4) if frac_of(v) is not None else None)
@@ -540,7 +539,7 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None,
-            "dtype": "tf32/bf16 mma, fp32 accumulate" if args.precision == "fast" else "f32 (3xTF32)",
+            "dtype": "fp16/bf16 tcgen05 operands (tf32 layer-1 projection), fp32 accumulate and state" if args.precision == "fast" else "f32 (3xTF32)",
             "data": "synthetic",
             "config": workload_config(world, B, T, args.precision),
             "serial": serial,

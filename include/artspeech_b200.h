@@ -359,8 +359,8 @@ ASB_API int asb_gru_train_backward(const float* whh_fwd, const float* whh_bwd, c
                            const float* gates, const int32_t* lengths_dev, int B, int T, int hidden, float* dgi,
                            float* dgh, float* hprev, void* stream);
 
-/* Decoder implementation: 1 = tcgen05/TMEM kernel (default in fast precision with n_samples = 50),
- * 0 = mma.sync kernel (always used in fp32 precision).  Both compute models.py:140-145.  The
+/* Decoder implementation: 2 = tcgen05/TMEM kernel with fp16 operands (default in fast precision with
+ * n_samples = 50), 1 = the same with tf32 operands (round 1), 0 = mma.sync kernel (always used in fp32 precision).  Both compute models.py:140-145.  The
  * layer-1 input projection follows the same switch (tcgen05 proj_umma.cu / mma.sync linear256). */
 ASB_API int asb_model_set_decoder(asb_model* m, int impl);
 

@@ -237,6 +237,30 @@ def test_two_devices_in_one_process(mods):
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
 
 
+def test_decoder_implementations_agree(mods):
+    """The three fused decoders of fast precision - tcgen05 with fp16 operands (default), tcgen05 with tf32
+    operands (round 1) and mma.sync tf32 - against each other and the fp32 oracle, on a batch that leaves a
+    partly filled 128-frame tile and with perturbed LayerNorm affines."""
+    models, omodel = mods
+    sd = omodel.randomize_affine(omodel.make_state_dict(45, 10, seed=0), seed=9)
+    net = _build(models, sd, "fast")
+    B, T = 41, 37
+    x = synthetic.tokens(B, T, 45, seed=3)
+    L = synthetic.sorted_lengths(B, 5, T, seed=3)
+    want = omodel.artspeech_forward(sd, x[:8], L[:8], torch.float32)
+    outs = {}
+    for impl in ("tcgen05", "tcgen05-tf32", "mma"):
+        net.set_decoder(impl)
+        with torch.no_grad():
+            outs[impl] = net(x.cuda(), L).cpu()
+        err = (outs[impl][:8, :want.shape[1]] - want).abs().max().item()
+        print(f"decoder[{impl}] max-abs vs fp32 oracle {err:.3e}")
+        assert err <= TOL["fast"] and not torch.isnan(outs[impl]).any()
+    assert (outs["tcgen05"] - outs["tcgen05-tf32"]).abs().max().item() <= 1e-3
+    assert (outs["tcgen05"] - outs["mma"]).abs().max().item() <= 1e-3
+    net.set_decoder("tcgen05")
+
+
 def test_errors_and_state_dict(mods):
     models, omodel = mods
     sd = omodel.make_state_dict(45, 2, seed=0)
