@@ -138,6 +138,10 @@ SIGNATURES = {
                                              ctypes.c_int, ctypes.c_int, _c_f32p, _c_f32p, ctypes.c_void_p]),
     "asb_gru_train_backward": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int,
                                               ctypes.c_int, ctypes.c_int, _c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p]),
+    "asb_lstm_train_forward": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int,
+                                              ctypes.c_int, ctypes.c_int, _c_f32p, _c_f32p, ctypes.c_void_p]),
+    "asb_lstm_train_backward": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int,
+                                               ctypes.c_int, ctypes.c_int, _c_f32p, _c_f32p, ctypes.c_void_p]),
     "asb_model_set_decoder": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "asb_model_set_recurrent": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "asb_model_profile_enable": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),

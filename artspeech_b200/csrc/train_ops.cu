@@ -398,6 +398,165 @@ gru_train_bwd_kernel(const float* __restrict__ whh_fwd, const float* __restrict_
   }
 }
 
+// ---------------------------------------------------------------- LSTM layer, training forward / backward
+// nn.LSTM cell (gate rows i, f, g, o): c' = f c + i g, h' = o tanh(c').  W_hh (512 x 128 fp32 = 256 KB) does not fit
+// a CTA's shared memory: three gates' worth (192 KB) lives there and the remaining 128 values each thread needs sit
+// in its REGISTERS for the whole sequence (the trick of lstm_fp32_kernel, gru.cu).  gi holds W_ih x + b_ih; b_hh is
+// added here.  Saved per (row, step, direction, unit): i, f, g, o, and c' (5 values).
+constexpr int kLGH = 4 * kH;
+
+__global__ void __launch_bounds__(256, 1)
+lstm_train_fwd_kernel(const float* __restrict__ whh_fwd, const float* __restrict__ whh_bwd,
+                      const float* __restrict__ bhh_fwd, const float* __restrict__ bhh_bwd,
+                      const float* __restrict__ gi, const int* __restrict__ lengths, float* __restrict__ out,
+                      float* __restrict__ gates, int B, int T) {
+  extern __shared__ __align__(16) float smem[];
+  float* W = smem;                  // [k][384] = (W_hh^T) columns of gates i, f, g
+  float* hsm = smem + kH * kGH;     // [2][8][128]
+  const int tid = threadIdx.x, u = tid & (kH - 1), half = tid >> 7;
+  const int dir = blockIdx.y, b0 = blockIdx.x * 8;
+  const float* whh = dir ? whh_bwd : whh_fwd;   // (512, 128) row-major like nn.LSTM.weight_hh
+  const float* bhh = dir ? bhh_bwd : bhh_fwd;
+  for (int i = tid; i < kGH * kH; i += 256) {
+    const int g = i / kH, k = i - g * kH;
+    W[k * kGH + g] = whh[i];
+  }
+  float wo[kH];
+#pragma unroll
+  for (int k = 0; k < kH; ++k) wo[k] = __ldg(whh + (size_t)(3 * kH + u) * kH + k);
+  const float bi = bhh[u], bf = bhh[kH + u], bg = bhh[2 * kH + u], bo = bhh[3 * kH + u];
+  for (int i = tid; i < 2 * 8 * kH; i += 256) hsm[i] = 0.f;
+  int len[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int b = b0 + 4 * half + r;
+    len[r] = b < B ? lengths[b] : 0;
+  }
+  const int Lmax = lengths[b0];
+  float h[4] = {0.f, 0.f, 0.f, 0.f}, c[4] = {0.f, 0.f, 0.f, 0.f};
+  __syncthreads();
+  int cur = 0;
+  for (int s = 0; s < Lmax; ++s) {
+    const int t = dir ? Lmax - 1 - s : s;
+    float ai[4] = {bi, bi, bi, bi}, af[4] = {bf, bf, bf, bf}, ag[4] = {bg, bg, bg, bg}, ao[4] = {bo, bo, bo, bo};
+    const float* hc = hsm + cur * 8 * kH + 4 * half * kH;
+#pragma unroll
+    for (int k = 0; k < kH; k += 4) {
+      float4 hv[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) hv[r] = *reinterpret_cast<const float4*>(hc + r * kH + k);
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        const float wi = W[(k + kk) * kGH + u], wf = W[(k + kk) * kGH + kH + u], wg = W[(k + kk) * kGH + 2 * kH + u];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float hk = kk == 0 ? hv[r].x : kk == 1 ? hv[r].y : kk == 2 ? hv[r].z : hv[r].w;
+          ai[r] = fmaf(wi, hk, ai[r]);
+          af[r] = fmaf(wf, hk, af[r]);
+          ag[r] = fmaf(wg, hk, ag[r]);
+          ao[r] = fmaf(wo[k + kk], hk, ao[r]);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      if (t < len[r]) {
+        const long long bt = (long long)(b0 + 4 * half + r) * T + t;
+        const float* p = gi + (bt * 2 + dir) * kLGH + u;
+        const float ig = 1.f / (1.f + expf(-(p[0] + ai[r])));
+        const float fg = 1.f / (1.f + expf(-(p[kH] + af[r])));
+        const float gg = tanhf(p[2 * kH] + ag[r]);
+        const float og = 1.f / (1.f + expf(-(p[3 * kH] + ao[r])));
+        c[r] = fg * c[r] + ig * gg;
+        h[r] = og * tanhf(c[r]);
+        out[bt * (2 * kH) + dir * kH + u] = h[r];
+        float* gs = gates + (bt * 2 + dir) * 5 * kH + u;
+        gs[0] = ig; gs[kH] = fg; gs[2 * kH] = gg; gs[3 * kH] = og; gs[4 * kH] = c[r];
+      }
+      hsm[(cur ^ 1) * 8 * kH + (4 * half + r) * kH + u] = h[r];
+    }
+    __syncthreads();
+    cur ^= 1;
+  }
+}
+
+// BPTT through one LSTM layer.  Rows i, f, g of W_hh (384 x 128) in shared memory, row block o (128 x 128): thread u
+// keeps COLUMN u of it (W_hh[384 + g][u], g < 128) in registers.  Per step: local derivatives -> dgi (= dgh: every
+// gate pre-activation is gi + W_hh h + b_hh) to global and to shared memory, then dh_prev = dpre . W_hh and
+// dc_prev = dc f.  cprev of a step is the saved c' of the step the forward pass came from.
+__global__ void __launch_bounds__(256, 1)
+lstm_train_bwd_kernel(const float* __restrict__ whh_fwd, const float* __restrict__ whh_bwd,
+                      const float* __restrict__ dout, const float* __restrict__ out, const float* __restrict__ gates,
+                      const int* __restrict__ lengths, float* __restrict__ dgi, float* __restrict__ hprev, int B, int T) {
+  extern __shared__ __align__(16) float smem[];
+  float* W = smem;                  // [g < 384][128]
+  float* gsm = smem + kGH * kH;     // [8][512] dpre of the current step
+  const int tid = threadIdx.x, u = tid & (kH - 1), half = tid >> 7;
+  const int dir = blockIdx.y, b0 = blockIdx.x * 8;
+  const float* whh = dir ? whh_bwd : whh_fwd;
+  for (int i = tid; i < kGH * kH / 4; i += 256)
+    reinterpret_cast<float4*>(W)[i] = __ldg(reinterpret_cast<const float4*>(whh) + i);
+  float wo[kH];
+#pragma unroll
+  for (int g = 0; g < kH; ++g) wo[g] = __ldg(whh + (size_t)(3 * kH + g) * kH + u);
+  int len[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int b = b0 + 4 * half + r;
+    len[r] = b < B ? lengths[b] : 0;
+  }
+  const int Lmax = lengths[b0];
+  float dh[4] = {0.f, 0.f, 0.f, 0.f}, dc[4] = {0.f, 0.f, 0.f, 0.f};
+  __syncthreads();
+  for (int s = 0; s < Lmax; ++s) {
+    const int t = dir ? s : Lmax - 1 - s;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      float d_i = 0.f, d_f = 0.f, d_g = 0.f, d_o = 0.f;
+      if (t < len[r]) {
+        const long long row = b0 + 4 * half + r;
+        const long long bt = row * T + t;
+        const int tp = dir ? t + 1 : t - 1;
+        const bool has_prev = tp >= 0 && tp < len[r];
+        const float hp = has_prev ? out[(row * T + tp) * (2 * kH) + dir * kH + u] : 0.f;
+        const float cp = has_prev ? gates[((row * T + tp) * 2 + dir) * 5 * kH + 4 * kH + u] : 0.f;
+        const float* gs = gates + (bt * 2 + dir) * 5 * kH + u;
+        const float ig = gs[0], fg = gs[kH], gg = gs[2 * kH], og = gs[3 * kH], cn = gs[4 * kH];
+        const float tc = tanhf(cn);
+        const float dht = dh[r] + dout[bt * (2 * kH) + dir * kH + u];
+        const float dct = dc[r] + dht * og * (1.f - tc * tc);
+        d_o = dht * tc * og * (1.f - og);
+        d_i = dct * gg * ig * (1.f - ig);
+        d_f = dct * cp * fg * (1.f - fg);
+        d_g = dct * ig * (1.f - gg * gg);
+        dc[r] = dct * fg;
+        float* o1 = dgi + (bt * 2 + dir) * kLGH + u;
+        o1[0] = d_i; o1[kH] = d_f; o1[2 * kH] = d_g; o1[3 * kH] = d_o;
+        hprev[(bt * 2 + dir) * kH + u] = hp;
+      }
+      float* g = gsm + (4 * half + r) * kLGH + u;
+      g[0] = d_i; g[kH] = d_f; g[2 * kH] = d_g; g[3 * kH] = d_o;
+    }
+    __syncthreads();
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const float* gr = gsm + 4 * half * kLGH;
+#pragma unroll 4
+    for (int g = 0; g < kGH; ++g) {
+      const float w = W[g * kH + u];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) acc[r] = fmaf(gr[r * kLGH + g], w, acc[r]);
+    }
+#pragma unroll
+    for (int g = 0; g < kH; ++g) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r) acc[r] = fmaf(gr[r * kLGH + 3 * kH + g], wo[g], acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) dh[r] = (t < len[r]) ? acc[r] : dh[r];
+    __syncthreads();
+  }
+}
+
 int grid_1d(long long n, int block, unsigned* out) {
   const long long blocks = (n + block - 1) / block;
   if (blocks > 0x7fffffffLL) return asb::set_error(ASB_ERR_INVALID, "too many elements");
@@ -550,5 +709,47 @@ extern "C" int asb_gru_train_backward(const float* whh_fwd, const float* whh_bwd
   gru_train_bwd_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(whh_fwd, whh_bwd, dout, out, gates,
                                                                               lengths_dev, dgi, dgh, hprev, B, T);
   ASB_CHECK_LAUNCH("gru_train_bwd_kernel");
+  return ASB_OK;
+}
+
+extern "C" int asb_lstm_train_forward(const float* whh_fwd, const float* whh_bwd, const float* bhh_fwd,
+                                      const float* bhh_bwd, const float* gi, const int32_t* lengths_dev, int B, int T,
+                                      int hidden, float* out, float* gates, void* stream) {
+  if (hidden != kH) return asb::set_error(ASB_ERR_UNSUPPORTED, "asb_lstm_train_forward: hidden_size must be %d", kH);
+  if (B <= 0 || T <= 0) return asb::set_error(ASB_ERR_INVALID, "asb_lstm_train_forward: empty batch");
+  if (!whh_fwd || !whh_bwd || !bhh_fwd || !bhh_bwd || !gi || !lengths_dev || !out || !gates)
+    return asb::set_error(ASB_ERR_INVALID, "asb_lstm_train_forward: null pointer");
+  const int smem = (kH * kGH + 2 * 8 * kH) * int(sizeof(float));
+  static asb::DeviceOnce once;
+  if (int rc = once.run([&] {
+        return asb::check_cuda(cudaFuncSetAttribute(lstm_train_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
+                               "lstm_train_fwd_kernel smem attribute");
+      }))
+    return rc;
+  dim3 grid((B + 7) / 8, 2);
+  lstm_train_fwd_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(whh_fwd, whh_bwd, bhh_fwd, bhh_bwd, gi,
+                                                                               lengths_dev, out, gates, B, T);
+  ASB_CHECK_LAUNCH("lstm_train_fwd_kernel");
+  return ASB_OK;
+}
+
+extern "C" int asb_lstm_train_backward(const float* whh_fwd, const float* whh_bwd, const float* dout, const float* out,
+                                       const float* gates, const int32_t* lengths_dev, int B, int T, int hidden,
+                                       float* dgi, float* hprev, void* stream) {
+  if (hidden != kH) return asb::set_error(ASB_ERR_UNSUPPORTED, "asb_lstm_train_backward: hidden_size must be %d", kH);
+  if (B <= 0 || T <= 0) return asb::set_error(ASB_ERR_INVALID, "asb_lstm_train_backward: empty batch");
+  if (!whh_fwd || !whh_bwd || !dout || !out || !gates || !lengths_dev || !dgi || !hprev)
+    return asb::set_error(ASB_ERR_INVALID, "asb_lstm_train_backward: null pointer");
+  const int smem = (kGH * kH + 8 * kLGH) * int(sizeof(float));
+  static asb::DeviceOnce once;
+  if (int rc = once.run([&] {
+        return asb::check_cuda(cudaFuncSetAttribute(lstm_train_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
+                               "lstm_train_bwd_kernel smem attribute");
+      }))
+    return rc;
+  dim3 grid((B + 7) / 8, 2);
+  lstm_train_bwd_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(whh_fwd, whh_bwd, dout, out, gates,
+                                                                               lengths_dev, dgi, hprev, B, T);
+  ASB_CHECK_LAUNCH("lstm_train_bwd_kernel");
   return ASB_OK;
 }

@@ -8,9 +8,9 @@ The torch submodules below are only PARAMETER CONTAINERS: they give identical in
 (same RNG consumption order as the reference constructor, models.py:109-120), identical
 ``state_dict`` keys, ``.to(device)`` and ``.parameters()``; the forward pass never calls their own
 ``forward`` and there is no CPU or eager fallback for it.  With autograd enabled (training,
-train_phoneme_to_articulation.py:84-96) the forward values still come from the kernels and the
-backward pass differentiates a recomputed torch graph of the same parameters (library code, see
-``_TrainingForward``); hand-written backward kernels are SURVEY.md row N2.
+train_phoneme_to_articulation.py:84-96) the module runs the unfused fp32 training path of
+``artspeech_b200/training.py``: a forward that saves its activations and hand-written backward kernels
+(GRU and LSTM cell, dropout included; no cuDNN / cuBLAS).
 """
 from __future__ import annotations
 
@@ -58,7 +58,7 @@ class _PredictorHandle:
 
 class _PredictorForward(torch.autograd.Function):
     """Standalone predictor under autograd: values from the kernel, gradient through the torch graph of
-    the same parameters (library code, like ``_TrainingForward``)."""
+    the same parameters (library code: this standalone use is the transformer model's, outside the hot path)."""
 
     @staticmethod
     def forward(ctx, module, inputs, *params):
@@ -165,7 +165,7 @@ class ArticulatorPredictor(nn.Module):
     def _graph(self, inputs):
         """models.py:23-33 as a differentiable torch graph.  The forward pass never comes here (the
         predictors are evaluated inside the fused CUDA decoder); this graph exists only for the backward
-        pass of training, which re-derives the activations with autograd (see ``_TrainingForward``)."""
+        pass of the standalone predictor (``_PredictorForward``) and as the fp64 truth in the gradient tests."""
         linear_out = self.linear(inputs)
         return torch.stack([self.x_coords(linear_out), self.y_coords(linear_out)], dim=2)
 
@@ -184,35 +184,6 @@ class _NativeHandle:
         except Exception:
             pass
         self.ptr = None
-
-
-class _TrainingForward(torch.autograd.Function):
-    """Forward = the native kernels (same values as in evaluation); backward = autograd through a
-    recomputed torch graph of the same module (``ArtSpeech._library_graph``: cuDNN GRU + cuBLAS
-    linears), i.e. the gradient of the fp32 model at the current parameters.  This is what lets
-    train_phoneme_to_articulation.py:84-96 run on the drop-in module; hand-written backward kernels
-    (BPTT through the resident-W_hh recurrent kernel, fused decoder backward) are SURVEY.md row N2 and
-    are not built - the backward pass is library code and is not counted in any benchmark."""
-
-    @staticmethod
-    def forward(ctx, module, x, lengths, *params):
-        ctx.module, ctx.x, ctx.lengths = module, x, lengths
-        ctx.n_params = len(params)
-        with torch.no_grad():
-            return module._native_forward(x, lengths)
-
-    @staticmethod
-    def backward(ctx, grad_out):
-        module = ctx.module
-        params = [p for p in module.parameters()]
-        # fp32 precision: keep cuDNN's recurrent GEMMs out of TF32 so the gradient is the fp32 one
-        tf32 = module.precision != "fp32"
-        with torch.enable_grad(), torch.backends.cudnn.flags(enabled=True, allow_tf32=tf32):
-            out = module._library_graph(ctx.x, ctx.lengths)
-            need = [p for p in params if p.requires_grad]
-            grads = torch.autograd.grad(out, need, grad_out.to(out.dtype), allow_unused=True)
-        it = iter(grads)
-        return (None, None, None) + tuple(next(it) if p.requires_grad else None for p in params)
 
 
 class ArtSpeech(nn.Module):
@@ -364,21 +335,15 @@ class ArtSpeech(nn.Module):
         """
         needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
         drops = self.training and self.rnn.dropout > 0
-        if needs_grad or (drops and self._cell == _lib.CELL_GRU):
+        if needs_grad or drops:
             if lengths_dev is not None or workspace is not None:
                 raise ValueError("lengths_dev / workspace are inference-only extensions")
             L = lengths.detach().cpu().tolist() if torch.is_tensor(lengths) else list(lengths)
             L = [int(v) for v in L]
-            if self._cell == _lib.CELL_GRU:
-                # training (train_phoneme_to_articulation.py:84-96): forward with saved activations and
-                # hand-written backward kernels (artspeech_b200/training.py), dropout included
-                from .training import ArtSpeechTrainingFunction
-                return ArtSpeechTrainingFunction.apply(self, x, L, *self.parameters())
-            if self.training and self.rnn.dropout > 0:
-                raise NotImplementedError("inter-layer dropout is implemented for the GRU cell only")
-            return _TrainingForward.apply(self, x, L, *self.parameters())
-        if drops:
-            raise NotImplementedError("inter-layer dropout is implemented for the GRU cell only")
+            # training (train_phoneme_to_articulation.py:84-96): forward with saved activations and
+            # hand-written backward kernels (artspeech_b200/training.py), GRU and LSTM cell, dropout included
+            from .training import ArtSpeechTrainingFunction
+            return ArtSpeechTrainingFunction.apply(self, x, L, *self.parameters())
         return self._native_forward(x, lengths, lengths_dev, workspace)
 
     def workspace_bytes(self, batch, seq_len):
@@ -538,8 +503,8 @@ class SimpleArtSpeech(nn.Module):
 
     def forward(self, x, lengths=None):
         """x (bs, seq_len) int64 -> (bs, seq_len, n_articulators, 2, n_samples) float32 (models.py:84-96).
-        Under autograd the values still come from the kernels and the backward pass differentiates a
-        recomputed torch graph of the same parameters (``_TrainingForward``)."""
+        Under autograd (or in train mode with dropout) it runs the native training path
+        (``training.SimpleArtSpeechTrainingFunction``)."""
         needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
         if needs_grad or (self.training and self.dropout.p > 0):
             from .training import SimpleArtSpeechTrainingFunction

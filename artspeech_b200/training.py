@@ -165,46 +165,55 @@ def _gru_params(rnn, layer):
     return out
 
 
-def gru_layer_forward(x, rnn, layer, lengths_dev, B, T):
-    """x (M, in) -> out (M, 2H) with packed-sequence semantics; returns (out, gi, gates)."""
+def rnn_layer_forward(x, rnn, layer, lengths_dev, B, T):
+    """One bidirectional nn.GRU / nn.LSTM layer: x (M, in) -> out (M, 2H) with packed-sequence semantics;
+    returns (out, gates)."""
     M = x.shape[0]
     H = rnn.hidden_size
+    G = 4 if isinstance(rnn, torch.nn.LSTM) else 3
     dev = x.device
     (wih_f, whh_f, bih_f, bhh_f), (wih_b, whh_b, bih_b, bhh_b) = _gru_params(rnn, layer)
-    gi = torch.empty(M, 2, 3 * H, dtype=_F32, device=dev)
-    flat = gi.view(M, 6 * H)
-    linear_forward(x, wih_f, bih_f, flat[:, :3 * H])
-    linear_forward(x, wih_b, bih_b, flat[:, 3 * H:])
+    gi = torch.empty(M, 2, G * H, dtype=_F32, device=dev)
+    flat = gi.view(M, 2 * G * H)
+    linear_forward(x, wih_f, bih_f, flat[:, :G * H])
+    linear_forward(x, wih_b, bih_b, flat[:, G * H:])
     out = torch.zeros(M, 2 * H, dtype=_F32, device=dev)
-    gates = torch.empty(M, 2, 4, H, dtype=_F32, device=dev)
-    _lib.check(_lib.lib().asb_gru_train_forward(_lib.ptr(whh_f), _lib.ptr(whh_b), _lib.ptr(bhh_f), _lib.ptr(bhh_b),
-                                                _lib.ptr(gi), _lib.ptr(lengths_dev), B, T, H, _lib.ptr(out),
-                                                _lib.ptr(gates), _st(dev)))
+    gates = torch.empty(M, 2, G + 1, H, dtype=_F32, device=dev)
+    fn = _lib.lib().asb_lstm_train_forward if G == 4 else _lib.lib().asb_gru_train_forward
+    _lib.check(fn(_lib.ptr(whh_f), _lib.ptr(whh_b), _lib.ptr(bhh_f), _lib.ptr(bhh_b), _lib.ptr(gi), _lib.ptr(lengths_dev),
+                  B, T, H, _lib.ptr(out), _lib.ptr(gates), _st(dev)))
     return out, gates
 
 
-def gru_layer_backward(d_out, x, out, gates, rnn, layer, lengths_dev, B, T, grads, need_dx=True):
+def rnn_layer_backward(d_out, x, out, gates, rnn, layer, lengths_dev, B, T, grads, need_dx=True):
     """BPTT through one bidirectional layer.  Returns the gradient wrt its input x (M, in) (or None)."""
     M = x.shape[0]
     H = rnn.hidden_size
+    G = 4 if isinstance(rnn, torch.nn.LSTM) else 3
     dev = x.device
     lib = _lib.lib()
     params = _gru_params(rnn, layer)
-    dgi = torch.zeros(M, 2, 3 * H, dtype=_F32, device=dev)
-    dgh = torch.zeros(M, 2, 3 * H, dtype=_F32, device=dev)
+    dgi = torch.zeros(M, 2, G * H, dtype=_F32, device=dev)
     hprev = torch.zeros(M, 2, H, dtype=_F32, device=dev)
-    _lib.check(lib.asb_gru_train_backward(_lib.ptr(params[0][1]), _lib.ptr(params[1][1]), _lib.ptr(d_out), _lib.ptr(out),
-                                          _lib.ptr(gates), _lib.ptr(lengths_dev), B, T, H, _lib.ptr(dgi), _lib.ptr(dgh),
-                                          _lib.ptr(hprev), _st(dev)))
-    dgi2, dgh2, hp2 = dgi.view(M, 6 * H), dgh.view(M, 6 * H), hprev.view(M, 2 * H)
+    if G == 4:
+        dgh = dgi            # every LSTM gate pre-activation is gi + W_hh h + b_hh
+        _lib.check(lib.asb_lstm_train_backward(_lib.ptr(params[0][1]), _lib.ptr(params[1][1]), _lib.ptr(d_out),
+                                               _lib.ptr(out), _lib.ptr(gates), _lib.ptr(lengths_dev), B, T, H,
+                                               _lib.ptr(dgi), _lib.ptr(hprev), _st(dev)))
+    else:
+        dgh = torch.zeros(M, 2, G * H, dtype=_F32, device=dev)
+        _lib.check(lib.asb_gru_train_backward(_lib.ptr(params[0][1]), _lib.ptr(params[1][1]), _lib.ptr(d_out),
+                                              _lib.ptr(out), _lib.ptr(gates), _lib.ptr(lengths_dev), B, T, H,
+                                              _lib.ptr(dgi), _lib.ptr(dgh), _lib.ptr(hprev), _st(dev)))
+    dgi2, dgh2, hp2 = dgi.view(M, 2 * G * H), dgh.view(M, 2 * G * H), hprev.view(M, 2 * H)
     dx = torch.empty_like(x) if need_dx else None
     for d, (wih, whh, bih, bhh) in enumerate(params):
-        gi_d, gh_d, hp_d = dgi2[:, d * 3 * H:(d + 1) * 3 * H], dgh2[:, d * 3 * H:(d + 1) * 3 * H], hp2[:, d * H:(d + 1) * H]
+        gi_d, gh_d, hp_d = dgi2[:, d * G * H:(d + 1) * G * H], dgh2[:, d * G * H:(d + 1) * G * H], hp2[:, d * H:(d + 1) * H]
         grads[id(wih)] = linear_backward_weight(gi_d, x, torch.empty_like(wih), None)
         grads[id(whh)] = linear_backward_weight(gh_d, hp_d, torch.empty_like(whh), None)
         gb_i, gb_h = torch.empty_like(bih), torch.empty_like(bhh)
-        _lib.check(lib.asb_colsum(_lib.ptr(gi_d), M, 3 * H, _ld(gi_d), _lib.ptr(gb_i), 0, _st(dev)))
-        _lib.check(lib.asb_colsum(_lib.ptr(gh_d), M, 3 * H, _ld(gh_d), _lib.ptr(gb_h), 0, _st(dev)))
+        _lib.check(lib.asb_colsum(_lib.ptr(gi_d), M, G * H, _ld(gi_d), _lib.ptr(gb_i), 0, _st(dev)))
+        _lib.check(lib.asb_colsum(_lib.ptr(gh_d), M, G * H, _ld(gh_d), _lib.ptr(gb_h), 0, _st(dev)))
         grads[id(bih)], grads[id(bhh)] = gb_i, gb_h
         if need_dx:
             linear_backward_input(gi_d, wih, dx, accumulate=d > 0)
@@ -257,11 +266,11 @@ class ArtSpeechTrainingFunction(torch.autograd.Function):
         n_art, d = module._dims[1], module._dims[4]
         with torch.cuda.device(dev):
             emb = _embedding_forward(module.embedding.weight, tok)
-            out0, gates0 = gru_layer_forward(emb, module.rnn, 0, ldev, B, T)
+            out0, gates0 = rnn_layer_forward(emb, module.rnn, 0, ldev, B, T)
             p_drop = float(module.rnn.dropout) if module.training else 0.0
             seed = _fresh_seed() if p_drop > 0 else 0
             in1 = dropout(out0, p_drop, seed) if p_drop > 0 else out0
-            out1, gates1 = gru_layer_forward(in1, module.rnn, 1, ldev, B, T)
+            out1, gates1 = rnn_layer_forward(in1, module.rnn, 1, ldev, B, T)
             lin = module.linear[0]
             hidden = linear_forward(out1, lin.weight, lin.bias, torch.empty(M, lin.weight.shape[0], dtype=_F32, device=dev), act=1)
             y = torch.empty(B, T, n_art, 2, d, dtype=_F32, device=dev)
@@ -289,9 +298,9 @@ class ArtSpeechTrainingFunction(torch.autograd.Function):
             linear_backward_weight(d_hidden, out1, gw, gb)
             grads[id(lin.weight)], grads[id(lin.bias)] = gw, gb
             d_out1 = linear_backward_input(d_hidden, lin.weight, torch.empty_like(out1))
-            d_in1 = gru_layer_backward(d_out1, in1, out1, gates1, module.rnn, 1, ldev, B, T, grads)
+            d_in1 = rnn_layer_backward(d_out1, in1, out1, gates1, module.rnn, 1, ldev, B, T, grads)
             d_out0 = dropout(d_in1, p_drop, seed) if p_drop > 0 else d_in1
-            d_emb = gru_layer_backward(d_out0, emb, out0, gates0, module.rnn, 0, ldev, B, T, grads)
+            d_emb = rnn_layer_backward(d_out0, emb, out0, gates0, module.rnn, 0, ldev, B, T, grads)
             grads[id(module.embedding.weight)] = _embedding_backward(d_emb, tok, module.embedding.weight)
         out = tuple(grads.get(id(p)) if p.requires_grad else None for p in module.parameters())
         return (None, None, None) + out

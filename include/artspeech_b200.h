@@ -359,6 +359,16 @@ ASB_API int asb_gru_train_backward(const float* whh_fwd, const float* whh_bwd, c
                            const float* gates, const int32_t* lengths_dev, int B, int T, int hidden, float* dgi,
                            float* dgh, float* hprev, void* stream);
 
+/* The same pair for nn.LSTM (RNNType.LSTM, phoneme_to_articulation/__init__.py:47-49): whh (4H, H), bhh (4H), gate
+ * rows i, f, g, o; gi (B*T, 2, 4H); gates (B*T, 2, 5, H) receives i, f, g, o and the new cell state.  Every gate
+ * pre-activation is gi + W_hh h + b_hh, so one gradient array serves both: dgi (B*T, 2, 4H), zeroed by the caller. */
+ASB_API int asb_lstm_train_forward(const float* whh_fwd, const float* whh_bwd, const float* bhh_fwd, const float* bhh_bwd,
+                           const float* gi, const int32_t* lengths_dev, int B, int T, int hidden, float* out,
+                           float* gates, void* stream);
+ASB_API int asb_lstm_train_backward(const float* whh_fwd, const float* whh_bwd, const float* dout, const float* out,
+                            const float* gates, const int32_t* lengths_dev, int B, int T, int hidden, float* dgi,
+                            float* hprev, void* stream);
+
 /* Decoder implementation: 2 = tcgen05/TMEM kernel with fp16 operands (default in fast precision with
  * n_samples = 50), 1 = the same with tf32 operands (round 1), 0 = mma.sync kernel (always used in fp32 precision).  Both compute models.py:140-145.  The
  * layer-1 input projection follows the same switch (tcgen05 proj_umma.cu / mma.sync linear256). */

@@ -571,6 +571,31 @@ def test_training_gradients_vs_fp64_oracle_ragged_batch(mods):
         assert err <= 2e-4 * max(1.0, gw.abs().max().item()), (k, err, gw.abs().max().item())
 
 
+def test_training_lstm_cell_gradients_vs_fp64(mods):
+    """The LSTM instantiation trains natively too (lstm_train_{fwd,bwd}_kernel): every gradient against fp64
+    autograd of the same module graph, ragged batch, cuDNN disabled."""
+    import copy
+    models, omodel = mods
+    torch.manual_seed(5)
+    net = models.ArtSpeech(45, 2, precision="fp32", rnn="lstm").cuda().train()
+    twin = copy.deepcopy(net).cpu().double()
+    B, T = 9, 14
+    x = synthetic.tokens(B, T, 45, seed=6)
+    L = [14, 13, 13, 10, 7, 4, 2, 1, 1]
+    w = torch.randn(B, T, 2, 2, 50, generator=torch.Generator().manual_seed(7))
+    with torch.backends.cudnn.flags(enabled=False):
+        out = net(x.cuda(), L)
+        (out * w.cuda()).sum().backward()
+    want = twin._library_graph(x, L)
+    (want * w.double()).sum().backward()
+    assert (out.detach().cpu().double() - want.detach()).abs().max().item() <= 1e-5
+    truth = dict(twin.named_parameters())
+    for k, p in net.named_parameters():
+        got, gw = p.grad.cpu().double(), truth[k].grad
+        err = (got - gw).abs().max().item()
+        assert err <= 2e-4 * max(1.0, gw.abs().max().item()), (k, err, gw.abs().max().item())
+
+
 def test_training_dropout(mods):
     """nn.GRU(dropout=p) between the layers (models.py:111) in train mode: a mask is applied (train != eval),
     torch.manual_seed reproduces it, eval mode ignores it, and the analytic gradient agrees with a central
