@@ -67,6 +67,11 @@ SIGNATURES = {
                                 ctypes.c_int, ctypes.c_void_p]),
     "asb_mean_euclidean": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_int,
                                           ctypes.c_void_p]),
+    "asb_point_distance": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_int, ctypes.c_void_p]),
+    "asb_point_distance_backward": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_int,
+                                                   ctypes.c_void_p]),
+    "asb_pearson": (ctypes.c_int, [_c_f32p, _c_f32p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, _c_f32p,
+                                   _c_f32p, ctypes.c_void_p]),
     "asb_min_distance": (ctypes.c_int, [_c_f32p, _c_f32p, ctypes.c_int64, ctypes.c_int, ctypes.c_int, _c_f32p,
                                         ctypes.c_void_p, ctypes.c_void_p]),
     "asb_tract_variables": (ctypes.c_int, [_c_f32p, ctypes.c_int64, ctypes.c_int,

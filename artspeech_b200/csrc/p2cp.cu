@@ -239,7 +239,105 @@ min_distance_kernel(const float* __restrict__ u, const float* __restrict__ v, fl
   }
 }
 
+// EuclideanDistance (phoneme_to_articulation/metrics.py:5-24): per-point distance of planar contours, and its
+// gradient wrt the first argument (the training criterion, train_phoneme_to_articulation.py:86).
+__global__ void __launch_bounds__(256)
+point_distance_kernel(const float* __restrict__ u, const float* __restrict__ v, float* __restrict__ out,
+                      long long items, int n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= items * n) return;
+  const long long item = i / n;
+  const int k = int(i - item * n);
+  const float dx = u[item * 2 * n + k] - v[item * 2 * n + k];
+  const float dy = u[item * 2 * n + n + k] - v[item * 2 * n + n + k];
+  out[i] = sqrtf(fmaf(dy, dy, dx * dx));
+}
+// grad_u[item][c][k] = g[item][k] * (u - v)[item][c][k] / d[item][k]  (0 where the two points coincide)
+__global__ void __launch_bounds__(256)
+point_distance_bwd_kernel(const float* __restrict__ u, const float* __restrict__ v, const float* __restrict__ g,
+                          float* __restrict__ grad_u, long long items, int n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= items * n) return;
+  const long long item = i / n;
+  const int k = int(i - item * n);
+  const float dx = u[item * 2 * n + k] - v[item * 2 * n + k];
+  const float dy = u[item * 2 * n + n + k] - v[item * 2 * n + n + k];
+  const float d = sqrtf(fmaf(dy, dy, dx * dx));
+  const float s = d > 0.f ? g[i] / d : 0.f;
+  grad_u[item * 2 * n + k] = s * dx;
+  grad_u[item * 2 * n + n + k] = s * dy;
+}
+
+// pearsons_correlation (root metrics.py:9-35) with its quirk (the x TARGETS are centred with the x OUTPUT mean,
+// :22): outputs / targets (B, T, N, 2, D) -> x_corr, y_corr (B, N, D); thread = (b, art, coordinate, point), two
+// passes over T in fp64.
+__global__ void __launch_bounds__(256)
+pearson_kernel(const float* __restrict__ o, const float* __restrict__ t, int B, int T, int N, int D,
+               float* __restrict__ x_corr, float* __restrict__ y_corr) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long total = (long long)B * N * 2 * D;
+  if (i >= total) return;
+  const int d = int(i % D);
+  const int c = int((i / D) % 2);
+  const int a = int((i / (2 * D)) % N);
+  const int b = int(i / ((long long)2 * D * N));
+  const size_t stride = (size_t)N * 2 * D;
+  const size_t base = ((size_t)b * T * N + a) * 2 * D + (size_t)c * D + d;
+  double so = 0.0, st = 0.0;
+  for (int k = 0; k < T; ++k) {
+    so += double(o[base + k * stride]);
+    st += double(t[base + k * stride]);
+  }
+  const double mo = so / T, mt = c == 0 ? mo : st / T;   // :22 - the x targets use the OUTPUT mean
+  double soo = 0.0, stt = 0.0, sot = 0.0;
+  for (int k = 0; k < T; ++k) {
+    const double vo = double(o[base + k * stride]) - mo, vt = double(t[base + k * stride]) - mt;
+    soo += vo * vo;
+    stt += vt * vt;
+    sot += vo * vt;
+  }
+  const float r = float(sot / (sqrt(soo) * sqrt(stt) + 1e-5));
+  (c == 0 ? x_corr : y_corr)[((size_t)b * N + a) * D + d] = r;
+}
+
 }  // namespace
+
+extern "C" int asb_point_distance(const float* u, const float* v, float* out, int64_t items, int n, void* stream) {
+  if (items < 0 || n <= 0) return asb::set_error(ASB_ERR_INVALID, "asb_point_distance: bad shape");
+  if (items == 0) return ASB_OK;
+  if (!u || !v || !out) return asb::set_error(ASB_ERR_INVALID, "asb_point_distance: null pointer");
+  const long long blocks = (items * n + 255) / 256;
+  if (blocks > 0x7fffffffLL) return asb::set_error(ASB_ERR_INVALID, "asb_point_distance: too many items");
+  point_distance_kernel<<<unsigned(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(u, v, out, items, n);
+  ASB_CHECK_LAUNCH("point_distance_kernel");
+  return ASB_OK;
+}
+
+extern "C" int asb_point_distance_backward(const float* u, const float* v, const float* grad_out, float* grad_u,
+                                           int64_t items, int n, void* stream) {
+  if (items < 0 || n <= 0) return asb::set_error(ASB_ERR_INVALID, "asb_point_distance_backward: bad shape");
+  if (items == 0) return ASB_OK;
+  if (!u || !v || !grad_out || !grad_u) return asb::set_error(ASB_ERR_INVALID, "asb_point_distance_backward: null pointer");
+  const long long blocks = (items * n + 255) / 256;
+  if (blocks > 0x7fffffffLL) return asb::set_error(ASB_ERR_INVALID, "asb_point_distance_backward: too many items");
+  point_distance_bwd_kernel<<<unsigned(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(u, v, grad_out, grad_u,
+                                                                                            items, n);
+  ASB_CHECK_LAUNCH("point_distance_bwd_kernel");
+  return ASB_OK;
+}
+
+extern "C" int asb_pearson(const float* outputs, const float* targets, int B, int T, int n_art, int n_points,
+                           float* x_corr, float* y_corr, void* stream) {
+  if (B <= 0 || T <= 0 || n_art <= 0 || n_points <= 0) return asb::set_error(ASB_ERR_INVALID, "asb_pearson: bad shape");
+  if (!outputs || !targets || !x_corr || !y_corr) return asb::set_error(ASB_ERR_INVALID, "asb_pearson: null pointer");
+  const long long total = (long long)B * n_art * 2 * n_points;
+  const long long blocks = (total + 255) / 256;
+  if (blocks > 0x7fffffffLL) return asb::set_error(ASB_ERR_INVALID, "asb_pearson: too many items");
+  pearson_kernel<<<unsigned(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(outputs, targets, B, T, n_art, n_points,
+                                                                                 x_corr, y_corr);
+  ASB_CHECK_LAUNCH("pearson_kernel");
+  return ASB_OK;
+}
 
 extern "C" int asb_p2cp(const float* u, const float* v, float* out, int64_t items, int n, int m, int layout,
                         void* stream) {

@@ -548,7 +548,12 @@ def run_test(epoch, model, dataloader, criterion, outputs_dir, articulators, dev
         tgt = targets[:, :T].contiguous()
         loss = criterion(outputs, tgt)                                         # :58-63
         mask = length_mask(L, T, device)
-        losses.append(loss[mask].mean().item() if loss.dim() >= 2 else float(loss))
+        # masked mean over the valid frames (:59-63), kept on the device: one host sync per evaluation, not per batch
+        if loss.dim() >= 2:
+            m = mask.view(*mask.shape, *([1] * (loss.dim() - 2))).to(loss.dtype)
+            losses.append((loss * m).sum() / (m.sum() * max(1, loss[0, 0].numel())))
+        else:
+            losses.append(loss.detach().reshape(()))
         p2cp = p2cp_distance(outputs, tgt)                                     # :65-84, all sentences at once
         zeros4 = torch.zeros(outputs.shape[0], T, 4, dtype=torch.float32, device=device)
         acc += accumulate_device(p2cp, zeros4, zeros4, lengths_dev)
@@ -569,7 +574,7 @@ def run_test(epoch, model, dataloader, criterion, outputs_dir, articulators, dev
                          epoch_outputs_dir, regularize_out)                    # :131-141
     reduce_accumulators(acc)
     reduce_accumulators(sacc)
-    info = {"loss": float(sum(losses) / len(losses)) if losses else float("nan")}
+    info = {"loss": float(torch.stack([v.double() for v in losses]).mean().item()) if losses else float("nan")}
     to_mm = dataset_config.RES * dataset_config.PIXEL_SPACING                  # :150
     info.update(run_test_info(acc, sacc, n, to_mm=to_mm, articulators=articulators))
     return info

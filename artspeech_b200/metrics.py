@@ -65,21 +65,50 @@ class MeanP2CPDistance(nn.Module):
         return self.reduction(out)
 
 
+class _PointDistance(torch.autograd.Function):
+    """Per-point distance of planar contours (asb_point_distance) with its gradient wrt the first argument
+    (asb_point_distance_backward); the targets of the criterion carry no gradient."""
+
+    @staticmethod
+    def forward(ctx, o, t):
+        n = o.shape[-1]
+        items = o.numel() // (2 * n)
+        out = torch.empty(*o.shape[:-2], n, dtype=torch.float32, device=o.device)
+        with torch.cuda.device(o.device):
+            _lib.check(_lib.lib().asb_point_distance(_lib.ptr(o), _lib.ptr(t), _lib.ptr(out), items, n,
+                                                     _lib.stream_ptr(o.device)))
+        ctx.save_for_backward(o, t)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        o, t = ctx.saved_tensors
+        n = o.shape[-1]
+        items = o.numel() // (2 * n)
+        g = grad_out.to(torch.float32).contiguous()
+        grad_o = torch.empty_like(o)
+        with torch.cuda.device(o.device):
+            _lib.check(_lib.lib().asb_point_distance_backward(_lib.ptr(o), _lib.ptr(t), _lib.ptr(g), _lib.ptr(grad_o),
+                                                              items, n, _lib.stream_ptr(o.device)))
+        return grad_o, None
+
+
 class EuclideanDistance(nn.Module):
-    """phoneme_to_articulation/metrics.py:5-24: per-point distance (*, N_art, N_samples)."""
+    """phoneme_to_articulation/metrics.py:5-24: per-point distance (*, N_art, N_samples) of (*, N_art, 2,
+    N_samples) contours; the training criterion (train_phoneme_to_articulation.py:86), differentiable wrt the
+    outputs.  Evaluated by the library on the CUDA device (CPU inputs are moved there and the result back)."""
 
     def __init__(self, reduction="mean"):
         super().__init__()
         self.reduction = getattr(torch, reduction, lambda x: x)
 
     def forward(self, outputs, targets):
-        # the training criterion (train_phoneme_to_articulation.py:86): differentiable tensor ops, always
-        # evaluated on the CUDA device (CPU inputs are moved there and the result moved back)
+        if outputs.shape != targets.shape or outputs.shape[-2] != 2:
+            raise ValueError("expected two (*, 2, N_samples) tensors of equal shape")
         dev = _lib.device_of(outputs, targets)
-        o, t = outputs.to(dev), targets.to(dev)
-        dx = o[..., 0, :] - t[..., 0, :]
-        dy = o[..., 1, :] - t[..., 1, :]
-        return self.reduction(torch.sqrt(dx ** 2 + dy ** 2)).to(outputs.device)
+        o = outputs.to(device=dev, dtype=torch.float32).contiguous()
+        t = targets.detach().to(device=dev, dtype=torch.float32).contiguous()
+        return self.reduction(_PointDistance.apply(o, t)).to(outputs.device)
 
 
 def p2cp_distance(outputs, targets):
@@ -106,20 +135,21 @@ def euclidean_distance(outputs, targets):
 
 def pearsons_correlation(outputs, targets):
     """metrics.py:9-35, including its quirk (x target mean taken from the x outputs, :22).
-    (bs, T, N, 2, D) -> x_corr, y_corr (bs, N, D).  Tensor ops on the CUDA device (the per-sentence
-    form run_test needs is the kernel asb_eval_sentence_metrics)."""
-    eps = 1e-5
+    (bs, T, N, 2, D) -> x_corr, y_corr (bs, N, D), computed by asb_pearson (two passes over T in fp64); the
+    per-sentence, length-masked form run_test needs is asb_eval_sentence_metrics."""
+    if outputs.shape != targets.shape or outputs.dim() != 5 or outputs.shape[3] != 2:
+        raise ValueError("expected two (bs, T, N_art, 2, N_samples) tensors of equal shape")
     dev, home = _lib.device_of(outputs, targets), outputs.device
-    outputs, targets = outputs.to(dev), targets.to(dev)     # evaluated on the CUDA device, returned where it came from
-    xo, yo = outputs[:, :, :, 0, :], outputs[:, :, :, 1, :]
-    xt, yt = targets[:, :, :, 0, :], targets[:, :, :, 1, :]
-    vxo = xo - xo.mean(dim=1, keepdim=True)
-    vxt = xt - xo.mean(dim=1, keepdim=True)
-    x_corr = (vxo * vxt).sum(1) / (torch.sqrt((vxo ** 2).sum(1)) * torch.sqrt((vxt ** 2).sum(1)) + eps)
-    vyo = yo - yo.mean(dim=1, keepdim=True)
-    vyt = yt - yt.mean(dim=1, keepdim=True)
-    y_corr = (vyo * vyt).sum(1) / (torch.sqrt((vyo ** 2).sum(1)) * torch.sqrt((vyt ** 2).sum(1)) + eps)
-    return x_corr.to(home), y_corr.to(home)
+    o = _as_f32_cuda(outputs, dev).contiguous()
+    t = _as_f32_cuda(targets, dev).contiguous()
+    B, T, N, _, D = o.shape
+    x_corr = torch.empty(B, N, D, dtype=torch.float32, device=dev)
+    y_corr = torch.empty(B, N, D, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().asb_pearson(_lib.ptr(o), _lib.ptr(t), B, T, N, D, _lib.ptr(x_corr), _lib.ptr(y_corr),
+                                          _lib.stream_ptr(dev)))
+    dt = outputs.dtype if outputs.dtype.is_floating_point else torch.float32
+    return x_corr.to(device=home, dtype=dt), y_corr.to(device=home, dtype=dt)
 
 
 class P2CPDistance(nn.Module):

@@ -71,6 +71,19 @@ ASB_API int asb_p2cp(const float* u, const float* v, float* out, int64_t items, 
 ASB_API int asb_mean_euclidean(const float* u, const float* v, float* out, int64_t items, int n,
                        void* stream);
 
+/* EuclideanDistance.forward with reduction "none", phoneme_to_articulation/metrics.py:5-24: planar (2,n) contours
+ * -> out (items, n) = per-point distance; and its gradient wrt u (the training criterion,
+ * train_phoneme_to_articulation.py:86): grad_u (items, 2, n) = grad_out * (u - v) / distance (0 where the points
+ * coincide). */
+ASB_API int asb_point_distance(const float* u, const float* v, float* out, int64_t items, int n, void* stream);
+ASB_API int asb_point_distance_backward(const float* u, const float* v, const float* grad_out, float* grad_u,
+                                int64_t items, int n, void* stream);
+
+/* pearsons_correlation, root metrics.py:9-35 (time axis = dim 1; the x targets are centred with the x OUTPUT
+ * mean, :22): outputs / targets (B, T, n_art, 2, n_points) fp32 -> x_corr, y_corr (B, n_art, n_points). */
+ASB_API int asb_pearson(const float* outputs, const float* targets, int B, int T, int n_art, int n_points,
+                float* x_corr, float* y_corr, void* stream);
+
 /* Closest pair of two planar contours per item: u (items, 2, n), v (items, 2, m) fp32 ->
  * out_d (items) = min_{i,j} |u_i - v_j|, out_ij (items, 2) int32 = the pair attaining it (smallest
  * i*m + j among ties; may be NULL).  The reduction inside CriticalLoss.forward,

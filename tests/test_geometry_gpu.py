@@ -188,11 +188,17 @@ def test_metric_helpers_accept_cpu_tensors_and_run_on_the_gpu(asb):
     xc, yc = M.pearsons_correlation(pred, tgt)
     wx, wy = og.pearsons_correlation(pred, tgt)
     assert xc.device.type == "cpu" and xc.shape == wx.shape
-    assert torch.allclose(xc.double(), wx, atol=2e-4) and torch.allclose(yc.double(), wy, atol=2e-4)
+    assert torch.allclose(xc.double(), wx, atol=2e-6) and torch.allclose(yc.double(), wy, atol=2e-6)
     d = M.EuclideanDistance("none")(pred, tgt)
     assert d.device.type == "cpu" and d.shape == (3, 17, 4, 50)
     want = torch.sqrt(((pred.double() - tgt.double()) ** 2).sum(dim=-2))
     assert torch.allclose(d.double(), want, rtol=1e-5, atol=1e-9)
+    # the criterion's gradient (asb_point_distance_backward) against fp64 autograd of the formula
     p = pred.clone().cuda().requires_grad_(True)
+    w = torch.randn(3, 17, 4, 50, generator=torch.Generator().manual_seed(3))
+    (M.EuclideanDistance("none")(p, tgt.cuda()) * w.cuda()).sum().backward()
+    p64 = pred.double().requires_grad_(True)
+    (torch.sqrt(((p64 - tgt.double()) ** 2).sum(dim=-2)) * w.double()).sum().backward()
+    assert torch.allclose(p.grad.cpu().double(), p64.grad, rtol=1e-4, atol=1e-6)
     M.EuclideanDistance("mean")(p, tgt.cuda()).backward()
-    assert p.grad is not None and torch.isfinite(p.grad).all()
+    assert torch.isfinite(p.grad).all()
