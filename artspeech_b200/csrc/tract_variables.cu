@@ -4,21 +4,24 @@
 // _calculate_TV (:23-35), which the reference calls once per frame from a Python loop with
 // three .item() host syncs per search (phoneme_to_articulation/__init__.py:242-261).
 //
-// Round-2 kernel.  A TEAM of 8 lanes owns one contour set (4 sets per warp, 32 per CTA).  Persistent
-// CTAs, one per SM: the six contours of the next 32 sets are staged in shared memory by 1-D bulk async
-// copies (TMA, one 400-byte copy per contour) into a 2-stage mbarrier ring while the current 32 are
-// searched.  Inside a team every search is split 2 x 4: lane (h, q) keeps one HALF of the rows of the
-// first point set in registers as natural fp32x2 pairs and streams one QUARTER of the columns of the
-// second; per (row pair, column) the body is 2 FADD2 + FMUL2 + FFMA2 + one FMNMX3 - all 32 lanes busy,
-// 8 % padding at most (the round-1 kernel gave a lane whole columns: 62-78 % of the lanes had work, and
-// every row was an LDS broadcast per two columns).  Distances use the direct (dx*dx + dy*dy) form in
-// fp32; only the minimum per column is tracked.  The team reduces (distance, j) with the smaller j
-// winning ties, then the rows are re-evaluated against the winning column with the same instructions
-// and the smallest i that reproduces the minimum bit for bit is taken: the reference's tie-break
-// (smallest j among the global minima, then smallest i for that j, tract_variables.py:26-29).
-// Shared-memory banks: a set is 600 floats (600 mod 32 = 24), so the four teams of a warp and the
-// row halves (26 floats apart) / column quarters (7, 10 or 13 floats apart) of a team all fall into
-// distinct banks; lanes that share a row half or a column quarter read the same word (broadcast).
+// Round-2 kernel.  A TEAM of 8 lanes owns one contour set (4 sets per warp).  Persistent CTAs, one per SM, of
+// NW <= 14 compute warps + one PRODUCER warp: the contours of the next group of 4 NW sets are staged in
+// shared memory by 1-D bulk async copies (TMA) into a 2-stage full/empty mbarrier ring while the current group
+// is searched; adjacent contours of a set are merged into one copy (two copies per set in the thesis layout
+// instead of five: a 400-byte bulk copy costs as much to issue as a large one, and with five the kernel was
+// bound by issuing them).  Inside a team a search is split HS x (8 / HS): lane (h, q) keeps the rows of part h
+// of the first point set in registers as natural fp32x2 pairs and streams the columns of part q of the second,
+// two columns at a time with the next pair's operands prefetched; per (row pair, column) the body is
+// 2 FADD2 + FMUL2 + FFMA2 + one FMNMX3 - all 32 lanes busy, <= 12 % padding (the round-1 kernel gave a lane
+// whole columns: 62-78 % of the lanes had work, and every row was an LDS broadcast per two columns).
+// Distances use the direct (dx*dx + dy*dy) form in fp32; only the minimum per column is tracked.  The four
+// searches of a set are reduced TOGETHER by (distance, j) shuffles with the smaller j winning ties, then the
+// rows are re-evaluated against the winning column with the scan's roundings and the smallest i that
+// reproduces the minimum bit for bit is taken: the reference's tie-break (smallest j among the global minima,
+// then smallest i for that j, tract_variables.py:26-29).
+// Shared-memory banks: a set is 500 (or 600) floats, so the four teams of a warp start 20 (24) banks apart
+// and the row parts / column parts of a team fall into distinct banks for the 50 x 50 search (a few 2-way
+// conflicts remain in the 15-row searches); lanes that share a row part or a column part read the same word.
 #include <utility>
 
 #include "asb_common.cuh"
@@ -31,8 +34,8 @@ constexpr int kD = 50;
 constexpr int kItemF = 2 * kD;
 constexpr int kTeam = 8;                          // lanes per contour set
 constexpr int kStages = 2;
-// NW compute warps (4 teams each) + one producer warp; NW = 14 when a set needs 5 staged contours (the
-// upper incisor shared by all sets, evaluation.py:93-109), 8 when it needs 6 (shared memory bound)
+// NW compute warps (4 teams each) + one producer warp; NW <= 14 when a set needs 5 staged contours (the
+// upper incisor shared by all sets, evaluation.py:93-109), <= 8 when it needs 6 (shared memory bound)
 constexpr int kTeamsPerWarp = 32 / kTeam;
 // shared-memory slots
 enum { S_LLIP = 0, S_PHAR = 1, S_SPM = 2, S_TONGUE = 3, S_UINC = 4, S_ULIP = 5, S_COUNT = 6 };
