@@ -216,6 +216,9 @@ gru_fast_kernel(const uint32_t* __restrict__ frag_fwd, const uint32_t* __restric
 }
 
 // ---------------------------------------------------------------- fp32 mode (FFMA, W_hh^T in smem)
+// R = batch rows per thread (the CTA owns 2 R rows): the step is bound by the FFMA pipe (3 x 128 FMAs per row and
+// thread), so the launcher takes R = 2 while that still fits one wave of the machine - twice the CTAs, half the step.
+template <int R>
 __global__ void __launch_bounds__(256, 1)
 gru_fp32_kernel(const float* __restrict__ wt_fwd, const float* __restrict__ wt_bwd,
                 const float* __restrict__ bhhn_fwd, const float* __restrict__ bhhn_bwd,
@@ -223,48 +226,56 @@ gru_fp32_kernel(const float* __restrict__ wt_fwd, const float* __restrict__ wt_b
                 int T) {
   extern __shared__ __align__(16) float smem[];
   float* W = smem;                  // [k][384]
-  float* hsm = smem + kH * kGH;     // [2][8][128]
+  float* hsm = smem + kH * kGH;     // [2][2 R][128]
   const int tid = threadIdx.x, u = tid & (kH - 1), half = tid >> 7;
-  const int dir = blockIdx.y, b0 = blockIdx.x * 8;
+  const int dir = blockIdx.y, b0 = blockIdx.x * 2 * R;
   const float* wt = dir ? wt_bwd : wt_fwd;
   const float bn = (dir ? bhhn_bwd : bhhn_fwd)[u];
   for (int i = tid; i < kH * kGH / 4; i += 256)
     reinterpret_cast<float4*>(W)[i] = __ldg(reinterpret_cast<const float4*>(wt) + i);
-  for (int i = tid; i < 2 * 8 * kH; i += 256) hsm[i] = 0.f;
-  int len[4];
+  for (int i = tid; i < 2 * 2 * R * kH; i += 256) hsm[i] = 0.f;
+  int len[R];
 #pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    const int b = b0 + 4 * half + r;
+  for (int r = 0; r < R; ++r) {
+    const int b = b0 + R * half + r;
     len[r] = b < B ? lengths[b] : 0;
   }
   const int Lmax = lengths[b0];
-  float h[4] = {0.f, 0.f, 0.f, 0.f};
+  float h[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) h[r] = 0.f;
   __syncthreads();
   int cur = 0;
   for (int s = 0; s < Lmax; ++s) {
     const int t = dir ? Lmax - 1 - s : s;
-    float gr[4], gz[4], gn[4];
+    float gr[R], gz[R], gn[R];
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
+    for (int r = 0; r < R; ++r) {
       if (t < len[r]) {
-        const float* p = gi + (((long long)(b0 + 4 * half + r) * T + t) * 2 + dir) * kGH + u;
+        const float* p = gi + (((long long)(b0 + R * half + r) * T + t) * 2 + dir) * kGH + u;
         gr[r] = __ldg(p); gz[r] = __ldg(p + kH); gn[r] = __ldg(p + 2 * kH);
       } else {
         gr[r] = gz[r] = gn[r] = 0.f;
       }
     }
-    float ar[4] = {0.f, 0.f, 0.f, 0.f}, az[4] = {0.f, 0.f, 0.f, 0.f}, an[4] = {bn, bn, bn, bn};
-    const float* hc = hsm + cur * 8 * kH + 4 * half * kH;
+    float ar[R], az[R], an[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      ar[r] = 0.f;
+      az[r] = 0.f;
+      an[r] = bn;
+    }
+    const float* hc = hsm + cur * 2 * R * kH + R * half * kH;
 #pragma unroll 2
     for (int k = 0; k < kH; k += 4) {
-      float4 hv[4];
+      float4 hv[R];
 #pragma unroll
-      for (int r = 0; r < 4; ++r) hv[r] = *reinterpret_cast<const float4*>(hc + r * kH + k);
+      for (int r = 0; r < R; ++r) hv[r] = *reinterpret_cast<const float4*>(hc + r * kH + k);
 #pragma unroll
       for (int kk = 0; kk < 4; ++kk) {
         const float wr = W[(k + kk) * kGH + u], wz = W[(k + kk) * kGH + kH + u], wn = W[(k + kk) * kGH + 2 * kH + u];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
+        for (int r = 0; r < R; ++r) {
           const float hk = kk == 0 ? hv[r].x : kk == 1 ? hv[r].y : kk == 2 ? hv[r].z : hv[r].w;
           ar[r] = fmaf(wr, hk, ar[r]);
           az[r] = fmaf(wz, hk, az[r]);
@@ -273,15 +284,15 @@ gru_fp32_kernel(const float* __restrict__ wt_fwd, const float* __restrict__ wt_b
       }
     }
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
+    for (int r = 0; r < R; ++r) {
       const float rg = 1.f / (1.f + expf(-(gr[r] + ar[r])));
       const float zg = 1.f / (1.f + expf(-(gz[r] + az[r])));
       const float ng = tanhf(gn[r] + rg * an[r]);
       const float hn = (1.f - zg) * ng + zg * h[r];
       const bool valid = t < len[r];
       h[r] = valid ? hn : h[r];
-      hsm[(cur ^ 1) * 8 * kH + (4 * half + r) * kH + u] = h[r];
-      if (valid) out[((long long)(b0 + 4 * half + r) * T + t) * (2 * kH) + dir * kH + u] = h[r];
+      hsm[(cur ^ 1) * 2 * R * kH + (R * half + r) * kH + u] = h[r];
+      if (valid) out[((long long)(b0 + R * half + r) * T + t) * (2 * kH) + dir * kH + u] = h[r];
     }
     __syncthreads();
     cur ^= 1;
@@ -409,13 +420,18 @@ int launch_recurrent_layer(const asb_model* m, int layer, const float* gi, const
     static DeviceOnce once;
     const int smem = (kH * kGH + 2 * 8 * kH) * int(sizeof(float));
     if (int rc = once.run([&] {
-          return check_cuda(cudaFuncSetAttribute(gru_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
-                            "gru_fp32_kernel smem attribute");
+          cudaError_t e = cudaFuncSetAttribute(gru_fp32_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+          if (e == cudaSuccess) e = cudaFuncSetAttribute(gru_fp32_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+          return check_cuda(e, "gru_fp32_kernel smem attribute");
         }))
       return rc;
-    dim3 grid((B + 7) / 8, 2);
-    gru_fp32_kernel<<<grid, 256, smem, st>>>(w.whh_t[layer][0], w.whh_t[layer][1], w.bhh_n[layer][0],
-                                              w.bhh_n[layer][1], gi, lengths, out, B, T);
+    if (2 * ((B + 3) / 4) <= sm_count()) {
+      gru_fp32_kernel<2><<<dim3((B + 3) / 4, 2), 256, smem, st>>>(w.whh_t[layer][0], w.whh_t[layer][1], w.bhh_n[layer][0],
+                                                                 w.bhh_n[layer][1], gi, lengths, out, B, T);
+    } else {
+      gru_fp32_kernel<4><<<dim3((B + 7) / 8, 2), 256, smem, st>>>(w.whh_t[layer][0], w.whh_t[layer][1], w.bhh_n[layer][0],
+                                                                 w.bhh_n[layer][1], gi, lengths, out, B, T);
+    }
     ASB_CHECK_LAUNCH("gru_fp32_kernel");
     return ASB_OK;
   }
