@@ -14,6 +14,14 @@
 //   * values are rounded with cvt.rn.satfinite.f16x2.f32 (un-normalised ReLU outputs stay far below the
 //     fp16 range for any sane checkpoint; satfinite keeps an outlier finite instead of producing NaN).
 //
+// FP32 PRECISION (kSplit = true): the same kernel with SPLIT operands.  Every activation and every weight is
+// carried as hi + lo, hi = fp16(v), lo = fp16(v - hi) (22 significand bits together), and a product is three
+// MMAs, a_lo w_hi + a_hi w_lo + a_hi w_hi, accumulated in fp32 in tensor memory (the dropped a_lo w_lo term is
+// below 2^-22 of the product).  hi pairs occupy the first 16 columns of a chunk's 32 accumulator columns, the
+// residual pairs the second 16 (all 32 were loaded into registers before either half is stored); a weight
+// piece is followed through the ring by its residual piece, so a product costs two ring stages and the
+// image is twice the fast one.  Contours agree with the fp32 FFMA decoder (decoder.cu) to ~1e-6.
+//
 // Same computation as decoder.cu (models.py:140-145 with ArticulatorPredictor :7-33) for a tile of
 // 128 frames: linear.0 + ReLU, then per articulator LN -> FC(128,256) -> ReLU -> LN -> FC(256,256)
 // -> ReLU -> LN -> x/y heads -> sigmoid, written once in the final (frames, N_art, 2, D) layout.
@@ -104,8 +112,11 @@ constexpr int kLinChunk = 128 * 32;         // one 64-k block of linear.0: 128 r
 constexpr int kFcChunk = 256 * 32;          // one 64-k block of FC1 / FC2: 256 rows x 128 B = 32 KB
 constexpr int kHeadChunk = kHeadN * 32;     // one 64-k block of the heads: 112 rows x 128 B = 14 KB
 constexpr int kArtParams = 1024;            // b1' (256) | b2' (256) | W2'1 (256) | bh' (128, zero padded) | Wh'1 (128)
-constexpr int kLinBlock = kLinParams + 4 * kLinChunk;
-constexpr int kArtBlock = kArtParams + 2 * kFcChunk + 4 * kFcChunk + 4 * kHeadChunk;
+// split (fp32 precision) images hold every piece twice: [piece hi][piece lo], a piece = one ring stage
+__host__ __device__ constexpr int lin_block(bool split) { return kLinParams + (split ? 2 : 1) * 4 * kLinChunk; }
+__host__ __device__ constexpr int art_block(bool split) {
+  return kArtParams + (split ? 2 : 1) * (2 * kFcChunk + 4 * kFcChunk + 4 * kHeadChunk);
+}
 constexpr int P_B1 = 0, P_B2 = 256, P_WS2 = 512, P_BH = 768, P_WSH = 896;
 
 // dynamic shared memory layout (bytes, base 1024-aligned)
@@ -121,25 +132,41 @@ __device__ __forceinline__ float round_f16(float x) { return __half2float(__floa
 
 // dst image of (W . diag(scale))[N][K] in fp16 as K/64 blocks of [Npad rows][64] with the 128-byte swizzle
 // (16-byte unit u of a row lands at u ^ (row & 7))
+// bpp = blocks per piece (ring stage).  split: piece p is stored as [hi blocks][lo blocks], lo = fp16(w - fp16(w)).
 __global__ void pack_umma16_kernel(const float* __restrict__ src, const float* __restrict__ scale,
-                                   __half* __restrict__ dst, int n_src, int row0, int n_pad, int K) {
+                                   __half* __restrict__ dst, int n_src, int row0, int n_pad, int K, int bpp,
+                                   int split) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_src * K) return;
   const int ns = i / K, k = i - ns * K;
   const int n = ns + row0;
   const int kc = k >> 6, kk = k & 63;
-  const int off = kc * (n_pad * kBlockK) + (n >> 3) * 512 + (n & 7) * 64 + ((((kk >> 3) ^ (n & 7)) << 3) | (kk & 7));
+  const int block = n_pad * kBlockK;
+  const int in_block = (n >> 3) * 512 + (n & 7) * 64 + ((((kk >> 3) ^ (n & 7)) << 3) | (kk & 7));
+  const int piece = kc / bpp, bi = kc - piece * bpp;
   const float w = scale ? src[i] * scale[k] : src[i];
-  dst[off] = __float2half_rn(w);
+  const __half hi = __float2half_rn(w);
+  if (!split) {
+    dst[kc * block + in_block] = hi;
+  } else {
+    const int base = piece * 2 * bpp * block + bi * block + in_block;
+    dst[base] = hi;
+    dst[base + bpp * block] = __float2half_rn(w - __half2float(hi));
+  }
 }
 // dst[n] = sum_k fp16(W[n][k] * scale[k]): row sums of the folded weights exactly as the tensor cores
 // see them (the mean term of the deferred LayerNorm)
 __global__ void fold_wsum16_kernel(const float* __restrict__ W, const float* __restrict__ scale,
-                                   float* __restrict__ dst, int N, int K, double out_scale) {
+                                   float* __restrict__ dst, int N, int K, double out_scale, int split) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   double acc = 0.0;
-  for (int k = 0; k < K; ++k) acc += double(round_f16(W[(size_t)n * K + k] * scale[k]));
+  for (int k = 0; k < K; ++k) {
+    const float w = W[(size_t)n * K + k] * scale[k];
+    const float hi = round_f16(w);
+    acc += double(hi);
+    if (split) acc += double(round_f16(w - hi));
+  }
   dst[n] = float(acc * out_scale);
 }
 // dst[n] = b[n] + sum_k W[n][k] * beta[k]   (beta may be null)
@@ -153,6 +180,10 @@ __global__ void fold_bias16_kernel(const float* __restrict__ W, const float* __r
     for (int k = 0; k < K; ++k) acc += double(W[(size_t)n * K + k]) * double(beta[k]);
   dst[n] = float(acc * out_scale);
 }
+
+// residual store of the split variant; the one-element overload exists only so that the fast instantiation compiles
+__device__ __forceinline__ void st_lo16(uint32_t taddr, const uint32_t (&r)[16]) { tmem_st16(taddr, r); }
+__device__ __forceinline__ void st_lo16(uint32_t, const uint32_t (&)[1]) {}
 
 __device__ __forceinline__ void bar_sync_epilogue() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
@@ -205,7 +236,9 @@ struct UnitIter {
 //   heads    : A3 = P           -> D3 = Q[0,112)                (read by the output warps)
 // and the next articulator (parity flipped) puts its A1 into Q[128,256) while the heads GEMM runs;
 // its FC1 and the first FC2 epilogue chunks overlap the output warps' sigmoid + stores.
+template <bool kSplit>
 __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaArgs a) {
+  constexpr int kW = kSplit ? 2 : 1;   // ring stages per weight piece (hi, lo)
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // keeps the shared address space
   unsigned char* Ws = smem + kOffW;
@@ -267,7 +300,7 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
       UnitIter units(a);
       int tile, g0, g1;
       while (units.next(tile, g0, g1)) {
-        for (int j = 0; j < 2; ++j) push(a.image + kLinParams + 2 * j * kLinChunk, 2 * kLinChunk * 4);
+        for (int j = 0; j < 2 * kW; ++j) push(a.image + kLinParams + 2 * j * kLinChunk, 2 * kLinChunk * 4);
         for (int k = 0; k < g1 - g0; ++k) {
           const int art = g0 + k;
           if (k == g1 - g0 - 1) {   // last articulator of this unit: pull the NEXT unit's input tile towards L2
@@ -282,18 +315,19 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
                            : "memory");
             }
           }
-          const float* blk = a.image + kLinBlock + (size_t)art * kArtBlock;
+          const float* blk = a.image + lin_block(kSplit) + (size_t)art * art_block(kSplit);
           const uint32_t pb = pa & 1;
           mbar_wait(&pempty[pb], ((pa >> 1) & 1) ^ 1);
           mbar_arrive_expect_tx(&pfull[pb], kArtParams * 4);
           bulk_g2s(Ps + pb * kArtParams, blk, kArtParams * 4, &pfull[pb]);
           ++pa;
           const float* w1 = blk + kArtParams;
-          const float* w2 = w1 + 2 * kFcChunk;
-          const float* wh = w2 + 4 * kFcChunk;
-          for (int j = 0; j < 2; ++j) push(w1 + j * kFcChunk, kFcChunk * 4);
-          for (int j = 0; j < 4; ++j) push(w2 + j * kFcChunk, kFcChunk * 4);
-          for (int j = 0; j < 2; ++j) push(wh + 2 * j * kHeadChunk, 2 * kHeadChunk * 4);   // 14 KB blocks stay 1 KB aligned
+          const float* w2 = w1 + kW * 2 * kFcChunk;
+          const float* wh = w2 + kW * 4 * kFcChunk;
+          // split: the pieces alternate hi, lo in the image, so the same sequential walk streams both
+          for (int j = 0; j < 2 * kW; ++j) push(w1 + j * kFcChunk, kFcChunk * 4);
+          for (int j = 0; j < 4 * kW; ++j) push(w2 + j * kFcChunk, kFcChunk * 4);
+          for (int j = 0; j < 2 * kW; ++j) push(wh + 2 * j * kHeadChunk, 2 * kHeadChunk * 4);   // 14 KB blocks stay 1 KB aligned
         }
       }
     }
@@ -318,24 +352,39 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
           const int blk = (j >> 1) % blocks_per_stage;            // block inside the stage
           const bool opens = (j & 1) == 0 && blk == 0;
           const bool closes = (j & 1) == 1 && blk == blocks_per_stage - 1;
-          const uint32_t st = c % kStages;
+          const uint32_t st = c % kStages, st_lo = (c + 1) % kStages;   // split: the residual piece follows in the ring
           mbar_wait(&abar[j], (ph >> j) & 1);
           ph ^= 1u << j;
-          if (opens && ASB_DEC_ABLATE != 4) mbar_wait(&full[st], (c / kStages) & 1);
+          if (opens && ASB_DEC_ABLATE != 4) {
+            mbar_wait(&full[st], (c / kStages) & 1);
+            if (kSplit) mbar_wait(&full[st_lo], ((c + 1) / kStages) & 1);
+          }
           fence_after_sync();
           TR(0, 10 + j);
           // 32 k = 64 bytes into the 128-byte swizzled row: the descriptor's start address advances by 64 >> 4
           const uint64_t bdesc = smem_desc_k_sw128(smem_u32(Ws + st * kStageBytes + blk * block_bytes)) + uint64_t(4 * (j & 1));
+          const uint64_t bdesc_lo =
+              smem_desc_k_sw128(smem_u32(Ws + st_lo * kStageBytes + blk * block_bytes)) + uint64_t(4 * (j & 1));
           const uint32_t acol = a_tmem + j * kChunkK;
           if (elect_one()) {
 #pragma unroll
-            for (int ks = 0; ks < (ASB_DEC_ABLATE == 3 ? 0 : 2); ++ks)
-              mma_bf16_ts(d_tmem, acol + ks * 8, bdesc + uint64_t(2 * ks), idesc, (j | ks) != 0);
-            if (closes && ASB_DEC_ABLATE != 4) commit(&empty[st]);   // frees the stage once its MMAs have read it
+            for (int ks = 0; ks < (ASB_DEC_ABLATE == 3 ? 0 : 2); ++ks) {
+              if (kSplit) {   // hi pairs in columns [0, 16) of the chunk, residual pairs in [16, 32); small terms first
+                mma_bf16_ts(d_tmem, acol + 16 + ks * 8, bdesc + uint64_t(2 * ks), idesc, (j | ks) != 0);   // a_lo w_hi
+                mma_bf16_ts(d_tmem, acol + ks * 8, bdesc_lo + uint64_t(2 * ks), idesc, true);              // a_hi w_lo
+                mma_bf16_ts(d_tmem, acol + ks * 8, bdesc + uint64_t(2 * ks), idesc, true);                 // a_hi w_hi
+              } else {
+                mma_bf16_ts(d_tmem, acol + ks * 8, bdesc + uint64_t(2 * ks), idesc, (j | ks) != 0);
+              }
+            }
+            if (closes && ASB_DEC_ABLATE != 4) {   // frees the stage(s) once their MMAs have read them
+              commit(&empty[st]);
+              if (kSplit) commit(&empty[st_lo]);
+            }
             if (j == k_chunks - 1) commit(done);
           }
           __syncwarp();
-          if (closes) ++c;
+          if (closes) c += kW;
         }
         TR(0, 99);
       };
@@ -489,7 +538,7 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
       const f32x2 rs2 = pack2(rs, rs), nm2 = pack2(nm, nm), one2 = pack2(1.f, 1.f);
       f32x2 sa = pack2(0.f, 0.f), sb = sa, qa = sa, qb = sa;
       auto body = [&](uint32_t(&buf)[32], int ch, bool last) {
-        uint32_t h[16];
+        uint32_t h[16], l[kSplit ? 16 : 1];
 #pragma unroll
         for (int q = 0; q < (ASB_DEC_ABLATE == 1 || ASB_DEC_ABLATE == 2 ? 0 : 8); ++q) {
           const float4 b4 = lds4(b_addr + (32 * ch + 4 * q) * 4);
@@ -513,9 +562,17 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
           qb = fma2(p23, p23, qb);
           h[2 * q + 0] = pack_f16x2(v0, v1);
           h[2 * q + 1] = pack_f16x2(v2, v3);
+          if constexpr (kSplit) {
+            l[2 * q + 0] = residual_f16x2(v0, v1, h[2 * q + 0]);
+            l[2 * q + 1] = residual_f16x2(v2, v3, h[2 * q + 1]);
+          }
         }
         // 32 k as 16 columns of fp16 pairs, into the FIRST half of this chunk's own accumulator columns
-        if (ASB_DEC_ABLATE != 2) tmem_st16(region + 32 * ch, h);
+        // (split: the residual pairs into the second half)
+        if (ASB_DEC_ABLATE != 2) {
+          tmem_st16(region + 32 * ch, h);
+          if (kSplit) st_lo16(region + 32 * ch + 16, l);
+        }
         if (last) {   // the moments are published BEFORE the last chunk is signalled (their readers sit behind it)
           float s0, s1, s2, s3, q0, q1, q2, q3;
           unpack2(sa, s0, s1);
@@ -545,10 +602,15 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
 #pragma unroll 1
       for (int c = 0; c < 2; ++c) {
         const int ch = 2 * c + half;
-        uint32_t h[16];
+        uint32_t h[16], l[kSplit ? 16 : 1];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) h[i] = pack_f16x2(xrow[32 * ch + 2 * i], xrow[32 * ch + 2 * i + 1]);
+        for (int i = 0; i < 16; ++i) {
+          const float v0 = xrow[32 * ch + 2 * i], v1 = xrow[32 * ch + 2 * i + 1];
+          h[i] = pack_f16x2(v0, v1);
+          if constexpr (kSplit) l[i] = residual_f16x2(v0, v1, h[i]);
+        }
         tmem_st16(region + 128 + 32 * ch, h);
+        if (kSplit) st_lo16(region + 128 + 32 * ch + 16, l);
         signal(&a1bar[ch]);
       }
     };
@@ -589,15 +651,20 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
                             __uint_as_float(r2[4 * i + 2]), __uint_as_float(r2[4 * i + 3]));
           __syncwarp();
           if (c < 3) load_block(ch + 2, r2);   // the next block's loads fly under this block's conversion
-          uint32_t h[16];
+          uint32_t h[16], l[kSplit ? 16 : 1];
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
             const float4 v = *reinterpret_cast<const float4*>(tile32 + lane * kTilePitch + 4 * q);
             h[2 * q + 0] = pack_f16x2(v.x, v.y);
             h[2 * q + 1] = pack_f16x2(v.z, v.w);
+            if constexpr (kSplit) {
+              l[2 * q + 0] = residual_f16x2(v.x, v.y, h[2 * q + 0]);
+              l[2 * q + 1] = residual_f16x2(v.z, v.w, h[2 * q + 1]);
+            }
           }
           __syncwarp();   // the tile is rewritten by the next block
           tmem_st16(Q + 32 * ch, h);
+          if (kSplit) st_lo16(Q + 32 * ch + 16, l);
           signal(&chunk[ch]);
         }
         // ---- linear.0 epilogue: relu(D0 + b) -> LayerNorm(128) -> x-hat (fp32) kept in shared memory
@@ -669,23 +736,26 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
 
 namespace asb {
 
-size_t umma16_image_floats(int n_art) { return (size_t)kLinBlock + (size_t)n_art * kArtBlock; }
-
-bool umma16_decoder_supported(const asb_model* m) {
-  return m->precision == ASB_PRECISION_FAST && m->D == 50 && m->H == kH;
+size_t umma16_image_floats(int n_art, bool split) {
+  return (size_t)lin_block(split) + (size_t)n_art * art_block(split);
 }
 
+// both precisions: fast = fp16 operands, fp32 = split fp16 operands (three MMAs per product)
+bool umma16_decoder_supported(const asb_model* m) { return m->D == 50 && m->H == kH; }
+
+static bool split_of(const asb_model* m) { return m->precision != ASB_PRECISION_FAST; }
+
 static int pack_mat(const float* src, const float* scale, float* dst_floats, int n_src, int row0, int n_pad, int K,
-                    cudaStream_t st) {
+                    int bpp, bool split, cudaStream_t st) {
   const int n = n_src * K;
   pack_umma16_kernel<<<(n + 255) / 256, 256, 0, st>>>(src, scale, reinterpret_cast<__half*>(dst_floats), n_src, row0,
-                                                     n_pad, K);
+                                                     n_pad, K, bpp, split ? 1 : 0);
   ASB_CHECK_LAUNCH("pack_umma16_kernel");
   return ASB_OK;
 }
-static int fold_wsum(const float* W, const float* scale, float* dst, int N, int K, cudaStream_t st,
+static int fold_wsum(const float* W, const float* scale, float* dst, int N, int K, bool split, cudaStream_t st,
                      double out_scale = 1.0) {
-  fold_wsum16_kernel<<<(N + 127) / 128, 128, 0, st>>>(W, scale, dst, N, K, out_scale);
+  fold_wsum16_kernel<<<(N + 127) / 128, 128, 0, st>>>(W, scale, dst, N, K, out_scale, split ? 1 : 0);
   ASB_CHECK_LAUNCH("fold_wsum16_kernel");
   return ASB_OK;
 }
@@ -704,13 +774,15 @@ static int fold_bias(const float* W, const float* beta, const float* b, float* d
 
 int pack_umma16_image(asb_model* m, const asb_weights* s, cudaStream_t st) {
   float* img = m->w.umma16_image;
-  const size_t total = umma16_image_floats(m->N);
+  const bool split = split_of(m);
+  const int W = split ? 2 : 1;
+  const size_t total = umma16_image_floats(m->N, split);
   ASB_TRY(check_cuda(cudaMemsetAsync(img, 0, total * sizeof(float), st), "pack_umma16_image: memset"));
   ASB_TRY(fold_bias(nullptr, nullptr, s->linear_b, img, kH, 0, st));
-  ASB_TRY(pack_mat(s->linear_w, nullptr, img + kLinParams, kH, 0, kH, 2 * kH, st));
+  ASB_TRY(pack_mat(s->linear_w, nullptr, img + kLinParams, kH, 0, kH, 2 * kH, 2, split, st));
   const int D = m->D;
   for (int i = 0; i < m->N; ++i) {
-    float* blk = img + kLinBlock + (size_t)i * kArtBlock;
+    float* blk = img + lin_block(split) + (size_t)i * art_block(split);
     // LayerNorm affines folded forward: W' = W diag(gamma), b' = b + W beta   (models.py:11-21)
     ASB_TRY(fold_bias(s->fc1_w[i], s->ln0_b[i], s->fc1_b[i], blk + P_B1, kFc, kH, st));
     ASB_TRY(fold_bias(s->fc2_w[i], s->ln1_b[i], s->fc2_b[i], blk + P_B2, kFc, kFc, st));
@@ -718,16 +790,16 @@ int pack_umma16_image(asb_model* m, const asb_weights* s, cudaStream_t st) {
     const double kNegLog2e = -1.4426950408889634;
     ASB_TRY(fold_bias(s->xh_w[i], s->ln2_b[i], s->xh_b[i], blk + P_BH, D, kFc, st, kNegLog2e));
     ASB_TRY(fold_bias(s->yh_w[i], s->ln2_b[i], s->yh_b[i], blk + P_BH + D, D, kFc, st, kNegLog2e));
-    ASB_TRY(fold_wsum(s->fc2_w[i], s->ln1_w[i], blk + P_WS2, kFc, kFc, st));
-    ASB_TRY(fold_wsum(s->xh_w[i], s->ln2_w[i], blk + P_WSH, D, kFc, st, kNegLog2e));
-    ASB_TRY(fold_wsum(s->yh_w[i], s->ln2_w[i], blk + P_WSH + D, D, kFc, st, kNegLog2e));
+    ASB_TRY(fold_wsum(s->fc2_w[i], s->ln1_w[i], blk + P_WS2, kFc, kFc, split, st));
+    ASB_TRY(fold_wsum(s->xh_w[i], s->ln2_w[i], blk + P_WSH, D, kFc, split, st, kNegLog2e));
+    ASB_TRY(fold_wsum(s->yh_w[i], s->ln2_w[i], blk + P_WSH + D, D, kFc, split, st, kNegLog2e));
     float* w1 = blk + kArtParams;
-    float* w2 = w1 + 2 * kFcChunk;
-    float* wh = w2 + 4 * kFcChunk;
-    ASB_TRY(pack_mat(s->fc1_w[i], s->ln0_w[i], w1, kFc, 0, kFc, kH, st));
-    ASB_TRY(pack_mat(s->fc2_w[i], s->ln1_w[i], w2, kFc, 0, kFc, kFc, st));
-    ASB_TRY(pack_mat(s->xh_w[i], s->ln2_w[i], wh, D, 0, kHeadN, kFc, st));
-    ASB_TRY(pack_mat(s->yh_w[i], s->ln2_w[i], wh, D, D, kHeadN, kFc, st));
+    float* w2 = w1 + W * 2 * kFcChunk;
+    float* wh = w2 + W * 4 * kFcChunk;
+    ASB_TRY(pack_mat(s->fc1_w[i], s->ln0_w[i], w1, kFc, 0, kFc, kH, 1, split, st));
+    ASB_TRY(pack_mat(s->fc2_w[i], s->ln1_w[i], w2, kFc, 0, kFc, kFc, 1, split, st));
+    ASB_TRY(pack_mat(s->xh_w[i], s->ln2_w[i], wh, D, 0, kHeadN, kFc, 2, split, st));
+    ASB_TRY(pack_mat(s->yh_w[i], s->ln2_w[i], wh, D, D, kHeadN, kFc, 2, split, st));
   }
   return ASB_OK;
 }
@@ -735,8 +807,13 @@ int pack_umma16_image(asb_model* m, const asb_weights* s, cudaStream_t st) {
 int launch_decoder_umma16(const asb_model* m, const float* rnn_out, float* out, int M, cudaStream_t st) {
   static DeviceOnce once;
   if (int rc = once.run([&] {
-        return check_cuda(cudaFuncSetAttribute(decoder_umma16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes),
-                          "decoder_umma16_kernel smem attribute");
+        if (int r = check_cuda(cudaFuncSetAttribute(decoder_umma16_kernel<false>,
+                                                    cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes),
+                               "decoder_umma16_kernel smem attribute"))
+          return r;
+        return check_cuda(cudaFuncSetAttribute(decoder_umma16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               kSmemBytes),
+                          "decoder_umma16_kernel (split) smem attribute");
       }))
     return rc;
   const int sms = sm_count();
@@ -750,7 +827,10 @@ int launch_decoder_umma16(const asb_model* m, const float* rnn_out, float* out, 
   a.D = m->D;
   a.n_items = (long long)n_tiles * m->N;
   const int grid = int(a.n_items < sms ? a.n_items : sms);
-  decoder_umma16_kernel<<<grid, kThreads, kSmemBytes, st>>>(a);
+  if (split_of(m))
+    decoder_umma16_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(a);
+  else
+    decoder_umma16_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(a);
   ASB_CHECK_LAUNCH("decoder_umma16_kernel");
   return ASB_OK;
 }

@@ -94,7 +94,9 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   const size_t o_head_w = p.take(sizeof(float) * N * kHeadPad * kFc), o_head_b = p.take(sizeof(float) * N * kHeadPad);
   const bool umma = umma_decoder_supported(m);
   const size_t o_umma = umma ? p.take(sizeof(float) * umma_image_floats(n_art)) : 0;
-  const size_t o_umma16 = umma ? p.take(sizeof(float) * umma16_image_floats(n_art)) : 0;
+  const bool umma16 = umma16_decoder_supported(m);   // both precisions (fp32: split fp16 operands)
+  const size_t o_umma16 =
+      umma16 ? p.take(sizeof(float) * umma16_image_floats(n_art, m->precision != ASB_PRECISION_FAST)) : 0;
   const bool rnnu = rnn_umma_supported(m);
   size_t o_whhu[2][2] = {{0, 0}, {0, 0}};
   if (rnnu)
@@ -139,17 +141,17 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   w.ln2_w = F(o_ln2_w); w.ln2_b = F(o_ln2_b);
   w.head_w = F(o_head_w); w.head_b = F(o_head_b);
   w.umma_image = umma ? F(o_umma) : nullptr;
-  w.umma16_image = umma ? F(o_umma16) : nullptr;
+  w.umma16_image = umma16 ? F(o_umma16) : nullptr;
   w.proj_image = proj ? F(o_proj) : nullptr;
   for (int l = 0; l < 2; ++l)
     for (int d = 0; d < 2; ++d) w.whh_umma[l][d] = rnnu ? static_cast<void*>(b + o_whhu[l][d]) : nullptr;
-  m->decoder_impl = umma ? 2 : 0;   // fast precision: the fp16-operand tcgen05 decoder
+  m->decoder_impl = umma16 ? 2 : 0;   // the fp16-operand tcgen05 decoder (split operands in fp32 precision)
   m->rnn_impl = rnnu ? 1 : 0;   // fast precision: the tcgen05 kernel (W_hh in tensor memory); the LSTM cell exists only there
 
   int rc = pack_recurrent_weights(m, src, st);
   if (!rc) rc = pack_dense_weights(m, src, st);
   if (!rc && umma) rc = pack_umma_image(m, src, st);
-  if (!rc && umma) rc = pack_umma16_image(m, src, st);
+  if (!rc && umma16) rc = pack_umma16_image(m, src, st);
   if (!rc && proj) rc = pack_proj_image(m, st);
   if (!rc && rnnu) rc = pack_whh_umma(m, src, st);
   if (!rc) rc = check_cuda(cudaStreamSynchronize(st), "asb_model_create: packing kernels");
@@ -331,8 +333,10 @@ extern "C" int asb_model_set_recurrent(asb_model* m, int impl) {
 
 extern "C" int asb_model_set_decoder(asb_model* m, int impl) {
   if (!m) return set_error(ASB_ERR_INVALID, "asb_model_set_decoder: null model");
-  if (impl >= 1 && !m->w.umma_image)
-    return set_error(ASB_ERR_UNSUPPORTED, "asb_model_set_decoder: the tcgen05 decoder needs fast precision and n_samples = 50");
+  if (impl == 1 && !m->w.umma_image)
+    return set_error(ASB_ERR_UNSUPPORTED, "asb_model_set_decoder: the tf32 tcgen05 decoder needs fast precision and n_samples = 50");
+  if (impl == 2 && !m->w.umma16_image)
+    return set_error(ASB_ERR_UNSUPPORTED, "asb_model_set_decoder: the tcgen05 decoder needs n_samples = 50");
   if (impl < 0 || impl > 2) return set_error(ASB_ERR_INVALID, "asb_model_set_decoder: impl must be 0, 1 or 2");
   m->decoder_impl = impl;
   return ASB_OK;

@@ -93,7 +93,7 @@ int pack_umma_image(asb_model* m, const asb_weights* w, cudaStream_t st);
 int launch_decoder_umma(const asb_model* m, const float* rnn_out, float* out, int M, cudaStream_t st);
 
 // ---- tcgen05 decoder, fp16 operands (decoder_umma16.cu) -------------------------------
-size_t umma16_image_floats(int n_art);
+size_t umma16_image_floats(int n_art, bool split);
 bool umma16_decoder_supported(const asb_model* m);
 int pack_umma16_image(asb_model* m, const asb_weights* w, cudaStream_t st);
 int launch_decoder_umma16(const asb_model* m, const float* rnn_out, float* out, int M, cudaStream_t st);

@@ -175,6 +175,20 @@ __device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
   asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
   return r;
 }
+// the part of (lo, hi) the packed fp16 pair `packed` lost, again as an fp16 pair: with it the pair carries
+// 22 significand bits (the split operands of the fp32-precision tensor-core kernels)
+__device__ __forceinline__ uint32_t residual_f16x2(float lo, float hi, uint32_t packed) {
+  float f0, f1;
+  asm("{\n\t"
+      ".reg .b16 a, b;\n\t"
+      "mov.b32 {a, b}, %2;\n\t"
+      "cvt.f32.f16 %0, a;\n\t"
+      "cvt.f32.f16 %1, b;\n\t"
+      "}\n"
+      : "=f"(f0), "=f"(f1)
+      : "r"(packed));
+  return pack_f16x2(lo - f0, hi - f1);
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t to_tf32(float x) {

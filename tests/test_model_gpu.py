@@ -261,6 +261,30 @@ def test_decoder_implementations_agree(mods):
     net.set_decoder("tcgen05")
 
 
+def test_fp32_decoder_implementations_agree(mods):
+    """fp32 precision: the tcgen05 decoder with SPLIT fp16 operands (hi + lo, three MMAs per product; default)
+    against the fp32 FFMA decoder and the fp32 oracle, partly filled tile, perturbed LayerNorm affines."""
+    models, omodel = mods
+    sd = omodel.randomize_affine(omodel.make_state_dict(45, 10, seed=0), seed=9)
+    net = _build(models, sd, "fp32")
+    B, T = 41, 37
+    x = synthetic.tokens(B, T, 45, seed=3)
+    L = synthetic.sorted_lengths(B, 5, T, seed=3)
+    want = omodel.artspeech_forward(sd, x[:8], L[:8], torch.float32)
+    outs = {}
+    for impl in ("tcgen05", "mma"):
+        net.set_decoder(impl)
+        with torch.no_grad():
+            outs[impl] = net(x.cuda(), L).cpu()
+        err = (outs[impl][:8, :want.shape[1]] - want).abs().max().item()
+        print(f"fp32 decoder[{impl}] max-abs vs fp32 oracle {err:.3e}")
+        assert err <= TOL["fp32"] and not torch.isnan(outs[impl]).any()
+    assert (outs["tcgen05"] - outs["mma"]).abs().max().item() <= 5e-6
+    with pytest.raises(ValueError):
+        net.set_decoder("tcgen05-tf32")      # the tf32 kernel exists in fast precision only
+    net.set_decoder("tcgen05")
+
+
 def test_errors_and_state_dict(mods):
     models, omodel = mods
     sd = omodel.make_state_dict(45, 2, seed=0)
