@@ -99,6 +99,8 @@ SIGNATURES = {
     "asb_eval_accumulate_total": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                                  ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                                  ctypes.c_void_p]),
+    "asb_eval_accumulate_static": (ctypes.c_int, [_c_f32p, _c_f32p, _c_f32p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                                                  ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]),
     "asb_eval_step": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int32),
                                      ctypes.c_void_p, ctypes.c_int, _c_f32p, ctypes.POINTER(ctypes.c_int32), _c_f32p,
                                      ctypes.c_int64, ctypes.POINTER(AsbEvalBuffers), ctypes.c_void_p,

@@ -169,6 +169,57 @@ extern "C" int asb_eval_accumulate_total(const float* p2cp, const float* tv_pred
   return ASB_OK;
 }
 
+// ---- allocation-free variant: the per-utterance partials live in a file-scope device array ------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (graph capture, serving loops).  Every GPU that loads the library holds the array until exit.
+// Nothing in it has to start at zero: utterance_partials_kernel overwrites every element the reduction reads.
+// All calls on a device share it, so two calls that overlap on the GPU (different streams) race.
+constexpr int kStaticScratchDoubles = ASB_EVAL_STATIC_MAX_DOUBLES;
+static __device__ __align__(256) double g_static_partials[kStaticScratchDoubles];
+
+namespace {
+// `g_static_partials` in host code is the host-side stand-in of the symbol, not a device address: the address
+// is looked up once per device (with that device current) and cached.
+int static_partials(double** out) {
+  static std::atomic<double*> cache[64];
+  int dev = -1;
+  if (int rc = asb::check_cuda(cudaGetDevice(&dev), "asb_eval_accumulate_static: cudaGetDevice")) return rc;
+  const bool cached = dev >= 0 && dev < 64;
+  double* p = cached ? cache[dev].load(std::memory_order_acquire) : nullptr;
+  if (!p) {
+    if (int rc = asb::check_cuda(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_partials),
+                                 "asb_eval_accumulate_static: cudaGetSymbolAddress"))
+      return rc;
+    if (!p) return asb::set_error(ASB_ERR_CUDA, "asb_eval_accumulate_static: null symbol address");
+    if (cached) cache[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return ASB_OK;
+}
+}  // namespace
+
+extern "C" int asb_eval_accumulate_static(const float* p2cp, const float* tv_pred, const float* tv_target,
+                                          const int32_t* lengths_dev, int B, int T, int n_art, double* acc,
+                                          void* stream) {
+  if (B <= 0 || T <= 0 || n_art <= 0 || n_art + 13 > 64)
+    return asb::set_error(ASB_ERR_INVALID, "asb_eval_accumulate_static: bad shape (B %d, T %d, n_art %d)", B, T, n_art);
+  if ((long long)B * (n_art + 12) > kStaticScratchDoubles)
+    return asb::set_error(ASB_ERR_WORKSPACE,
+                          "asb_eval_accumulate_static: B * (n_art + 12) = %lld doubles exceeds the built-in scratch of "
+                          "%d doubles; use asb_eval_accumulate with caller-provided scratch",
+                          (long long)B * (n_art + 12), kStaticScratchDoubles);
+  if (!p2cp || !tv_pred || !tv_target || !lengths_dev || !acc)
+    return asb::set_error(ASB_ERR_INVALID, "asb_eval_accumulate_static: null pointer");
+  double* scratch = nullptr;
+  if (int rc = static_partials(&scratch)) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  utterance_partials_kernel<<<B, 256, 0, st>>>(p2cp, tv_pred, tv_target, lengths_dev, T, n_art, scratch);
+  ASB_CHECK_LAUNCH("utterance_partials_kernel (static scratch)");
+  reduce_partials_kernel<<<1, 1024, 0, st>>>(scratch, lengths_dev, B, T, n_art, acc, nullptr);
+  ASB_CHECK_LAUNCH("reduce_partials_kernel (static scratch)");
+  return ASB_OK;
+}
+
 extern "C" int asb_eval_sentence_metrics(const float* outputs, const float* targets, const int32_t* lengths_dev, int B,
                                          int T, int n_art, int n_points, double* scratch, double* acc, void* stream) {
   if (B <= 0 || T <= 0 || n_art <= 0 || n_points <= 0 || n_points > 64)

@@ -164,6 +164,19 @@ ASB_API int asb_eval_accumulate_total(const float* p2cp, const float* tv_pred, c
                               const int32_t* lengths_dev, int B, int T, int n_art, double* scratch,
                               double* acc, double* total, void* stream);
 
+/* asb_eval_accumulate WITHOUT caller scratch and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  The per-utterance partials live in a file-scope device array
+ * of ASB_EVAL_STATIC_MAX_DOUBLES doubles (256 KiB, held by every GPU that loads the library until exit); the
+ * call returns ASB_ERR_WORKSPACE when B * (n_art + 12) exceeds it (e.g. B <= 1489 at n_art = 10).  Same inputs,
+ * same `acc` (n_art+14 doubles, overwritten) and the same bits as asb_eval_accumulate.  It calls no cudaMalloc /
+ * cudaFree / allocating routine; the array's device address is looked up once per device (cudaGetSymbolAddress)
+ * on the first call there.  All calls on one GPU SHARE the array: calls that overlap on the GPU (different
+ * streams without an ordering between them) race; stream-ordered calls are safe, nothing needs clearing. */
+#define ASB_EVAL_STATIC_MAX_DOUBLES 32768
+ASB_API int asb_eval_accumulate_static(const float* p2cp, const float* tv_pred, const float* tv_target,
+                               const int32_t* lengths_dev, int B, int T, int n_art, double* acc, void* stream);
+
 /* The other per-sentence numbers of run_test (evaluation.py:68-84): outputs/targets
  * (B,T,n_art,2,n_points) fp32 planar, lengths_dev (B) DEVICE int32.  Per sentence and articulator:
  * the mean over valid frames of euclidean_distance (metrics.py:54-68) and, over the valid frames as
