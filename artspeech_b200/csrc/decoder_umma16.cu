@@ -253,8 +253,8 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
   uint64_t* empty = bars + 8;       // [kStages]  MMAs that read the stage completed
   uint64_t* pfull = bars + 16;      // [2]        articulator parameters landed
   uint64_t* pempty = bars + 18;     // [2]        epilogue and output warps finished with them
-  uint64_t* chunk = bars + 20;      // [8]        32-column K chunk j of the A operand is in TMEM (K = 256 GEMMs)
-  uint64_t* a1bar = bars + 28;      // [4]        the same for the A operand of FC1 (K = 128)
+  uint64_t* chunk = bars + 20;      // [4]        64 k (two 32-column chunks) of the A operand are in TMEM (K = 256 GEMMs)
+  uint64_t* a1bar = bars + 28;      // [2]        the same for the A operand of FC1 (K = 128)
   uint64_t* dbar = bars + 32;       // [4]        accumulator of linear.0 / FC1 / FC2 / heads complete
   uint64_t* d3_free = bars + 36;    //            the output warps have read the heads accumulator
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 37);
@@ -270,8 +270,8 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
       mbar_init(&pfull[s], 1);
       mbar_init(&pempty[s], kEpiWarps + kHeadWarps);
     }
-    for (int j = 0; j < 8; ++j) mbar_init(&chunk[j], 4);   // the four lane quarters of the owning half
-    for (int j = 0; j < 4; ++j) mbar_init(&a1bar[j], 4);
+    for (int j = 0; j < 4; ++j) mbar_init(&chunk[j], 8);   // 64 k of A: one 32-k chunk of each half x four lane quarters
+    for (int j = 0; j < 2; ++j) mbar_init(&a1bar[j], 8);
     for (int j = 0; j < 4; ++j) mbar_init(&dbar[j], 1);
     mbar_init(d3_free, kHeadWarps);
     fence_mbar_init();
@@ -337,53 +337,57 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
     {
       uint32_t c = 0, artc = 0, ph_chunk = 0, ph_a1 = 0;
       TR_DECL;
-      // K chunk j is issued as soon as its 32 A columns are in TMEM and its weight stage is in shared
-      // memory.  The whole warp walks the loop and one ELECTED lane issues (tools/micro/umma_rate.cu:
-      // behind `lane == 0` every MMA is wrapped in an R2UR/ELECT loop and costs ~300 clk to issue; this
-      // form issues 4 MMAs + commit + the waits in ~340 clk, hidden behind the 4 x 127 clk an N = 256
-      // chunk executes).  A stage costs one full-wait and one commit.
-      // k_chunks A chunks of 32 k (16 TMEM columns each, at a_tmem + 32 j); a weight block holds 64 k = two A
-      // chunks; a ring stage holds `blocks_per_stage` blocks of `block_bytes`.
-      auto gemm = [&](uint32_t d_tmem, uint32_t a_tmem, uint32_t n, int k_chunks, int blocks_per_stage,
+      // The whole warp walks the loop and one ELECTED lane issues (tools/micro/umma_rate.cu: behind
+      // `lane == 0` every MMA is wrapped in an R2UR/ELECT loop and costs ~300 clk to issue).
+      // One iteration = one 64-k WEIGHT BLOCK = two 32-k A chunks (one of each epilogue half, produced
+      // concurrently and signalled on ONE barrier of 8 arrivals): 4 MMAs (12 split) + the commits per iteration.
+      // With one iteration per 32-k chunk the issuing warp itself was the critical path of the kernel: ~450 clk
+      // per iteration (waits, descriptor moves to uniform registers, UTCHMMA / UTCBAR issue) x 20 per articulator.
+      // k_blocks blocks of 64 k (A columns at a_tmem + 64 b); a ring stage holds `blocks_per_stage` blocks.
+      auto gemm = [&](uint32_t d_tmem, uint32_t a_tmem, uint32_t n, int k_blocks, int blocks_per_stage,
                       uint32_t block_bytes, uint64_t* abar, uint32_t& ph, uint64_t* done) {
         const uint32_t idesc = idesc_f16_m128(n);
         TR(0, 100 + n);
-        for (int j = 0; j < k_chunks; ++j) {
-          const int blk = (j >> 1) % blocks_per_stage;            // block inside the stage
-          const bool opens = (j & 1) == 0 && blk == 0;
-          const bool closes = (j & 1) == 1 && blk == blocks_per_stage - 1;
+        for (int b = 0; b < k_blocks; ++b) {
+          const int blk = b % blocks_per_stage;            // block inside the stage
+          const bool opens = blk == 0;
+          const bool closes = blk == blocks_per_stage - 1;
           const uint32_t st = c % kStages, st_lo = (c + 1) % kStages;   // split: the residual piece follows in the ring
-          mbar_wait(&abar[j], (ph >> j) & 1);
-          ph ^= 1u << j;
+          mbar_wait(&abar[b], (ph >> b) & 1);
+          ph ^= 1u << b;
+          TR(0, 30 + b);
           if (opens && ASB_DEC_ABLATE != 4) {
             mbar_wait(&full[st], (c / kStages) & 1);
             if (kSplit) mbar_wait(&full[st_lo], ((c + 1) / kStages) & 1);
           }
           fence_after_sync();
-          TR(0, 10 + j);
-          // 32 k = 64 bytes into the 128-byte swizzled row: the descriptor's start address advances by 64 >> 4
-          const uint64_t bdesc = smem_desc_k_sw128(smem_u32(Ws + st * kStageBytes + blk * block_bytes)) + uint64_t(4 * (j & 1));
-          const uint64_t bdesc_lo =
-              smem_desc_k_sw128(smem_u32(Ws + st_lo * kStageBytes + blk * block_bytes)) + uint64_t(4 * (j & 1));
-          const uint32_t acol = a_tmem + j * kChunkK;
+          TR(0, 10 + b);
+          const uint64_t bdesc = smem_desc_k_sw128(smem_u32(Ws + st * kStageBytes + blk * block_bytes));
+          const uint64_t bdesc_lo = smem_desc_k_sw128(smem_u32(Ws + st_lo * kStageBytes + blk * block_bytes));
+          const uint32_t acol = a_tmem + b * 2 * kChunkK;
           if (elect_one()) {
 #pragma unroll
-            for (int ks = 0; ks < (ASB_DEC_ABLATE == 3 ? 0 : 2); ++ks) {
+            for (int ks = 0; ks < (ASB_DEC_ABLATE == 3 ? 0 : 4); ++ks) {
+              // 16 k = 32 bytes into the 128-byte swizzled row: the descriptor's start address advances by 32 >> 4;
+              // A: 32-column chunk ks / 2, fp16 pairs of its k-step ks % 2 at columns 8 (ks % 2)
+              const uint32_t ac = acol + (ks >> 1) * kChunkK + (ks & 1) * 8;
+              const uint64_t bd = bdesc + uint64_t(2 * ks), bd_lo = bdesc_lo + uint64_t(2 * ks);
               if (kSplit) {   // hi pairs in columns [0, 16) of the chunk, residual pairs in [16, 32); small terms first
-                mma_bf16_ts(d_tmem, acol + 16 + ks * 8, bdesc + uint64_t(2 * ks), idesc, (j | ks) != 0);   // a_lo w_hi
-                mma_bf16_ts(d_tmem, acol + ks * 8, bdesc_lo + uint64_t(2 * ks), idesc, true);              // a_hi w_lo
-                mma_bf16_ts(d_tmem, acol + ks * 8, bdesc + uint64_t(2 * ks), idesc, true);                 // a_hi w_hi
+                mma_bf16_ts(d_tmem, ac + 16, bd, idesc, (b | ks) != 0);   // a_lo w_hi
+                mma_bf16_ts(d_tmem, ac, bd_lo, idesc, true);              // a_hi w_lo
+                mma_bf16_ts(d_tmem, ac, bd, idesc, true);                 // a_hi w_hi
               } else {
-                mma_bf16_ts(d_tmem, acol + ks * 8, bdesc + uint64_t(2 * ks), idesc, (j | ks) != 0);
+                mma_bf16_ts(d_tmem, ac, bd, idesc, (b | ks) != 0);
               }
             }
             if (closes && ASB_DEC_ABLATE != 4) {   // frees the stage(s) once their MMAs have read them
               commit(&empty[st]);
               if (kSplit) commit(&empty[st_lo]);
             }
-            if (j == k_chunks - 1) commit(done);
+            if (b == k_blocks - 1) commit(done);
           }
           __syncwarp();
+          TR(0, 50 + b);
           if (closes) c += kW;
         }
         TR(0, 99);
@@ -402,14 +406,14 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
         {
           const uint32_t P = tmem_base + (artc & 1) * 256, Q = tmem_base + ((artc & 1) ^ 1) * 256;
           wait_heads_read();
-          gemm(P, Q, 128, 8, 2, kLinChunk * 4, chunk, ph_chunk, &dbar[0]);     // linear.0          K = 256: 4 blocks of 16 KB
+          gemm(P, Q, 128, 4, 2, kLinChunk * 4, chunk, ph_chunk, &dbar[0]);     // linear.0          K = 256: 4 blocks of 16 KB
         }
         for (int k = 0; k < g1 - g0; ++k) {
           const uint32_t P = tmem_base + (artc & 1) * 256, Q = tmem_base + ((artc & 1) ^ 1) * 256;
-          gemm(Q, P + 128, 256, 4, 1, 0, a1bar, ph_a1, &dbar[1]);              // Linear(128, 256): 2 blocks of 32 KB
+          gemm(Q, P + 128, 256, 2, 1, 0, a1bar, ph_a1, &dbar[1]);              // Linear(128, 256): 2 blocks of 32 KB
           wait_heads_read();
-          gemm(P, Q, 256, 8, 1, 0, chunk, ph_chunk, &dbar[2]);                 // Linear(256, 256): 4 blocks of 32 KB
-          gemm(Q, P, kHeadN, 8, 2, kHeadChunk * 4, chunk, ph_chunk, &dbar[3]);  // x/y heads: 4 blocks of 14 KB
+          gemm(P, Q, 256, 4, 1, 0, chunk, ph_chunk, &dbar[2]);                 // Linear(256, 256): 4 blocks of 32 KB
+          gemm(Q, P, kHeadN, 4, 2, kHeadChunk * 4, chunk, ph_chunk, &dbar[3]);  // x/y heads: 4 blocks of 14 KB
           ++artc;
         }
       }
@@ -581,7 +585,7 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
           unpack2(qb, q2, q3);
           publish(stat, (s0 + s1) + (s2 + s3), (q0 + q1) + (q2 + q3));
         }
-        signal(&chunk[ch]);
+        signal(&chunk[ch >> 1]);
       };
       if (ASB_DEC_ABLATE != 2) tmem_ld32(region + 32 * half, r);
 #pragma unroll
@@ -611,7 +615,7 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
         }
         tmem_st16(region + 128 + 32 * ch, h);
         if (kSplit) st_lo16(region + 128 + 32 * ch + 16, l);
-        signal(&a1bar[ch]);
+        signal(&a1bar[ch >> 1]);
       }
     };
 
@@ -665,7 +669,7 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
           __syncwarp();   // the tile is rewritten by the next block
           tmem_st16(Q + 32 * ch, h);
           if (kSplit) st_lo16(Q + 32 * ch + 16, l);
-          signal(&chunk[ch]);
+          signal(&chunk[ch >> 1]);
         }
         // ---- linear.0 epilogue: relu(D0 + b) -> LayerNorm(128) -> x-hat (fp32) kept in shared memory
         wait_d(0, unitc);

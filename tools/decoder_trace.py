@@ -16,7 +16,7 @@ with torch.no_grad():
         net(x, L)
 torch.cuda.synchronize()
 buf = (ctypes.c_longlong * (8 * 4096))()
-fn = _lib.lib().asb_debug_decoder_trace
+fn = getattr(_lib.lib(), os.environ.get("ASB_TRACE_FN", "asb_debug_decoder16_trace"))   # tf32 kernel: asb_debug_decoder_trace
 fn.argtypes = [ctypes.POINTER(ctypes.c_longlong)]
 assert fn(buf) == 0
 ev = []
@@ -30,7 +30,8 @@ ev.sort()
 t0 = ev[0][0]
 names = {99: "commit D", 200: "D ready seen", 201: "chunk signalled", 300: "heads begin", 301: "heads end"}
 limit = int(sys.argv[1]) if len(sys.argv) > 1 else 260
-for t, role, tag in ev[:limit]:
+skip = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+for t, role, tag in ev[skip:skip + limit]:
     if tag >= 600:
         what = {600: "heads D seen", 603: "heads D read (freed)", 604: "contours stored"}[tag]
     elif tag >= 500:
@@ -38,5 +39,6 @@ for t, role, tag in ev[:limit]:
     elif tag >= 400:
         what = f"copy into slot {tag - 400} issued"
     else:
-        what = names.get(tag, f"gemm N={tag - 100} begin" if tag >= 100 else f"A chunk {tag - 10} ready")
+        what = names.get(tag, f"gemm N={tag - 100} begin" if tag >= 100 else f"chunk {tag - 50} MMAs issued" if tag >= 50
+                         else f"A chunk {tag - 30} in TMEM seen" if tag >= 30 else f"A chunk {tag - 10} ready (weights too)")
     print(f"{t - t0:8d}  {['MMA ', 'EPI0', 'EPI1', 'PROD', 'OUT0', 'OUT1', 'OUT2', 'OUT3'][role]}  {what}")
