@@ -64,6 +64,10 @@
 #ifndef ASB_DEC_ABLATE
 #define ASB_DEC_ABLATE 0
 #endif
+// 1 = every lane stores 16-byte pieces of its own row (round-2 first form) instead of the transposed, coalesced stores
+#ifndef ASB_DEC_OUT_DIRECT
+#define ASB_DEC_OUT_DIRECT 0
+#endif
 
 #ifdef ASB_DEC_TRACE
 // timeline of CTA 0 (tools/decoder_trace.py): [role][event] = (tag, clock64) for the MMA thread (0),
@@ -125,7 +129,9 @@ constexpr int kOffX = kOffW + kStages * kStageBytes;
 constexpr int kOffP = kOffX + kTileM * kXStride * 4;
 constexpr int kOffLinB = kOffP + 2 * kArtParams * 4;
 constexpr int kOffStat = kOffLinB + kLinParams * 4;       // float2 [8][128 rows]: see Stat0/1/2 in the kernel
-constexpr int kOffBar = kOffStat + 8 * kTileM * 8;
+constexpr int kOffOut = kOffStat + 8 * kTileM * 8;          // [4 output warps][32 rows][32 floats]: store transposition
+constexpr int kOutTile = 32 * 32 * 4;
+constexpr int kOffBar = kOffOut + kHeadWarps * kOutTile;
 constexpr int kSmemBytes = kOffBar + 512 + 1024;  // + barriers + alignment slack
 
 __device__ __forceinline__ float round_f16(float x) { return __half2float(__float2half_rn(x)); }
@@ -427,11 +433,12 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
     const uint32_t ps_addr = smem_u32(Ps);
     uint32_t pa = 0, artc = 0;
     uint32_t r[32], r2[32], r4[4];
+    float4* otile = reinterpret_cast<float4*>(smem + kOffOut + (warp - kHeadWarp0) * kOutTile);
     TR_DECL;
     UnitIter units(a);
     int tile, g0, g1;
     while (units.next(tile, g0, g1)) {
-      const long long grow = (long long)tile * kTileM + row;
+      const long long grow0 = (long long)tile * kTileM + quarter * 32, grow = grow0 + lane;
       const bool live = grow < a.M;
       for (int k = 0; k < g1 - g0; ++k) {
         const int art = g0 + k;
@@ -450,40 +457,86 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
         // the head parameters carry the factor -log2(e): t = -log2(e) (rstd D + b - rstd mean ws)
         const f32x2 rs2 = pack2(-1.4426950408889634f * rstd, -1.4426950408889634f * rstd), nm2 = pack2(nm, nm);
         float* dst = a.out + (grow * a.n_art + art) * 100;
-        auto emit = [&](const uint32_t* v, int col) {   // 4 columns
-          const float4 b4 = lds4(prm + (P_BH + col) * 4);
-          const float4 w4 = lds4(prm + (P_WSH + col) * 4);
-          float t0, t1, t2, t3;
-          unpack2(fma2(rs2, pack2(__uint_as_float(v[0]), __uint_as_float(v[1])),
-                       fma2(nm2, pack2(w4.x, w4.y), pack2(b4.x, b4.y))), t0, t1);
-          unpack2(fma2(rs2, pack2(__uint_as_float(v[2]), __uint_as_float(v[3])),
-                       fma2(nm2, pack2(w4.z, w4.w), pack2(b4.z, b4.w))), t2, t3);
-          __stcs(reinterpret_cast<float4*>(dst + col),
-                 make_float4(sigmoid_exp2(t0), sigmoid_exp2(t1), sigmoid_exp2(t2), sigmoid_exp2(t3)));
-        };
-        tmem_ld32(Q, r);
-        tmem_ld_wait();
-        tmem_ld32(Q + 32, r2);
-        if (live) {
+        // plain shared-memory loads (not the volatile lds4): the compiler may batch them and interleave the 32
+        // independent sigmoid chains of a column group (serialised, a group cost ~1.8 k clk of pure latency)
+        const float4* prm4 = reinterpret_cast<const float4*>(Ps + pb * kArtParams);
+        auto sig32 = [&](const uint32_t(&v)[32], int col0, float (&y)[32]) {
 #pragma unroll
-          for (int q = 0; q < 8; ++q) emit(&r[4 * q], 4 * q);
-        }
+          for (int q = 0; q < 8; ++q) {
+            const float4 b4 = prm4[(P_BH + col0) / 4 + q];
+            const float4 w4 = prm4[(P_WSH + col0) / 4 + q];
+            unpack2(fma2(rs2, pack2(__uint_as_float(v[4 * q + 0]), __uint_as_float(v[4 * q + 1])),
+                         fma2(nm2, pack2(w4.x, w4.y), pack2(b4.x, b4.y))), y[4 * q + 0], y[4 * q + 1]);
+            unpack2(fma2(rs2, pack2(__uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3])),
+                         fma2(nm2, pack2(w4.z, w4.w), pack2(b4.z, b4.w))), y[4 * q + 2], y[4 * q + 3]);
+          }
+#pragma unroll
+          for (int i = 0; i < 32; ++i) asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y[i]) : "f"(y[i]));
+#pragma unroll
+          for (int i = 0; i < 32; ++i) asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y[i]) : "f"(1.f + y[i]));
+        };
+        // 32 columns of the thread's own row -> the warp's transposition tile (16-byte unit u of row r at
+        // u ^ (r & 7): conflict-free both ways) -> COALESCED stores: one warp instruction writes 4 rows x 128
+        // contiguous bytes (with every lane storing 16 bytes of its own row - 4000 bytes apart - an instruction
+        // is 32 half-sector requests).
+        auto emit32 = [&](const uint32_t(&v)[32], int chunk) {
+          float y[32];
+          sig32(v, 32 * chunk, y);
+#if ASB_DEC_OUT_DIRECT
+          if (live) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              __stcs(reinterpret_cast<float4*>(dst + 32 * chunk + 4 * q),
+                     make_float4(y[4 * q], y[4 * q + 1], y[4 * q + 2], y[4 * q + 3]));
+          }
+#else
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            otile[lane * 8 + (q ^ (lane & 7))] = make_float4(y[4 * q], y[4 * q + 1], y[4 * q + 2], y[4 * q + 3]);
+          __syncwarp();
+          float4 val[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int rr = 4 * i + (lane >> 3);
+            val[i] = otile[rr * 8 + ((lane & 7) ^ (rr & 7))];
+          }
+          // rows 4 i + lane / 8 of this warp's 32: frame stride n_art * 100 floats
+          float* o = a.out + ((grow0 + (lane >> 3)) * a.n_art + art) * 100 + 32 * chunk + 4 * (lane & 7);
+          const long long rows_left = a.M - grow0 - (lane >> 3);
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (4 * i < rows_left) __stcs(reinterpret_cast<float4*>(o + (size_t)(4 * i) * a.n_art * 100), val[i]);
+          __syncwarp();   // the tile is rewritten by the next chunk
+#endif
+        };
+        // The accumulator columns are overwritten by FC2 of the NEXT articulator, which waits for the release
+        // below: it comes after ONE column group (two groups stay in registers; with all 100 columns loaded first the
+        // emission had no registers left to overlap its chains, with the release after two groups FC2 waited).
+        tmem_ld32(Q, r);
+        tmem_ld32(Q + 32, r2);
         tmem_ld_wait();
+        emit32(r, 0);
+        TR(4 + (warp - kHeadWarp0), 605);
         tmem_ld32(Q + 64, r);
         tmem_ld4(Q + 96, r4);
-        if (live) {
-#pragma unroll
-          for (int q = 0; q < 8; ++q) emit(&r2[4 * q], 32 + 4 * q);
-        }
         tmem_ld_wait();
         fence_before_sync();
         __syncwarp();
         if (lane == 0) mbar_arrive(d3_free);       // the accumulator columns may be overwritten now
         TR(4 + (warp - kHeadWarp0), 603);
-        if (live) {
-#pragma unroll
-          for (int q = 0; q < 8; ++q) emit(&r[4 * q], 64 + 4 * q);
-          emit(r4, 96);
+        emit32(r2, 1);
+        TR(4 + (warp - kHeadWarp0), 606);
+        emit32(r, 2);
+        TR(4 + (warp - kHeadWarp0), 607);
+        if (live) {   // the last 4 of the 100 columns
+          const float4 b4 = prm4[(P_BH + 96) / 4], w4 = prm4[(P_WSH + 96) / 4];
+          float t0, t1, t2, t3;
+          unpack2(fma2(rs2, pack2(__uint_as_float(r4[0]), __uint_as_float(r4[1])),
+                       fma2(nm2, pack2(w4.x, w4.y), pack2(b4.x, b4.y))), t0, t1);
+          unpack2(fma2(rs2, pack2(__uint_as_float(r4[2]), __uint_as_float(r4[3])),
+                       fma2(nm2, pack2(w4.z, w4.w), pack2(b4.z, b4.w))), t2, t3);
+          __stcs(reinterpret_cast<float4*>(dst + 96),
+                 make_float4(sigmoid_exp2(t0), sigmoid_exp2(t1), sigmoid_exp2(t2), sigmoid_exp2(t3)));
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&pempty[pb]);

@@ -3,6 +3,9 @@ import os
 import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
+from artspeech_b200 import _lib
+if os.environ.get("ASB_LIB"):   # a tools/build_variant.py library
+    _lib.LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), os.environ["ASB_LIB"])
 from artspeech_b200 import models, synthetic
 from oracle import model as omodel
 

@@ -33,7 +33,7 @@ limit = int(sys.argv[1]) if len(sys.argv) > 1 else 260
 skip = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 for t, role, tag in ev[skip:skip + limit]:
     if tag >= 600:
-        what = {600: "heads D seen", 603: "heads D read (freed)", 604: "contours stored"}[tag]
+        what = {600: "heads D seen", 603: "heads D read (freed)", 604: "contours stored", 605: "columns 0-31 out", 606: "columns 32-63 out", 607: "columns 64-95 out"}[tag]
     elif tag >= 500:
         what = f"weights in slot {tag - 500} seen"
     elif tag >= 400:
