@@ -77,7 +77,8 @@ def workload_config(world, B, T, precision):
 
 
 class ClockSampler:
-    """SM clock + throttle reasons sampled every 2 ms through NVML while the timed region runs."""
+    """SM clock + throttle reasons sampled every ms through NVML while the timed region runs (NVML is set up
+    before the region; the region itself adds one sample while its queue is still draining)."""
 
     def __init__(self, index):
         self.index = index
@@ -88,36 +89,48 @@ class ClockSampler:
         self.thread = None
         self.error = None
 
+    def _init(self):
+        """NVML set-up, done synchronously in start(): it takes longer than a short timed region."""
+        import pynvml as nv
+        nv.nvmlInit()
+        self._nv = nv
+        self._h = nv.nvmlDeviceGetHandleByIndex(self.index)
+        self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(self._h, nv.NVML_CLOCK_SM))
+        self._flags = {
+            "hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown",
+                                   getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0)),
+            "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown",
+                                           getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0)),
+            "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown",
+                                           getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0)),
+            "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap",
+                                    getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0)),
+        }
+        self._get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons",
+                                    getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons", None))
+
+    def sample(self):
+        self.samples.append(float(self._nv.nvmlDeviceGetClockInfo(self._h, self._nv.NVML_CLOCK_SM)))
+        if self._get_reasons is not None:
+            r = int(self._get_reasons(self._h))
+            for name, bit in self._flags.items():
+                if bit and (r & int(bit)):
+                    self.reasons.add(name)
+
     def _run(self):
         try:
-            import pynvml as nv
-            nv.nvmlInit()
-            h = nv.nvmlDeviceGetHandleByIndex(self.index)
-            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
-            flags = {
-                "hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown")
-                else nv.nvmlClocksThrottleReasonHwSlowdown,
-                "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown",
-                                               getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0)),
-                "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown",
-                                               getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0)),
-                "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap",
-                                        getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0)),
-            }
-            get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons",
-                                  getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons", None))
             while not self._stop.is_set():
-                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
-                if get_reasons is not None:
-                    r = int(get_reasons(h))
-                    for name, bit in flags.items():
-                        if bit and (r & int(bit)):
-                            self.reasons.add(name)
-                self._stop.wait(0.002)
-        except Exception as exc:  # NVML missing: report it instead of inventing numbers
+                self.sample()
+                self._stop.wait(0.001)
+        except Exception as exc:  # report it instead of inventing numbers
             self.error = repr(exc)
 
     def start(self):
+        try:
+            self._init()
+        except Exception as exc:  # NVML missing
+            self.error = repr(exc)
+            return
         self.thread = threading.Thread(target=self._run, daemon=True)
         self.thread.start()
 
@@ -327,7 +340,7 @@ def run_ours(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    def pipelined_region(net, steps, warm):
+    def pipelined_region(net, steps, warm, sampler=None):
         """K steps, two in flight; ONE all-reduce of the running totals at the end; returns (ms, total)."""
         pipe = evaluation.PipelinedEvaluator(net, B, T, upper_incisor=uinc_d, depth=2)
         pipe.begin()
@@ -343,6 +356,8 @@ def run_ours(args):
             pipe.step(tok_sets[i & 1], lengths, lengths_dev, tgt_sets[i & 1])
         total = pipe.finish(reduce=True)
         e.record()
+        if sampler is not None and sampler.thread is not None:
+            sampler.sample()                    # the queue is still draining: one sample is certainly under load
         torch.cuda.synchronize()
         launches = _lib.launch_count() - l0
         barrier()
@@ -352,7 +367,7 @@ def run_ours(args):
     pipelined_region(model, 2, W)              # first-touch, NCCL communicator, clocks
     sampler = ClockSampler(visible_index(local_rank))
     sampler.start()
-    total_ms, total_acc, launches = pipelined_region(model, K, W)
+    total_ms, total_acc, launches = pipelined_region(model, K, W, sampler)
     clocks = sampler.stop()
     value = world * frames * K / (total_ms * 1e-3)
     summary = evaluation.summarize(total_acc, N_ART)
