@@ -104,6 +104,8 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
       for (int d = 0; d < 2; ++d) o_whhu[l][d] = p.take(whh_umma_bytes(m));
   const bool proj = proj_umma_supported(m);
   const size_t o_proj = proj ? p.take(sizeof(float) * proj_image_floats(m)) : 0;
+  const bool proj16 = proj_umma16_supported(m);
+  const size_t o_proj16 = proj16 ? p.take(sizeof(float) * proj16_image_floats(m)) : 0;
 
   cudaError_t e = cudaMalloc(&m->arena, p.total);
   if (e != cudaSuccess) {
@@ -143,6 +145,7 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   w.umma_image = umma ? F(o_umma) : nullptr;
   w.umma16_image = umma16 ? F(o_umma16) : nullptr;
   w.proj_image = proj ? F(o_proj) : nullptr;
+  w.proj16_image = proj16 ? F(o_proj16) : nullptr;
   for (int l = 0; l < 2; ++l)
     for (int d = 0; d < 2; ++d) w.whh_umma[l][d] = rnnu ? static_cast<void*>(b + o_whhu[l][d]) : nullptr;
   m->decoder_impl = umma16 ? 2 : 0;   // the fp16-operand tcgen05 decoder (split operands in fp32 precision)
@@ -153,6 +156,7 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   if (!rc && umma) rc = pack_umma_image(m, src, st);
   if (!rc && umma16) rc = pack_umma16_image(m, src, st);
   if (!rc && proj) rc = pack_proj_image(m, st);
+  if (!rc && proj16) rc = pack_proj16_image(m, src, st);
   if (!rc && rnnu) rc = pack_whh_umma(m, src, st);
   if (!rc) rc = check_cuda(cudaStreamSynchronize(st), "asb_model_create: packing kernels");
   if (rc) {
@@ -267,7 +271,9 @@ static int forward_impl(asb_model* m, const int64_t* x, int T_in, const int32_t*
     if ((rc = launch_recurrent_layer(m, 0, ws.gi, ws.lengths, ws.out0, B, T, st))) return rc;
   }
   mark(2);
-  if (m->w.proj_image && m->decoder_impl >= 1) {  // the tcgen05 kernels are selected together
+  if (m->w.proj16_image && m->decoder_impl == 2) {  // the tcgen05 kernels are selected together
+    if ((rc = launch_proj_umma16(m, ws.out0, ws.gi, int(M), st))) return rc;
+  } else if (m->w.proj_image && m->decoder_impl == 1) {
     if ((rc = launch_proj_umma(m, ws.out0, ws.gi, int(M), st))) return rc;
   } else {
     if ((rc = launch_linear(m, ws.out0, m->w.wih1, m->w.bih1, ws.gi, int(M), 2 * m->G * kH, 2 * kH, st))) return rc;

@@ -37,6 +37,8 @@ struct PackedWeights {
   float* umma16_image;
   // pre-swizzled tf32 image of wih1 for the tcgen05 layer-1 projection (proj_umma.cu); fast mode only
   float* proj_image;
+  // fp16-operand image of W_ih_l1 (proj_umma16.cu); both precisions (fp32: hi + lo pieces)
+  float* proj16_image;
   // bf16 W_hh images (K-major, 128-byte swizzle) kept in shared memory by the tcgen05 recurrent
   // kernel (gru_umma.cu); fast mode only
   void* whh_umma[2][2];
@@ -103,6 +105,11 @@ size_t proj_image_floats(const asb_model* m);
 bool proj_umma_supported(const asb_model* m);
 int pack_proj_image(asb_model* m, cudaStream_t st);   // after pack_dense_weights (reads w.wih1)
 int launch_proj_umma(const asb_model* m, const float* A, float* C, int M, cudaStream_t st);
+// ---- the same with fp16 operands (split operands in fp32 precision), proj_umma16.cu ------
+size_t proj16_image_floats(const asb_model* m);
+bool proj_umma16_supported(const asb_model* m);
+int pack_proj16_image(asb_model* m, const asb_weights* src, cudaStream_t st);
+int launch_proj_umma16(const asb_model* m, const float* A, float* C, int M, cudaStream_t st);
 
 // ---- tcgen05 recurrent layer (gru_umma.cu) -------------------------------------------
 size_t whh_umma_bytes(const asb_model* m);
