@@ -20,7 +20,13 @@
 //     thread-local -, keep h (and the LSTM's c) in fp32 registers, write h as bf16 back into the B
 //     operand and the fp32 output row, and hand over to the MMA warp through one mbarrier; the
 //     input pre-activations of the next step are prefetched while the MMAs run.
+//   * kSplit = true (fp32 precision, GRU): W_hh and h are carried as hi + lo fp16 pairs (hi = fp16(v),
+//     lo = fp16(v - hi): 22 significand bits), a product is three MMAs (W_lo h_hi + W_hi h_lo + W_hi h_hi, fp32
+//     accumulate), W_hh takes 2 x 192 columns of tensor memory, h two 4 KB operands, and the gates use expf /
+//     tanhf.  72 MMAs per step instead of 24: ~0.9 us per step against 2.9 us of the FFMA kernel (gru.cu) with
+//     the same 1e-5 agreement (the LSTM's 2 x 256 columns do not fit beside the accumulators).
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include <cstdlib>
 
@@ -74,15 +80,22 @@ __host__ __device__ constexpr uint32_t sw128_bf16(uint32_t row, uint32_t k, uint
          ((((k & 63u) >> 3) ^ (row & 7u)) << 4) + (k & 7u) * 2u;
 }
 
-// whh (G*128, 128) fp32 -> bf16, same row-major layout (a row = the 64 TMEM columns of one lane)
-__global__ void pack_whh_umma_kernel(const float* __restrict__ whh, __nv_bfloat16* __restrict__ img, int G) {
+// whh (G*128, 128) fp32 -> bf16, same row-major layout (a row = the 64 TMEM columns of one lane);
+// split: fp16 hi image followed by the fp16 residual image
+__global__ void pack_whh_umma_kernel(const float* __restrict__ whh, uint16_t* __restrict__ img, int G, int split) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= G * kH * kH) return;
-  img[i] = __float2bfloat16_rn(whh[i]);
+  if (!split) {
+    img[i] = __bfloat16_as_ushort(__float2bfloat16_rn(whh[i]));
+  } else {
+    const __half hi = __float2half_rn(whh[i]);
+    img[i] = __half_as_ushort(hi);
+    img[G * kH * kH + i] = __half_as_ushort(__float2half_rn(whh[i] - __half2float(hi)));
+  }
 }
 
 struct RnnArgs {
-  const __nv_bfloat16* img[2];   // per direction
+  const uint16_t* img[2];        // per direction: bf16 (fast) or fp16 hi | fp16 lo (split)
   const float* bhhn[2];          // GRU: b_hh of the n gate
   const float* gi;               // (B*T, 2, G*H) input pre-activations, or (layer 0) null:
   const long long* tokens;       //   (B, T_in) token ids and
@@ -95,13 +108,16 @@ struct RnnArgs {
 };
 
 // CPT = batch columns per epilogue thread; the CTA owns 2 * CPT batch rows
-template <int G, int CPT>
+template <int G, int CPT, bool kSplit>
 __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) {
+  static_assert(!kSplit || G == 3, "split operands: 2 x G x 64 columns of W_hh must fit beside the accumulators");
+  constexpr int kW = kSplit ? 2 : 1;
+  constexpr int kHs = kW * kHsBytes;                 // split: the hi operand followed by the residual operand
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // keeps the shared address space
-  unsigned char* Hs = smem;                          // 4 KB
-  uint64_t* bars = reinterpret_cast<uint64_t*>(Hs + kHsBytes);
-  float* Gs = reinterpret_cast<float*>(Hs + kHsBytes + 64);   // [kGiSlots][CPT][G][256 threads] input pre-activations
+  unsigned char* Hs = smem;                          // 4 KB (8 KB split)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(Hs + kHs);
+  float* Gs = reinterpret_cast<float*>(Hs + kHs + 64);   // [kGiSlots][CPT][G][256 threads] input pre-activations
   int* Toks = reinterpret_cast<int*>(Gs + kGiSlots * CPT * G * 256);   // [2 * CPT rows][T] token ids (layer 0)
   uint64_t* h_ready = bars + 1;  // h (bf16) of this step is in shared memory, D has been read
   uint64_t* d_ready = bars + 2;  // this step's MMAs completed
@@ -112,7 +128,8 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
   const int b0 = blockIdx.x * 2 * CPT;
   const int Lmax = a.lengths[b0];   // sorted descending: the tile's first row is its longest
   constexpr int GH = G * kH;
-  constexpr uint32_t kTmemCols = (kACol0 + G * 64 <= 256) ? 256 : 512;
+  constexpr uint32_t kTmemCols = (kACol0 + kW * G * 64 <= 256) ? 256 : 512;
+  static_assert(kACol0 + kW * G * 64 <= 512, "tensor memory");
 
   if (tid == 0) {
     mbar_init(h_ready, kEpiWarps);
@@ -120,7 +137,7 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
     fence_mbar_init();
   }
   if (warp == kCtlWarp) tmem_alloc(tmem_slot, kTmemCols);
-  for (int i = tid; i < kHsBytes / 4; i += kThreads) reinterpret_cast<uint32_t*>(Hs)[i] = 0u;   // h0 = 0
+  for (int i = tid; i < kHs / 4; i += kThreads) reinterpret_cast<uint32_t*>(Hs)[i] = 0u;   // h0 = 0
   if (a.tokens) {   // layer 0: the embedding + input projection is a table look-up done by this kernel
     for (int i = tid; i < 2 * CPT * a.T; i += kThreads) {
       const int row = i / a.T, t = i - row * a.T;
@@ -142,7 +159,7 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
   if (warp == kCtlWarp) {
     // the whole warp walks the loop, one ELECTED lane issues (behind `lane == 0` the compiler wraps
     // every tcgen05.mma in an R2UR/ELECT loop that costs far more than the MMA itself)
-    const uint32_t idesc = idesc_bf16_m128(kRows);
+    const uint32_t idesc = kSplit ? idesc_f16_m128(kRows) : idesc_bf16_m128(kRows);
     const uint64_t bdesc0 = smem_desc_k_sw128(smem_u32(Hs));
     const uint32_t tmem_a = tmem_d + kACol0;
     TR_DECL;
@@ -160,7 +177,13 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
           for (int kt = 0; kt < 8; ++kt) {
             // k-step kt: 8 TMEM columns of A; B: atom kt / 4, 32 bytes (2 descriptor units) per step
             const uint64_t bd = bdesc0 + uint64_t(((kt >> 2) * kRows * 128) >> 4) + uint64_t(2 * (kt & 3));
-            mma_bf16_ts(tmem_d + g * kRows, tmem_a + g * 64 + kt * 8, bd, idesc, kt != 0);
+            if (kSplit) {   // small terms first; W_lo from column (G + g) * 64, h_lo kHsBytes behind h_hi
+              mma_bf16_ts(tmem_d + g * kRows, tmem_a + (G + g) * 64 + kt * 8, bd, idesc, kt != 0);
+              mma_bf16_ts(tmem_d + g * kRows, tmem_a + g * 64 + kt * 8, bd + uint64_t(kHsBytes >> 4), idesc, true);
+              mma_bf16_ts(tmem_d + g * kRows, tmem_a + g * 64 + kt * 8, bd, idesc, true);
+            } else {
+              mma_bf16_ts(tmem_d + g * kRows, tmem_a + g * 64 + kt * 8, bd, idesc, kt != 0);
+            }
           }
         commit(d_ready);
       }
@@ -177,7 +200,7 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
       const uint32_t ta = tmem_d + (uint32_t(quarter * 32) << 16) + kACol0 + colhalf * 32;
       uint32_t w[32];
 #pragma unroll 1
-      for (int g = 0; g < G; ++g) {
+      for (int g = 0; g < kW * G; ++g) {   // split: the G residual tiles follow the G hi tiles, in the image and in TMEM
         const uint4* src = reinterpret_cast<const uint4*>(a.img[dir] + (size_t)(g * kH + u) * kH + colhalf * 64);
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
@@ -266,7 +289,12 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
       for (int j = 0; j < CPT; ++j) {
         const bool valid = t < len[j];
         float hn;
-        if (G == 3) {   // GRU, gate rows r, z, n
+        if (G == 3 && kSplit) {   // fp32 precision: the gate functions of gru_fp32_kernel
+          const float r = 1.f / (1.f + expf(-(gc[j][0] + __uint_as_float(d[0][j]))));
+          const float z = 1.f / (1.f + expf(-(gc[j][1] + __uint_as_float(d[1][j]))));
+          const float nn = tanhf(gc[j][2] + r * (__uint_as_float(d[2][j]) + bn));
+          hn = nn + z * (h[j] - nn);
+        } else if (G == 3) {   // GRU, gate rows r, z, n
           const float r = sigmoid_f(gc[j][0] + __uint_as_float(d[0][j]));
           const float z = sigmoid_f(gc[j][1] + __uint_as_float(d[1][j]));
           const float nn = tanh_f(gc[j][2] + r * (__uint_as_float(d[2][j]) + bn));
@@ -282,7 +310,13 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
         }
         h[j] = valid ? hn : h[j];
         const int n = colhalf * CPT + j;
-        *reinterpret_cast<__nv_bfloat16*>(Hs + sw128_bf16(n, u, kRows * 128)) = __float2bfloat16_rn(h[j]);
+        if (kSplit) {
+          const __half hi = __float2half_rn(h[j]);
+          *reinterpret_cast<__half*>(Hs + sw128_bf16(n, u, kRows * 128)) = hi;
+          *reinterpret_cast<__half*>(Hs + kHsBytes + sw128_bf16(n, u, kRows * 128)) = __float2half_rn(h[j] - __half2float(hi));
+        } else {
+          *reinterpret_cast<__nv_bfloat16*>(Hs + sw128_bf16(n, u, kRows * 128)) = __float2bfloat16_rn(h[j]);
+        }
       }
       if (warp == 0) TR(1, 13);
 #if !ASB_RNN_FENCE_AT_MMA
@@ -318,10 +352,14 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
 
 namespace asb {
 
-size_t whh_umma_bytes(const asb_model* m) { return (size_t)m->G * kTileBytes; }
+static bool split_of(const asb_model* m) { return m->precision != ASB_PRECISION_FAST; }
 
+size_t whh_umma_bytes(const asb_model* m) { return (size_t)m->G * kTileBytes * (split_of(m) ? 2 : 1); }
+
+// fast precision: GRU and LSTM (bf16 operands); fp32 precision: the GRU with split fp16 operands
 bool rnn_umma_supported(const asb_model* m) {
-  return m->precision == ASB_PRECISION_FAST && (m->G == 3 || m->G == 4) && m->H == kH;
+  if (m->H != kH) return false;
+  return split_of(m) ? m->G == 3 : (m->G == 3 || m->G == 4);
 }
 
 int pack_whh_umma(asb_model* m, const asb_weights* src, cudaStream_t st) {
@@ -329,7 +367,7 @@ int pack_whh_umma(asb_model* m, const asb_weights* src, cudaStream_t st) {
     for (int dir = 0; dir < 2; ++dir) {
       const int n = m->G * kH * kH;
       pack_whh_umma_kernel<<<(n + 255) / 256, 256, 0, st>>>(
-          src->rnn_w_hh[layer][dir], reinterpret_cast<__nv_bfloat16*>(m->w.whh_umma[layer][dir]), m->G);
+          src->rnn_w_hh[layer][dir], reinterpret_cast<uint16_t*>(m->w.whh_umma[layer][dir]), m->G, split_of(m) ? 1 : 0);
       ASB_CHECK_LAUNCH("pack_whh_umma_kernel");
     }
   return ASB_OK;
@@ -348,29 +386,31 @@ static int rows_per_column(int B) {
 #endif
 }
 
-template <int G>
+template <int G, bool kSplit>
 static int launch_rnn_umma_g(const asb_model* m, RnnArgs& a, int B, bool use_tokens, cudaStream_t st) {
   const int cpt = rows_per_column(B);
   const int tok_bytes = 2 * cpt * a.T * 4;
   if (!use_tokens || tok_bytes > kMaxTokenBytes) a.tokens = nullptr;   // the caller materialised gi instead
-  const int smem = kHsBytes + 64 + 1024 + kGiSlots * cpt * G * 1024 + (a.tokens ? tok_bytes : 0);
-  static DeviceOnce once;   // one instance per G (function template)
+  constexpr int kHs = (kSplit ? 2 : 1) * kHsBytes;
+  const int smem = kHs + 64 + 1024 + kGiSlots * cpt * G * 1024 + (a.tokens ? tok_bytes : 0);
+  static DeviceOnce once;   // one instance per (G, kSplit) (function template)
   if (int rc = once.run([&] {
-        const int max_smem = kHsBytes + 64 + 1024 + kGiSlots * 8 * G * 1024 + kMaxTokenBytes;
-        cudaError_t e = cudaFuncSetAttribute(rnn_umma_kernel<G, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        const int max_smem = kHs + 64 + 1024 + kGiSlots * 8 * G * 1024 + kMaxTokenBytes;
+        cudaError_t e =
+            cudaFuncSetAttribute(rnn_umma_kernel<G, 2, kSplit>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         if (e == cudaSuccess)
-          e = cudaFuncSetAttribute(rnn_umma_kernel<G, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+          e = cudaFuncSetAttribute(rnn_umma_kernel<G, 4, kSplit>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         if (e == cudaSuccess)
-          e = cudaFuncSetAttribute(rnn_umma_kernel<G, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+          e = cudaFuncSetAttribute(rnn_umma_kernel<G, 8, kSplit>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         return check_cuda(e, "rnn_umma_kernel smem attribute");
       }))
     return rc;
   if (cpt == 2) {
-    rnn_umma_kernel<G, 2><<<dim3((B + 3) / 4, 2), kThreads, smem, st>>>(a);
+    rnn_umma_kernel<G, 2, kSplit><<<dim3((B + 3) / 4, 2), kThreads, smem, st>>>(a);
   } else if (cpt == 4) {
-    rnn_umma_kernel<G, 4><<<dim3((B + 7) / 8, 2), kThreads, smem, st>>>(a);
+    rnn_umma_kernel<G, 4, kSplit><<<dim3((B + 7) / 8, 2), kThreads, smem, st>>>(a);
   } else {
-    rnn_umma_kernel<G, 8><<<dim3((B + 15) / 16, 2), kThreads, smem, st>>>(a);
+    rnn_umma_kernel<G, 8, kSplit><<<dim3((B + 15) / 16, 2), kThreads, smem, st>>>(a);
   }
   ASB_CHECK_LAUNCH("rnn_umma_kernel");
   return ASB_OK;
@@ -386,13 +426,15 @@ int launch_rnn_umma(const asb_model* m, int layer, const float* gi, const long l
                     const int* lengths, float* out, int B, int T, cudaStream_t st) {
   RnnArgs a;
   for (int d = 0; d < 2; ++d) {
-    a.img[d] = reinterpret_cast<const __nv_bfloat16*>(m->w.whh_umma[layer][d]);
+    a.img[d] = reinterpret_cast<const uint16_t*>(m->w.whh_umma[layer][d]);
     a.bhhn[d] = m->w.bhh_n[layer][d];
   }
   a.gi = gi; a.lengths = lengths; a.out = out; a.B = B; a.T = T;
   a.tokens = tokens; a.tab = m->w.tab0; a.T_in = T_in; a.V = m->V; a.tok_flag = m->tok_flag_dev;
   const bool use_tokens = tokens != nullptr && layer == 0;
-  return m->G == 3 ? launch_rnn_umma_g<3>(m, a, B, use_tokens, st) : launch_rnn_umma_g<4>(m, a, B, use_tokens, st);
+  if (split_of(m)) return launch_rnn_umma_g<3, true>(m, a, B, use_tokens, st);
+  return m->G == 3 ? launch_rnn_umma_g<3, false>(m, a, B, use_tokens, st)
+                   : launch_rnn_umma_g<4, false>(m, a, B, use_tokens, st);
 }
 
 }  // namespace asb

@@ -149,7 +149,7 @@ extern "C" int asb_model_create(const asb_weights* src, int vocab, int n_art, in
   for (int l = 0; l < 2; ++l)
     for (int d = 0; d < 2; ++d) w.whh_umma[l][d] = rnnu ? static_cast<void*>(b + o_whhu[l][d]) : nullptr;
   m->decoder_impl = umma16 ? 2 : 0;   // the fp16-operand tcgen05 decoder (split operands in fp32 precision)
-  m->rnn_impl = rnnu ? 1 : 0;   // fast precision: the tcgen05 kernel (W_hh in tensor memory); the LSTM cell exists only there
+  m->rnn_impl = rnnu ? 1 : 0;   // the tcgen05 kernel (W_hh in tensor memory): fast precision GRU / LSTM, fp32 precision GRU (split operands)
 
   int rc = pack_recurrent_weights(m, src, st);
   if (!rc) rc = pack_dense_weights(m, src, st);
@@ -329,7 +329,7 @@ extern "C" int asb_model_decode(asb_model* m, const float* features, int64_t row
 extern "C" int asb_model_set_recurrent(asb_model* m, int impl) {
   if (!m) return set_error(ASB_ERR_INVALID, "asb_model_set_recurrent: null model");
   if (impl == 1 && !m->w.whh_umma[0][0])
-    return set_error(ASB_ERR_UNSUPPORTED, "asb_model_set_recurrent: the tcgen05 recurrent kernel needs fast precision and the GRU cell");
+    return set_error(ASB_ERR_UNSUPPORTED, "asb_model_set_recurrent: the tcgen05 recurrent kernel has no fp32-precision LSTM");
   if (impl != 0 && impl != 1) return set_error(ASB_ERR_INVALID, "asb_model_set_recurrent: impl must be 0 or 1");
   if (impl == 0 && m->G != ASB_CELL_GRU)
     return set_error(ASB_ERR_UNSUPPORTED, "asb_model_set_recurrent: the mma.sync kernel implements the GRU cell only");

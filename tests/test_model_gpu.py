@@ -285,6 +285,28 @@ def test_fp32_decoder_implementations_agree(mods):
     net.set_decoder("tcgen05")
 
 
+def test_fp32_recurrent_implementations_agree(mods):
+    """fp32 precision: the tcgen05 recurrent kernel with split fp16 operands (W_hh and h as hi + lo, three MMAs
+    per product; default) against the FFMA kernel and the fp32 oracle, ragged lengths, 300 steps."""
+    models, omodel = mods
+    sd = omodel.make_state_dict(45, 3, seed=4)
+    net = _build(models, sd, "fp32", n_art=3)
+    B, T = 13, 300
+    x = synthetic.tokens(B, T, 45, seed=6)
+    L = synthetic.sorted_lengths(B, 7, T, seed=6)
+    want = omodel.artspeech_forward(sd, x[:4], L[:4], torch.float32)
+    outs = {}
+    for impl in ("tcgen05", "mma"):
+        net.set_recurrent(impl)
+        with torch.no_grad():
+            outs[impl] = net(x.cuda(), L).cpu()
+        err = (outs[impl][:4, :want.shape[1]] - want).abs().max().item()
+        print(f"fp32 recurrent[{impl}] max-abs vs fp32 oracle {err:.3e}")
+        assert err <= TOL["fp32"] and not torch.isnan(outs[impl]).any()
+    assert (outs["tcgen05"] - outs["mma"]).abs().max().item() <= 5e-6
+    net.set_recurrent("tcgen05")
+
+
 def test_errors_and_state_dict(mods):
     models, omodel = mods
     sd = omodel.make_state_dict(45, 2, seed=0)
