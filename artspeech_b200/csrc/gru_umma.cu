@@ -7,17 +7,18 @@
 // Blackwell mapping
 //   * one CTA = 2*CPT (4, 8 or 16) batch rows of one direction - as few as still fill one wave of
 //     SMs, because the gate math (6 MUFU per unit and row) is what bounds a step;
-//   * W_hh (bf16) is the A operand and lives in tensor memory: lane = gate row, 64 columns per gate
-//     (two consecutive-k bf16 per 32-bit column), written ONCE with tcgen05.st at kernel start -
+//   * W_hh (fp16; bf16 until round 2: 8 significand bits against 11, and the recurrent operands dominated the
+//     fast-mode contour error) is the A operand and lives in tensor memory: lane = gate row, 64 columns per gate
+//     (two consecutive-k fp16 per 32-bit column), written ONCE with tcgen05.st at kernel start -
 //     G * 64 columns next to the G * 16 accumulator columns.  (The first version kept W_hh in shared
 //     memory: every step then re-read 96 KB through the SS form, 32+ clk per MMA; the TS form
 //     issues an N = 16 MMA every ~11 clk, tools/micro/umma_rate.cu.)
-//   * per step ONE ELECTED lane of a converged warp issues G x 8 tcgen05.mma (kind::f16, bf16 in,
-//     fp32 accumulate, M = 128 gate rows, N = 16 batch rows, K = 16): B = h as bf16 (shared
+//   * per step ONE ELECTED lane of a converged warp issues G x 8 tcgen05.mma (kind::f16, fp16 in,
+//     fp32 accumulate, M = 128 gate rows, N = 16 batch rows, K = 16): B = h as fp16 (shared
 //     memory, 4 KB, K-major, 128-byte swizzle), D = G x 16 columns, lane = hidden unit;
 //   * the 8 epilogue warps (thread = hidden unit, CPT batch columns) read D with tcgen05.ld - the
 //     gate pre-activations of one (unit, row) sit in the same lane, so the gate math is
-//     thread-local -, keep h (and the LSTM's c) in fp32 registers, write h as bf16 back into the B
+//     thread-local -, keep h (and the LSTM's c) in fp32 registers, write h as fp16 back into the B
 //     operand and the fp32 output row, and hand over to the MMA warp through one mbarrier; the
 //     input pre-activations of the next step are prefetched while the MMAs run.
 //   * kSplit = true (fp32 precision, GRU): W_hh and h are carried as hi + lo fp16 pairs (hi = fp16(v),
@@ -62,7 +63,7 @@ using namespace asb;
 using namespace asb::umma;
 
 constexpr int kRows = 16;                    // the MMA's N (columns past the CTA's rows stay zero)
-constexpr int kTileBytes = 128 * kH * 2;     // one gate tile of W_hh in bf16: 32 KB
+constexpr int kTileBytes = 128 * kH * 2;     // one gate tile of W_hh in fp16: 32 KB
 constexpr int kAhead = 3, kGiSlots = 4;        // look-ahead of the input pre-activations (steps), ring slots
 constexpr int kACol0 = 64;                   // TMEM: accumulators in columns [0, G*16), W_hh from column 64
 constexpr int kHsBytes = 2 * kRows * 128;    // h as the B operand: 2 k-atoms x 16 rows x 128 B
@@ -73,20 +74,20 @@ constexpr int kThreads = 288;
 __device__ __forceinline__ float sigmoid_f(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
 __device__ __forceinline__ float tanh_f(float x) { return 2.f * sigmoid_f(2.f * x) - 1.f; }
 
-// byte offset of element (row, k) inside a K-major, 128-byte-swizzled bf16 operand whose k-atoms
+// byte offset of element (row, k) inside a K-major, 128-byte-swizzled 16-bit operand whose k-atoms
 // (64 elements) are `atom_bytes` apart
 __host__ __device__ constexpr uint32_t sw128_bf16(uint32_t row, uint32_t k, uint32_t atom_bytes) {
   return (k >> 6) * atom_bytes + (row >> 3) * 1024u + (row & 7u) * 128u +
          ((((k & 63u) >> 3) ^ (row & 7u)) << 4) + (k & 7u) * 2u;
 }
 
-// whh (G*128, 128) fp32 -> bf16, same row-major layout (a row = the 64 TMEM columns of one lane);
+// whh (G*128, 128) fp32 -> fp16, same row-major layout (a row = the 64 TMEM columns of one lane);
 // split: fp16 hi image followed by the fp16 residual image
 __global__ void pack_whh_umma_kernel(const float* __restrict__ whh, uint16_t* __restrict__ img, int G, int split) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= G * kH * kH) return;
   if (!split) {
-    img[i] = __bfloat16_as_ushort(__float2bfloat16_rn(whh[i]));
+    img[i] = __half_as_ushort(__float2half_rn(whh[i]));
   } else {
     const __half hi = __float2half_rn(whh[i]);
     img[i] = __half_as_ushort(hi);
@@ -95,7 +96,7 @@ __global__ void pack_whh_umma_kernel(const float* __restrict__ whh, uint16_t* __
 }
 
 struct RnnArgs {
-  const uint16_t* img[2];        // per direction: bf16 (fast) or fp16 hi | fp16 lo (split)
+  const uint16_t* img[2];        // per direction: fp16 (fast) or fp16 hi | fp16 lo (split)
   const float* bhhn[2];          // GRU: b_hh of the n gate
   const float* gi;               // (B*T, 2, G*H) input pre-activations, or (layer 0) null:
   const long long* tokens;       //   (B, T_in) token ids and
@@ -119,7 +120,7 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
   uint64_t* bars = reinterpret_cast<uint64_t*>(Hs + kHs);
   float* Gs = reinterpret_cast<float*>(Hs + kHs + 64);   // [kGiSlots][CPT][G][256 threads] input pre-activations
   int* Toks = reinterpret_cast<int*>(Gs + kGiSlots * CPT * G * 256);   // [2 * CPT rows][T] token ids (layer 0)
-  uint64_t* h_ready = bars + 1;  // h (bf16) of this step is in shared memory, D has been read
+  uint64_t* h_ready = bars + 1;  // h (fp16) of this step is in shared memory, D has been read
   uint64_t* d_ready = bars + 2;  // this step's MMAs completed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
 
@@ -159,7 +160,7 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
   if (warp == kCtlWarp) {
     // the whole warp walks the loop, one ELECTED lane issues (behind `lane == 0` the compiler wraps
     // every tcgen05.mma in an R2UR/ELECT loop that costs far more than the MMA itself)
-    const uint32_t idesc = kSplit ? idesc_f16_m128(kRows) : idesc_bf16_m128(kRows);
+    const uint32_t idesc = idesc_f16_m128(kRows);
     const uint64_t bdesc0 = smem_desc_k_sw128(smem_u32(Hs));
     const uint32_t tmem_a = tmem_d + kACol0;
     TR_DECL;
@@ -315,7 +316,7 @@ __global__ void __launch_bounds__(kThreads, 1) rnn_umma_kernel(const RnnArgs a) 
           *reinterpret_cast<__half*>(Hs + sw128_bf16(n, u, kRows * 128)) = hi;
           *reinterpret_cast<__half*>(Hs + kHsBytes + sw128_bf16(n, u, kRows * 128)) = __float2half_rn(h[j] - __half2float(hi));
         } else {
-          *reinterpret_cast<__nv_bfloat16*>(Hs + sw128_bf16(n, u, kRows * 128)) = __float2bfloat16_rn(h[j]);
+          *reinterpret_cast<__half*>(Hs + sw128_bf16(n, u, kRows * 128)) = __float2half_rn(h[j]);
         }
       }
       if (warp == 0) TR(1, 13);
@@ -356,7 +357,7 @@ static bool split_of(const asb_model* m) { return m->precision != ASB_PRECISION_
 
 size_t whh_umma_bytes(const asb_model* m) { return (size_t)m->G * kTileBytes * (split_of(m) ? 2 : 1); }
 
-// fast precision: GRU and LSTM (bf16 operands); fp32 precision: the GRU with split fp16 operands
+// fast precision: GRU and LSTM (fp16 operands); fp32 precision: the GRU with split fp16 operands
 bool rnn_umma_supported(const asb_model* m) {
   if (m->H != kH) return false;
   return split_of(m) ? m->G == 3 : (m->G == 3 || m->G == 4);

@@ -187,8 +187,8 @@ class _NativeHandle:
 
 
 class ArtSpeech(nn.Module):
-    """models.py:99-145.  ``precision``: "fast" (bf16 recurrent GEMM, tf32 elsewhere, fp32
-    accumulate/state; contours within 2e-3 of the fp32 reference) or "fp32" (within 1e-5).
+    """models.py:99-145.  ``precision``: "fast" (fp16 GEMM operands on the tensor cores, fp32 accumulate/state;
+    contours within 2e-3 of the fp32 reference) or "fp32" (operands split into hi + lo fp16 pairs, within 1e-5).
     ``rnn``: "gru" (the reference's cell, models.py:111) or "lstm" (the other member of RNNType,
     phoneme_to_articulation/__init__.py:47-49; same state_dict keys as nn.LSTM).
     Token ids outside [0, vocab_size) raise IndexError like nn.Embedding (models.py:135): at once for host

@@ -554,7 +554,7 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None,
-            "dtype": "fp16/bf16 tcgen05 operands (tf32 layer-1 projection), fp32 accumulate and state" if args.precision == "fast" else "f32 (3xTF32)",
+            "dtype": "fp16 tcgen05 operands, fp32 accumulate and state; fp32 geometry" if args.precision == "fast" else "f32 accumulate over split fp16 operands (hi + lo); fp32 geometry",
             "data": "synthetic",
             "config": workload_config(world, B, T, args.precision),
             "serial": serial,

@@ -195,8 +195,9 @@ typedef struct asb_model asb_model;
 #define ASB_CELL_GRU 3  /* nn.GRU, gate rows r, z, n (models.py:111) - both precisions                       */
 #define ASB_CELL_LSTM 4 /* nn.LSTM, gate rows i, f, g, o (RNNType.LSTM, phoneme_to_articulation/__init__.py:47-49)
                            - both precisions (fast: tcgen05 kernel; fp32: lstm_fp32_kernel) */
-#define ASB_PRECISION_FAST 0 /* bf16 recurrent GEMM, tf32 elsewhere, fp32 accumulate/state (2e-3 gate) */
-#define ASB_PRECISION_FP32 1 /* 3xTF32 / FFMA everywhere (1e-5 gate)                                  */
+#define ASB_PRECISION_FAST 0 /* fp16 GEMM operands on tcgen05, fp32 accumulate/state (2e-3 gate) */
+#define ASB_PRECISION_FP32 1 /* split fp16 operands (hi + lo, three MMAs per product) on tcgen05; FFMA / 3xTF32 kernels
+                                for the LSTM, n_samples != 50 and set_decoder / set_recurrent (1e-5 gate) */
 
 /* Device pointers to fp32 parameters in the reference's state_dict layout (SURVEY.md 8b;
  * models.py:109-120).  Arrays of per-articulator pointers are HOST arrays of device pointers. */

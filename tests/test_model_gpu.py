@@ -351,10 +351,15 @@ def test_tcgen05_recurrent_kernel_matches_register_resident_kernel(mods):
             b = net(x.cuda(), L)
         torch.cuda.synchronize()
         assert not torch.isnan(b).any()
-        assert float((a - b).abs().max()) <= 1e-3, (B, T, float((a - b).abs().max()))
+        # the register-resident kernel keeps bf16 operands (8 significand bits), the tcgen05 kernel fp16 (11): the two
+        # differ by the former's rounding, and the tcgen05 kernel is the one closer to the fp32 oracle
+        assert float((a - b).abs().max()) <= 2e-3, (B, T, float((a - b).abs().max()))
         nb = min(B, 6)
         want = omodel.artspeech_forward(sd, x[:nb], L[:nb], torch.float32)
-        assert float((b[:nb, :want.shape[1]].cpu() - want).abs().max()) <= 2e-3
+        err_b = float((b[:nb, :want.shape[1]].cpu() - want).abs().max())
+        err_a = float((a[:nb, :want.shape[1]].cpu() - want).abs().max())
+        print(f"recurrent kernels [{B}x{T}] vs fp32 oracle: tcgen05 (fp16) {err_b:.3e}, mma.sync (bf16) {err_a:.3e}")
+        assert err_b <= 1.2e-3 and err_a <= 2e-3
 
 
 @pytest.mark.parametrize("precision,tol", [("fast", 2e-3), ("fp32", 1e-5)])
