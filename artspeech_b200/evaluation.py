@@ -384,9 +384,10 @@ class PipelinedEvaluator:
     step's chain on another stream the recurrent kernels of step i+1 run beside the geometry kernels of
     step i.  Every slot owns its buffers and its running total; ``finish()`` joins the streams, adds
     the slots' totals and sums them over ranks with ONE all-reduce per evaluation (run_test aggregates
-    once, evaluation.py:142-159)."""
+    once, evaluation.py:142-159).  Measured at batch 256 x 100 (tools/pipeline_depth.py, 60 steps): 0.437 / 0.372 /
+    0.351 / 0.351 ms per step at depth 1 / 2 / 3 / 4."""
 
-    def __init__(self, model, batch, seq_len, articulators=None, upper_incisor=None, depth=2):
+    def __init__(self, model, batch, seq_len, articulators=None, upper_incisor=None, depth=3):
         dev = model.embedding.weight.device
         self.model, self.device, self.depth = model, dev, depth
         self.articulators = articulators

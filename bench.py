@@ -12,7 +12,7 @@ encoder_decoder/evaluation.py:142-159).
 
 Prints ONE JSON line (rank 0).
   value     frames/s with inputs resident in HBM: K steps through PipelinedEvaluator (each step ONE
-            native call, asb_eval_step; two steps in flight on two streams, two input sets of 103 MB
+            native call, asb_eval_step; three steps in flight on three streams, two input sets of 103 MB
             alternate, per-step working set 335 MB > L2), the WHOLE region between two CUDA events,
             the all-reduce included, max over ranks.  `serial` holds the round-1 measure (one captured
             step at a time, L2 flushed between steps, per-step events) beside it.
@@ -72,7 +72,7 @@ def workload_config(world, B, T, precision):
                            f"all-reduce of {N_ART + 14} fp64 per evaluation",
             "l2": "two input sets (103 MB each) alternate, per-step working set 335 MB > L2; the `serial` record "
                   "flushes 256 MiB between steps",
-            "launch": "each step is one native call (asb_eval_step); two steps in flight on two streams "
+            "launch": "each step is one native call (asb_eval_step); three steps in flight on three streams "
                       "(PipelinedEvaluator); the whole K-step region is timed between two CUDA events"}
 
 
@@ -341,8 +341,8 @@ def run_ours(args):
         return float(t.item())
 
     def pipelined_region(net, steps, warm, sampler=None):
-        """K steps, two in flight; ONE all-reduce of the running totals at the end; returns (ms, total)."""
-        pipe = evaluation.PipelinedEvaluator(net, B, T, upper_incisor=uinc_d, depth=2)
+        """K steps, three in flight; ONE all-reduce of the running totals at the end; returns (ms, total)."""
+        pipe = evaluation.PipelinedEvaluator(net, B, T, upper_incisor=uinc_d, depth=3)
         pipe.begin()
         for i in range(warm):
             pipe.step(tok_sets[i & 1], lengths, lengths_dev, tgt_sets[i & 1])
@@ -678,7 +678,7 @@ def config5_sweep(model, dev, rank, world, n_utt, max_over_ranks, barrier):
         dev_len.append(L.to(dev))
         valid += int(L.sum())
     uinc = synthetic.UPPER_INCISOR_REF.to(dev)
-    pipe = evaluation.PipelinedEvaluator(model, Bc, Tc, upper_incisor=uinc, depth=2)
+    pipe = evaluation.PipelinedEvaluator(model, Bc, Tc, upper_incisor=uinc, depth=3)
 
     def run():
         pipe.begin()
