@@ -396,15 +396,18 @@ ASB_API int asb_lstm_train_backward(const float* whh_fwd, const float* whh_bwd, 
                             const float* gates, const int32_t* lengths_dev, int B, int T, int hidden, float* dgi,
                             float* hprev, void* stream);
 
-/* Decoder implementation: 2 = tcgen05/TMEM kernel with fp16 operands (default in fast precision with
- * n_samples = 50), 1 = the same with tf32 operands (round 1), 0 = mma.sync kernel (always used in fp32 precision).  Both compute models.py:140-145.  The
- * layer-1 input projection follows the same switch (tcgen05 proj_umma.cu / mma.sync linear256). */
+/* Decoder implementation: 2 = tcgen05/TMEM kernel with fp16 operands (default with n_samples = 50; in fp32
+ * precision the same kernel with split hi + lo operands), 1 = the tcgen05 kernel with tf32 operands (round 1; fast
+ * precision only), 0 = mma.sync kernel (single-pass tf32, 3xTF32 in fp32 precision; any n_samples).  All compute
+ * models.py:140-145.  The layer-1 input projection follows the same switch (proj_umma16.cu / proj_umma.cu /
+ * mma.sync linear256). */
 ASB_API int asb_model_set_decoder(asb_model* m, int impl);
 
-/* Recurrent-layer implementation (fast precision): 1 = W_hh resident in TENSOR MEMORY, tcgen05.mma
- * kind::f16 (TS form) with the gates fused behind tcgen05.ld (default; GRU and LSTM; 0.55 us per
- * time step at batch 256 on B200), 0 = W_hh resident in registers, mma.sync bf16 (GRU only,
- * 0.84-0.91 us per step).  Both compute models.py:111,136-138. */
+/* Recurrent-layer implementation: 1 = W_hh resident in TENSOR MEMORY, tcgen05.mma kind::f16 (TS form) with the
+ * gates fused behind tcgen05.ld (default; fast precision: fp16 operands, GRU and LSTM, 0.55 us per time step at
+ * batch 256 on B200; fp32 precision: split hi + lo operands, GRU only, 1.07 us per step), 0 = fast precision:
+ * W_hh resident in registers, mma.sync bf16 (GRU only, 0.84-0.91 us per step); fp32 precision: the FFMA kernels
+ * (GRU 2.9 us per step; the LSTM's only implementation there).  All compute models.py:111,136-138. */
 ASB_API int asb_model_set_recurrent(asb_model* m, int impl);
 
 /* Per-stage device timing of asb_model_forward (CUDA events on `stream`): enable, run forwards,
