@@ -3,6 +3,9 @@ import os
 import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
+from artspeech_b200 import _lib
+if os.environ.get("ASB_LIB"):   # a tools/build_variant.py library
+    _lib.LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), os.environ["ASB_LIB"])
 from artspeech_b200 import evaluation, models, synthetic
 
 B, T = 256, 100
@@ -11,7 +14,7 @@ L = [T] * B
 ld = torch.tensor(L, dtype=torch.int32, device="cuda")
 sets = [(synthetic.tokens(B, T, 45, seed=s).cuda(),
          synthetic.contours(B * T, 10, 50, seed=10 + s, device="cuda").view(B, T, 10, 2, 50)) for s in range(2)]
-for depth in (1, 2, 3, 4):
+for depth in ((3,) if os.environ.get("ASB_LIB") or len(sys.argv) > 2 else (1, 2, 3, 4)):
     pipe = evaluation.PipelinedEvaluator(net, B, T, depth=depth)
     best = None
     for rep in range(3):
