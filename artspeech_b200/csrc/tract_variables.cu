@@ -396,6 +396,9 @@ static int tv_launch(const float* sets_ptr, int64_t sets, int n_art, const int32
       nw = cand;
     }
   }
+#ifdef ASB_TV_FORCE_NW   // experiments (tools/build_variant.py)
+  nw = ASB_TV_FORCE_NW < max_nw ? ASB_TV_FORCE_NW : max_nw;
+#endif
   const size_t smem = tv_smem_bytes(nw, slots);
   static asb::DeviceOnce once;
   if (int rc = once.run([&] {
