@@ -308,6 +308,30 @@ def test_fp32_recurrent_implementations_agree(mods):
     net.set_recurrent("tcgen05")
 
 
+@pytest.mark.parametrize("precision", ["fast", "fp32"])
+@pytest.mark.parametrize("n_samples", [40, 64])
+def test_other_contour_sizes(mods, precision, n_samples):
+    """ArtSpeech(n_samples != 50) (models.py:100-101): the tcgen05 decoder and projection are specialised for 50
+    points, other sizes run the mma.sync decoder / projection; the recurrent layers are the same kernels."""
+    models, omodel = mods
+    sd = omodel.make_state_dict(45, 4, n_samples=n_samples, seed=5)
+    net = models.ArtSpeech(45, 4, n_samples=n_samples, precision=precision)
+    net.load_state_dict(sd)
+    net = net.cuda().eval()
+    B, T = 9, 31
+    x = synthetic.tokens(B, T, 45, seed=8)
+    L = synthetic.sorted_lengths(B, 3, T, seed=8)
+    with torch.no_grad():
+        out = net(x.cuda(), L).cpu()
+    want = omodel.artspeech_forward(sd, x, L, torch.float32)
+    assert out.shape == want.shape == (B, max(L), 4, 2, n_samples)
+    err = (out - want).abs().max().item()
+    print(f"n_samples={n_samples}[{precision}] max-abs {err:.3e}")
+    assert err <= TOL[precision]
+    with pytest.raises(ValueError):
+        net.set_decoder("tcgen05")
+
+
 def test_errors_and_state_dict(mods):
     models, omodel = mods
     sd = omodel.make_state_dict(45, 2, seed=0)
