@@ -99,7 +99,12 @@ constexpr int kTileM = 128;
 constexpr int kHeadN = 112;                 // 2 * 50 head rows padded to a multiple of 16
 constexpr int kChunkK = 32;                 // K extent of one A chunk (one A-ready barrier): 16 TMEM columns of fp16 pairs
 constexpr int kBlockK = 64;                 // fp16 per 128-byte swizzle row: one weight block serves two A chunks
-constexpr int kStages = 4;                  // weight ring: 32 KB stages = one 256-row block or two 128- / 112-row ones
+#ifndef ASB_DEC_STAGES
+#define ASB_DEC_STAGES 4
+#endif
+// (measured with 2 / 3 / 4 stages: 0.098 / 0.100 / 0.100 ms fast precision - the ring is not what bounds the kernel;
+// four keep two hi + lo piece pairs in flight in fp32 precision)
+constexpr int kStages = ASB_DEC_STAGES;     // weight ring: 32 KB stages = one 256-row block or two 128- / 112-row ones
 constexpr int kStageBytes = 256 * 128;
 constexpr int kXStride = 129;               // x-hat row stride (floats), conflict-free per-thread rows
 constexpr int kTilePitch = 36;              // per-warp 32 x 32 transposition tile of the input load (floats per row)
@@ -430,7 +435,6 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
-    const uint32_t ps_addr = smem_u32(Ps);
     uint32_t pa = 0, artc = 0;
     uint32_t r[32], r2[32], r4[4];
     float4* otile = reinterpret_cast<float4*>(smem + kOffOut + (warp - kHeadWarp0) * kOutTile);
@@ -444,7 +448,6 @@ __global__ void __launch_bounds__(kThreads, 1) decoder_umma16_kernel(const UmmaA
         const int art = g0 + k;
         const uint32_t Q = tmem_base + lane_sel + ((artc & 1) ^ 1) * 256;
         const uint32_t pb = pa & 1;
-        const uint32_t prm = ps_addr + pb * kArtParams * 4;
         mbar_wait(&pfull[pb], (pa >> 1) & 1);
         mbar_wait(&dbar[3], artc & 1);
         fence_after_sync();
