@@ -476,7 +476,7 @@ def run_ours(args):
         model32 = models.ArtSpeech(VOCAB, N_ART, precision="fp32")
         model32.load_state_dict(model.state_dict())
         model32 = model32.to(dev).eval()
-        k32 = max(2, min(K, 8))
+        k32 = max(2, K)
         ms32, acc32, _ = pipelined_region(model32, k32, 3)
         s32 = evaluation.summarize(acc32, N_ART)
         fp32_mode = {"value": world * frames * k32 / (ms32 * 1e-3), "unit": UNIT, "ms_per_step": ms32 / k32,
@@ -709,13 +709,14 @@ def config5_sweep(model, dev, rank, world, n_utt, max_over_ranks, barrier):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--seq-len", type=int, default=100)
     ap.add_argument("--precision", default="fast", choices=["fast", "fp32"])
-    ap.add_argument("--cpu-batch", type=int, default=32, help="utterances in the bounded CPU-baseline sample")
+    ap.add_argument("--cpu-batch", type=int, default=256,
+                    help="utterances in the bounded CPU-baseline sample (256 = one whole configs[1] batch, ~10 s of host time)")
     ap.add_argument("--ref-batch", type=int, default=16, help="utterances per step of --impl reference")
     ap.add_argument("--c3-frames", type=int, default=1048576)
     ap.add_argument("--c5-utterances", type=int, default=65536)
