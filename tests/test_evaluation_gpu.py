@@ -232,3 +232,35 @@ def test_graphed_evaluator_follows_weight_changes(setup):
     c = g()["outputs"]
     torch.cuda.synchronize()
     assert torch.equal(c, want)
+
+
+@pytest.mark.parametrize("precision", ["fast", "fp32"])
+def test_repeated_runs_are_bit_identical(precision):
+    """Every kernel of the path is deterministic by construction (fixed summation orders, no atomics on results):
+    the forward and a whole evaluation with three steps in flight on three streams must repeat bit for bit.
+    Stands in for racecheck, which is closed on this pool (tools/determinism_check.py is the long version)."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from artspeech_b200 import evaluation, models
+    torch.manual_seed(1)
+    net = models.ArtSpeech(45, 10, precision=precision).cuda().eval()
+    B, T = 41, 37
+    x = synthetic.tokens(B, T, 45, seed=4).cuda()
+    L = [int(v) for v in synthetic.sorted_lengths(B, 9, T, seed=4)]
+    with torch.no_grad():
+        first = net(x, L).clone()
+        for _ in range(8):
+            assert torch.equal(net(x, L), first)
+    ld = torch.tensor(L, dtype=torch.int32, device="cuda")
+    sets = [(synthetic.tokens(B, T, 45, seed=s).cuda(),
+             synthetic.contours(B * T, 10, 50, seed=10 + s, device="cuda").view(B, T, 10, 2, 50)) for s in range(3)]
+    pipe = evaluation.PipelinedEvaluator(net, B, T, depth=3)
+    totals = []
+    for _ in range(4):
+        pipe.begin()
+        for i in range(7):
+            pipe.step(sets[i % 3][0], L, ld, sets[i % 3][1])
+        totals.append(pipe.finish(reduce=False).clone())
+    torch.cuda.synchronize()
+    assert all(torch.equal(t, totals[0]) for t in totals[1:])
+    assert float(totals[0][-1]) == 7.0 * sum(L)
