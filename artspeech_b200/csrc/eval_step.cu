@@ -5,7 +5,7 @@
 // The step is ~10 kernels of 20-150 us each.  Enqueued from Python they leave the device idle between
 // launches (0.9 ms eager vs 0.48 ms of device time per 25 600-frame step); enqueued from here the host
 // needs ~30 us per step, so an evaluation loop over resident batches is device-bound without a CUDA graph
-// per batch, and two steps can be kept in flight on two streams from one host thread.
+// per batch, and several steps (three by default, evaluation.PipelinedEvaluator) can be kept in flight on their own streams from one host thread.
 //
 // The target's tract variables do not depend on the forward pass: they run on `side_stream` (forked
 // here, joined before the accumulation), enqueued AFTER the forward's kernels - a full wave of

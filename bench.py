@@ -564,7 +564,7 @@ def run_ours(args):
             "kernel_ms_sum": round(kernel_sum, 4),
             "kernel_ms_how": "CUDA events with the launches queued behind a spin kernel (no host gap inside an interval), "
                              "L2 flushed before each; sum <= serial ms_per_step x 1.1 is the consistency check, the "
-                             "pipelined ms_per_step is below the sum because two steps overlap",
+                             "pipelined ms_per_step is below the sum because three steps overlap",
             "roofline": roofline, "fp32_mode": fp32_mode, "gpu_baseline": gpu_baseline, "configs": configs,
             "cpu_baseline": cpu_baseline,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
